@@ -1,0 +1,195 @@
+/*
+ * tt_b200.h - C ABI of libtt_b200.so: the two_towers training + retrieval hot path on B200 (sm_100a).
+ *
+ * The reference (mateomarin/two_towers) has no FFI: its boundary is the Python nn.Module surface and
+ * every op below is whatever stock PyTorch dispatches at the cited call site (cuDNN GRU, cuBLAS, ATen).
+ * Each entry point names the reference lines it replaces.  The Python host in two_towers_b200/ binds
+ * these with ctypes and mirrors the reference classes on top.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to caller-owned memory; row-major, contiguous unless a stride is given
+ *   - activations / parameters fp32; token ids int32 or int64 (flag); result indices int64 (torch convention)
+ *   - no hidden allocation: scratch comes from the caller, sized by the matching *_workspace() function
+ *   - returns 0 on success, negative on error (tt_last_error() gives the text); no exceptions cross the ABI
+ *   - stream is a cudaStream_t passed as void*; the caller has made the right device current
+ *   - re-entrant per stream; the only global state is one-time cudaFuncSetAttribute and the error string
+ */
+#ifndef TT_B200_H
+#define TT_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TT_OK 0
+#define TT_ERR_INVALID (-1)
+#define TT_ERR_CUDA (-2)
+#define TT_ERR_WORKSPACE (-3)
+
+int tt_abi_version(void);
+const char* tt_last_error(void);
+/* which engine the GEMM-shaped ops run on: "simt-fp32" or "tcgen05-bf16x3" */
+const char* tt_engine(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K-A  embedding gather.  Replaces the per-word CPU lookup `self.word2vec[word]` + zero padding
+ * (simple_two_tower.py:88-110, enhanced_two_tower.py:144-166) and nn.Embedding of the missing token-id
+ * model (train_two_tower.py:29).  Row pad_id (if >= 0) reads as all zeros; ids outside [0,vocab) -> zeros.
+ * out [n_tokens, E] fp32. */
+int tt_embed_gather(const void* ids, int ids_are_i64, int64_t n_tokens, const float* table, int64_t vocab,
+                    int32_t E, int64_t pad_id, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K-B + K-C  one GRU layer, all timesteps, 1 or 2 directions (dir 1 = reverse).  Replaces nn.GRU
+ * (simple_two_tower.py:17-32, margin_two_tower.py:12-28, enhanced_two_tower.py:17-33): gate order r,z,n,
+ *   r = s(gi_r+gh_r)  z = s(gi_z+gh_z)  n = tanh(gi_n + r*gh_n)  h = (1-z)*n + z*h,  zero initial state.
+ * The input is either x [B,T,In] fp32, or (ids != NULL) rows of `table` gathered on the fly (In == table E).
+ * dropout_p > 0 applies inverted dropout to the INPUT with the library's Philox stream (seed, offset)
+ * - this is nn.GRU's inter-layer dropout when used for layer 1 (reference: dropout=0.1).
+ * lengths (optional, [B]): steps t >= lengths[b] keep h and emit 0 (pack_padded_sequence semantics);
+ * NULL = the reference behaviour (all T steps processed). */
+typedef struct tt_gru_layer {
+  int32_t B, T, In, H, ndir;
+  int32_t save_for_backward;       /* 1: fill `gates` */
+  const float* x;                  /* [B,T,In] or NULL when ids given */
+  const void* ids;                 /* [B,T] or NULL */
+  int32_t ids_are_i64;
+  int32_t _pad0;
+  const float* table;              /* [vocab,In] */
+  int64_t vocab, pad_id;
+  float dropout_p;
+  int32_t _pad1;
+  uint64_t seed, offset;
+  const float* w_ih[2];            /* [3H,In] */
+  const float* w_hh[2];            /* [3H,H]  */
+  const float* b_ih[2];            /* [3H]    */
+  const float* b_hh[2];            /* [3H]    */
+  const int32_t* lengths;          /* [B] or NULL */
+  float* out;                      /* [B,T,ndir*H] */
+  float* h_n;                      /* [ndir,B,H]   */
+  float* gates;                    /* [ndir,B,T,4H] (r,z,n,gh_n) when save_for_backward */
+  void* workspace;
+  uint64_t workspace_bytes;
+} tt_gru_layer;
+
+uint64_t tt_gru_layer_fwd_workspace(const tt_gru_layer* a);
+int tt_gru_layer_fwd(const tt_gru_layer* a, void* stream);
+
+/* K-C' fused BPTT of the same layer (autograd of nn.GRU at loss.backward(), simple_two_tower.py:237).
+ * `fwd` carries the forward pointers (x/ids, weights, out, gates).  d_out / d_h_n may be NULL (= zero).
+ * Weight grads are WRITTEN (not accumulated).  d_x may be NULL (frozen embedding table below layer 0). */
+typedef struct tt_gru_layer_grad {
+  tt_gru_layer fwd;
+  const float* d_out;              /* [B,T,ndir*H] or NULL */
+  const float* d_h_n;              /* [ndir,B,H]   or NULL */
+  float* d_x;                      /* [B,T,In]     or NULL */
+  float* d_w_ih[2];
+  float* d_w_hh[2];
+  float* d_b_ih[2];
+  float* d_b_hh[2];
+  void* workspace;
+  uint64_t workspace_bytes;
+} tt_gru_layer_grad;
+
+uint64_t tt_gru_layer_bwd_workspace(const tt_gru_layer_grad* a);
+int tt_gru_layer_bwd(const tt_gru_layer_grad* a, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K-D  projection head on the pooled state cat(h_n[-2], h_n[-1]):
+ *   y1 = v W1^T + b1 ; y2 = relu(LayerNorm(y1; eps 1e-5)) ; [y3 = y2 W2^T + b2] ; [out = y/max(|y|,1e-12)]
+ * Replaces query_proj/doc_proj/projection + F.normalize (simple_two_tower.py:35-61,
+ * margin_two_tower.py:30-35,58-62, enhanced_two_tower.py:36-60).  v is given as two halves
+ * (v_lo = h_n[-2], v_hi = h_n[-1], each [B,In/2]) so the concat is never materialised.
+ * D2 == 0: no second Linear (margin).  dropout_p > 0 applies the reference's nn.Dropout(0.1) that follows the ReLU
+ * (simple_two_tower.py:39, margin_two_tower.py:34; train mode only) with the library's Philox stream. */
+typedef struct tt_head {
+  int32_t B, In, P1, D2, normalize;
+  float dropout_p;
+  uint64_t seed, offset;
+  const float* v_lo; const float* v_hi;
+  const float* w1; const float* b1; const float* ln_w; const float* ln_b;
+  const float* w2; const float* b2;
+  float* y1;        /* [B,P1] pre-LN (saved) */
+  float* stats;     /* [B,2] mean, rstd (saved) */
+  float* y2;        /* [B,P1] post ReLU (+dropout) (saved; == output when D2==0 and !normalize) */
+  float* y3;        /* [B,D2] pre-normalise (saved; == output when !normalize); unused if D2==0 */
+  float* out;       /* [B,Dout] normalised output when normalize, else may be NULL */
+  float* norm;      /* [B] when normalize */
+} tt_head;
+int tt_head_fwd(const tt_head* a, void* stream);
+
+typedef struct tt_head_grad {
+  tt_head fwd;
+  const float* d_out;              /* [B,Dout] */
+  float* d_v_lo; float* d_v_hi;    /* [B,In/2] each */
+  float* d_w1; float* d_b1; float* d_ln_w; float* d_ln_b; float* d_w2; float* d_b2;   /* written */
+  void* workspace; uint64_t workspace_bytes;
+} tt_head_grad;
+uint64_t tt_head_bwd_workspace(const tt_head_grad* a);
+int tt_head_bwd(const tt_head_grad* a, void* stream);
+
+/* F.normalize(p=2, dim=1, eps) alone (margin_two_tower.py:39-40,77-78; enhanced_two_tower.py:74-75) */
+int tt_l2norm_fwd(const float* x, int32_t B, int32_t D, float eps, float* y, float* norm, void* stream);
+int tt_l2norm_bwd(const float* y, const float* norm, const float* dy, int32_t B, int32_t D, float eps,
+                  float* dx, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K-E  in-batch score + cross-entropy, never materialising the [Bl,Bg] matrix.
+ *   logit[i][j] = <x_i, y_j> * inv_temp - margin * (j != pos_offset + i),   i < Bl, j < Bg
+ *   row_loss[i] = logsumexp_j logit[i][j] - logit[i][pos_offset+i]
+ * Replaces matmul/temperature + [eye-margin shift] + F.cross_entropy(sim, arange):
+ *   simple_two_tower.py:73-78 (call twice with x,y swapped), margin_two_tower.py:80-85,
+ *   enhanced_two_tower.py:77-82, 92-101 (margin > 0).  Under data parallelism x = this rank's rows,
+ *   y = the all-gathered matrix and pos_offset = rank * Bl.
+ * bwd: dx[i] = gscale*inv_temp*sum_j (p_ij - 1{j=pos}) y_j ;  dy[j] = gscale*inv_temp*sum_i (p_ij - 1{..}) x_i
+ *   dx, dy are WRITTEN. */
+uint64_t tt_score_ce_workspace(int32_t Bl, int32_t Bg, int32_t D);
+int tt_score_ce_fwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
+                    float inv_temp, float margin, float* row_loss, float* row_lse,
+                    void* workspace, uint64_t workspace_bytes, void* stream);
+int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
+                    float inv_temp, float margin, const float* row_lse, float gscale,
+                    float* dx, float* dy, void* workspace, uint64_t workspace_bytes, void* stream);
+
+/* K-F / K-H  row-wise exact-fp32 top-k of  score(i,j) = <x_i,y_j>  (mode 0)  or cosine (mode 1, norms
+ * clamped at 1e-8 like F.cosine_similarity).  Every dot product is one fp32 FMA chain over d = 0..D-1 in
+ * ascending order, so equal inputs give bit-equal scores; ties break to the LOWEST index.
+ * mask_pos_offset >= 0: score(i, mask_pos_offset+i) := -1 before selection (get_hard_negatives,
+ * enhanced_two_tower.py:123-133).  index_base is added to the emitted indices (global ids of a corpus shard:
+ * the retrieval scan simple_two_tower.py:333-340 / validate_enhanced.py:73-80 / app.py:94-101).
+ * k <= 32.  out_val [Q,k] fp32 descending, out_idx [Q,k] int64.  Rows with N < k are padded (-inf, -1). */
+uint64_t tt_rows_topk_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode);
+int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
+                 int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx,
+                 void* workspace, uint64_t workspace_bytes, void* stream);
+
+/* K-I  merge S per-shard top-k lists ([S,Q,k] each, as all-gathered) into the global top-k:
+ * order by score descending, then lowest global id.  Entries with idx < 0 are ignored. */
+int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k,
+                  float* out_val, int64_t* out_idx, void* stream);
+
+/* MRR@k / recall: rank (1-based) of the first entry of topk_idx[q] equal to relevant[q], 0 if none;
+ * rr = 1/rank (simple_two_tower.py:364-373, compare_models.py:55-74). */
+int tt_mrr_ranks(const int64_t* topk_idx, const int64_t* relevant, int32_t Q, int32_t k,
+                 int32_t* first_rank, float* rr, void* stream);
+
+/* K-G  explicit-negatives hinge (enhanced_two_tower.py:102-121):
+ *   row_loss[i] = max(0, margin - cos(q_i,pos_i) + mean_k cos(q_i, neg[i*k+kk])),  cos eps 1e-8
+ * bwd writes dq, dpos, dneg scaled by gscale (= upstream_grad / B). */
+int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D,
+                 float margin, float* row_loss, void* stream);
+int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D,
+                 float margin, float gscale, float* dq, float* dpos, float* dneg, void* stream);
+
+/* plain fp32 GEMM used by the ops above, exported for kernel-level tests:
+ * C[M,N] = alpha * A[M,K] * B[N,K]^T + beta * C + bias[N]   (bias may be NULL) */
+int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+               const float* bias, int32_t M, int32_t N, int32_t K, float alpha, float beta, void* stream);
+
+/* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
+int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

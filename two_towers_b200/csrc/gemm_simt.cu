@@ -1,0 +1,164 @@
+// fp32 SIMT GEMM with generic operand strides, 2-way pointer batching, split-K and segmented
+// (batch x time) reduction views.  This is the exact-fp32 engine: it serves the small GEMMs (head,
+// per-step recurrence at tiny batch) and is the on-device cross-check for the tcgen05 bf16x3 engine.
+// Tile 128x128x16, 256 threads, 8x8 register micro-tile split in 4+4 so shared-memory float4 reads are
+// conflict free.  Each C element is ONE fp32 FMA chain over the reduction index in ascending order.
+#include <stdarg.h>
+#include "common.cuh"
+#include "simt_tile.cuh"
+
+namespace tt {
+
+static thread_local char g_err[512] = "ok";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+template <bool A_RC, bool B_RC>
+__global__ void __launch_bounds__(NT) gemm_f32_kernel(GemmArgs g) {
+  __shared__ __align__(16) float As[BK][LDS];
+  __shared__ __align__(16) float Bs[BK][LDS];
+  const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+  const int batch = blockIdx.z / g.splitk, split = blockIdx.z % g.splitk;
+  const float* __restrict__ A = g.A[batch];
+  const float* __restrict__ B = g.B[batch];
+  float* __restrict__ C = g.C[batch];
+  const float* __restrict__ bias = g.bias[batch];
+  const int bm = blockIdx.y * BM, bn = blockIdx.x * BN;
+  int kchunk = (g.K + g.splitk - 1) / g.splitk;
+  kchunk = (kchunk + BK - 1) / BK * BK;
+  const int kbeg = split * kchunk;
+  const int kend = min(g.K, kbeg + kchunk);
+
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  float ra[8], rb[8];
+  if (kbeg < kend) {
+    load_frag<A_RC>(ra, A, g.a_rs, g.a_cs, bm, g.M, kbeg, kend, g.seg_len, g.seg_stride, g.a_seg_off, t);
+    load_frag<B_RC>(rb, B, g.b_rs, g.b_cs, bn, g.N, kbeg, kend, g.seg_len, g.seg_stride, g.b_seg_off, t);
+  }
+  for (int k0 = kbeg; k0 < kend; k0 += BK) {
+    __syncthreads();
+    store_frag<A_RC>(ra, As, t);
+    store_frag<B_RC>(rb, Bs, t);
+    __syncthreads();
+    if (k0 + BK < kend) {
+      load_frag<A_RC>(ra, A, g.a_rs, g.a_cs, bm, g.M, k0 + BK, kend, g.seg_len, g.seg_stride, g.a_seg_off, t);
+      load_frag<B_RC>(rb, B, g.b_rs, g.b_cs, bn, g.N, k0 + BK, kend, g.seg_len, g.seg_stride, g.b_seg_off, t);
+    }
+    tile_fma(acc, As, Bs, tx, ty);
+  }
+
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int m = bm + tile_row(ty, i);
+    if (m >= g.M) continue;
+    float* crow = C + (int64_t)m * g.ldc;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int n = bn + tile_col(tx, j);
+      if (n >= g.N) continue;
+      float v = g.alpha * acc[i][j];
+      if (g.splitk > 1) {
+        if (split == 0 && bias) v += bias[n];
+        atomicAdd(crow + n, v);
+      } else {
+        if (g.beta != 0.f) v += g.beta * crow[n];
+        if (bias) v += bias[n];
+        crow[n] = v;
+      }
+    }
+  }
+}
+
+__global__ void scale_rows_kernel(float* C, int64_t ldc, int M, int N, float beta) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)M * N) return;
+  float* p = C + (i / N) * ldc + (i % N);
+  *p = beta == 0.f ? 0.f : beta * *p;
+}
+
+int gemm_f32(const GemmArgs& gin, cudaStream_t s) {
+  GemmArgs g = gin;
+  if (g.M <= 0 || g.N <= 0) return TT_OK;
+  if (g.nbatch < 1) g.nbatch = 1;
+  TT_CHECK_ARG(g.nbatch <= 2, "gemm_f32: nbatch %d > 2", g.nbatch);
+  const int64_t tiles = ceil_div(g.M, BM) * ceil_div(g.N, BN) * g.nbatch;
+  if (g.splitk <= 0) {
+    g.splitk = 1;
+    if (tiles < 148 && g.K >= 4096) {
+      int64_t want = ceil_div(2 * 148, tiles);
+      int64_t maxs = g.K / 1024;
+      g.splitk = (int)(want < maxs ? want : maxs);
+      if (g.splitk < 1) g.splitk = 1;
+    }
+  }
+  if (g.splitk > 1) {
+    // atomics accumulate into C: pre-scale it by beta (0 -> clear)
+    if (g.beta != 1.f) {
+      for (int b = 0; b < g.nbatch; ++b) {
+        int64_t n = (int64_t)g.M * g.N;
+        scale_rows_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
+      }
+      TT_LAUNCH_CHECK();
+    }
+  }
+  dim3 grid((unsigned)ceil_div(g.N, BN), (unsigned)ceil_div(g.M, BM), (unsigned)(g.nbatch * g.splitk));
+  const bool arc = g.a_cs == 1, brc = g.b_cs == 1;
+  if (arc && brc) gemm_f32_kernel<true, true><<<grid, NT, 0, s>>>(g);
+  else if (arc && !brc) gemm_f32_kernel<true, false><<<grid, NT, 0, s>>>(g);
+  else if (!arc && brc) gemm_f32_kernel<false, true><<<grid, NT, 0, s>>>(g);
+  else gemm_f32_kernel<false, false><<<grid, NT, 0, s>>>(g);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+// ------------------------------------------------------------------------------ column sums
+__global__ void colsum_kernel(const float* __restrict__ X, int64_t ld, int64_t M, int N, float* out) {
+  __shared__ float red[8][33];
+  const int n = blockIdx.x * 32 + threadIdx.x;
+  float acc = 0.f;
+  if (n < N)
+    for (int64_t m = (int64_t)blockIdx.y * 8 + threadIdx.y; m < M; m += (int64_t)gridDim.y * 8) acc += X[m * ld + n];
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && n < N) {
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v += red[i][threadIdx.x];
+    atomicAdd(out + n, v);
+  }
+}
+int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cudaStream_t s) {
+  TT_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * N, s));
+  if (M <= 0 || N <= 0) return TT_OK;
+  int64_t gy = ceil_div(M, 64);
+  if (gy > 128) gy = 128;
+  colsum_kernel<<<dim3((unsigned)ceil_div(N, 32), (unsigned)gy), dim3(32, 8), 0, s>>>(X, ld, M, N, out);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+}  // namespace tt
+
+extern "C" {
+int tt_abi_version(void) { return 1; }
+const char* tt_last_error(void) { return tt::last_error(); }
+
+int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,
+               int32_t M, int32_t N, int32_t K, float alpha, float beta, void* stream) {
+  tt::GemmArgs g{};
+  g.A[0] = A; g.B[0] = B; g.C[0] = C; g.bias[0] = bias;
+  g.a_rs = lda; g.a_cs = 1; g.b_rs = ldb; g.b_cs = 1; g.ldc = ldc;
+  g.M = M; g.N = N; g.K = K; g.nbatch = 1; g.splitk = 1; g.alpha = alpha; g.beta = beta;
+  return tt::gemm_f32(g, (cudaStream_t)stream);
+}
+}
