@@ -1,0 +1,80 @@
+"""CPU: the C-ABI library loads and exports every symbol include/tt_b200.h declares; struct layouts seen by
+ctypes equal the C compiler's.  No compute calls (no GPU here)."""
+import ctypes
+import os
+import re
+import subprocess
+import tempfile
+
+import pytest
+
+from conftest import ROOT
+from two_towers_b200 import _lib
+
+HEADER = os.path.join(ROOT, "include", "tt_b200.h")
+
+
+def _declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(tt_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_declares_functions():
+    syms = _declared_symbols()
+    assert len(syms) >= 20 and "tt_gru_layer_fwd" in syms and "tt_rows_topk" in syms
+
+
+def test_library_exports_every_declared_symbol():
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for s in _declared_symbols():
+        assert hasattr(handle, s), f"{s} declared in tt_b200.h but not exported"
+
+
+def test_binding_covers_every_declared_symbol():
+    assert sorted(_lib.SIGNATURES) == _declared_symbols()
+
+
+def test_library_reports_version_and_engine_without_gpu():
+    lib = _lib.lib()
+    assert lib.tt_abi_version() == 1
+    assert lib.tt_engine().decode() in ("simt-fp32", "tcgen05-bf16x3")
+
+
+def test_struct_layouts_match_c_compiler():
+    prog = r'''
+#include <stdio.h>
+#include <stddef.h>
+#include "tt_b200.h"
+int main(void){
+  printf("%zu %zu %zu %zu\n", sizeof(tt_gru_layer), sizeof(tt_gru_layer_grad), sizeof(tt_head), sizeof(tt_head_grad));
+  printf("%zu %zu %zu %zu %zu\n", offsetof(tt_gru_layer,x), offsetof(tt_gru_layer,seed), offsetof(tt_gru_layer,w_ih),
+         offsetof(tt_gru_layer,lengths), offsetof(tt_gru_layer,workspace_bytes));
+  printf("%zu %zu %zu\n", offsetof(tt_head,seed), offsetof(tt_head,v_lo), offsetof(tt_head,norm));
+  printf("%zu %zu\n", offsetof(tt_gru_layer_grad,d_out), offsetof(tt_head_grad,d_out));
+  return 0; }
+'''
+    with tempfile.TemporaryDirectory() as d:
+        c = os.path.join(d, "l.c")
+        open(c, "w").write(prog)
+        exe = os.path.join(d, "l")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
+        out = subprocess.check_output([exe]).decode().split()
+    out = list(map(int, out))
+    G, GG, H, HG = _lib.GruLayer, _lib.GruLayerGrad, _lib.Head, _lib.HeadGrad
+    exp = [ctypes.sizeof(G), ctypes.sizeof(GG), ctypes.sizeof(H), ctypes.sizeof(HG),
+           G.x.offset, G.seed.offset, G.w_ih.offset, G.lengths.offset, G.workspace_bytes.offset,
+           H.seed.offset, H.v_lo.offset, H.norm.offset, GG.d_out.offset, HG.d_out.offset]
+    assert out == exp
+
+
+def test_cpu_tensors_are_rejected_loudly():
+    import torch
+    import two_towers_b200 as tt
+    m = tt.EnhancedTwoTowerModel(20, 4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.randn(2, 3, 20), torch.randn(2, 3, 20))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        tt.InfoNCELoss()(torch.randn(2, 4), torch.randn(2, 4))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        tt.get_hard_negatives(torch.randn(4), torch.randn(5, 4), 0, 2)

@@ -1,0 +1,112 @@
+"""CPU: host-side mirror of the reference interface - state_dict keys/shapes, init parity from the same seed,
+constructor / attribute surface - and the data-parallel plumbing under gloo with world_size 2."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import two_towers_b200 as tt
+from oracle import ref_port as rp
+from two_towers_b200 import distributed as dops
+
+CASES = [("simple", tt.SimpleTwoTower, 300, 16), ("margin", tt.TwoTowerModel, 300, 16),
+         ("enhanced", tt.EnhancedTwoTowerModel, 300, 8)]
+
+
+@pytest.mark.parametrize("kind,cls,E,H", CASES)
+def test_state_dict_matches_reference_layout_and_init(kind, cls, E, H):
+    torch.manual_seed(7)
+    ours = cls(E, H)
+    torch.manual_seed(7)
+    port = rp.build_port(kind, E, H)
+    a, b = ours.state_dict(), port.state_dict()
+    assert list(a.keys()) == list(b.keys())
+    for k in a:
+        assert a[k].shape == b[k].shape, k
+        assert torch.equal(a[k], b[k]), f"{k}: same seed must give the reference's init"
+    ours.load_state_dict(b, strict=True)
+    port.load_state_dict(a, strict=True)
+
+
+def test_param_counts_match_survey():
+    n = lambda m: sum(p.numel() for p in m.parameters())
+    assert n(tt.SimpleTwoTower(300, 128)) == 1336192
+    assert n(tt.TwoTowerModel(300, 256)) == 4211456
+    assert n(tt.EnhancedTwoTowerModel(300, 128)) == 4409088
+    assert len(tt.SimpleTwoTower(300, 8).state_dict()) == 44
+    assert len(tt.TwoTowerModel(300, 8).state_dict()) == 36
+
+
+def test_module_surface():
+    m = tt.EnhancedTwoTowerModel(embedding_dim=300, hidden_dim=8)
+    assert tt.EnhancedTwoTower is tt.EnhancedTwoTowerModel
+    for a in ("query_encoder", "doc_encoder", "query_proj", "doc_proj", "encode_query", "encode_doc"):
+        assert hasattr(m, a)
+    mm = tt.TwoTowerModel(300, 8)
+    for a in ("projection", "encode", "compute_similarity", "encode_query", "encode_doc"):
+        assert hasattr(mm, a)
+    from two_towers_b200 import enhanced_two_tower, margin_two_tower, simple_two_tower, two_tower_model
+    assert simple_two_tower.InfoNCELoss().temperature == 0.1
+    assert margin_two_tower.InfoNCELoss().temperature == 0.07
+    assert enhanced_two_tower.InfoNCELoss().temperature == 0.07
+    l = enhanced_two_tower.MarginRankingLoss()
+    assert (l.margin, l.temperature) == (0.2, 0.1)
+    tok = two_tower_model.TwoTowerModel(vocab_size=50, embedding_dim=12, hidden_dim=6,
+                                        pretrained_embeddings=torch.randn(50, 12), freeze_embeddings=True)
+    assert sum(p.numel() for p in tok.parameters()) == 2 * (18 * 12 + 18 * 6 + 36)
+    # optimizer / clipping plumbing used by the reference loops (simple_two_tower.py:193,239)
+    opt = torch.optim.AdamW(m.parameters(), lr=1e-4, weight_decay=0.01)
+    assert len(opt.param_groups[0]["params"]) == 44 - 0
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _dp_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        Bl, D = 3, 5
+        qg = torch.randn(world * Bl, D); dg = torch.randn(world * Bl, D)
+        w = torch.nn.Parameter(torch.randn(D, D))            # a "tower" shared by all ranks
+        # single-process oracle on the concatenated batch
+        wf = w.detach().clone().requires_grad_(True)
+        full = rp.margin_ce_inbatch(qg @ wf, dg @ wf, 0.2, 0.1)
+        full.backward()
+        # sharded: local rows vs all-gathered docs, local partial = sum(rows)/B_global
+        q, d = qg[rank * Bl:(rank + 1) * Bl] @ w, dg[rank * Bl:(rank + 1) * Bl] @ w
+        d_all = dops.all_gather_rows(d)
+        s = (q @ d_all.t()) / 0.1
+        mask = torch.ones_like(s); idx = torch.arange(Bl); mask[idx, idx + rank * Bl] = 0
+        s = s - 0.2 * mask
+        part = torch.nn.functional.cross_entropy(s, idx + rank * Bl, reduction="sum") / (world * Bl)
+        loss = dops.sum_over_ranks(part, dist.group.WORLD)
+        red = dops.GradientAllReducer([w], bucket_bytes=1)
+        loss.backward()
+        red.finish()
+        ok = abs(loss.item() - full.item()) < 1e-5 * abs(full.item()) and \
+            (w.grad - wf.grad).norm() < 1e-5 * wf.grad.norm()
+        lo, hi = dops.shard_bounds(11)
+        ok = ok and (lo, hi) == ((0, 6) if rank == 0 else (6, 11))
+        ret[rank] = (bool(ok), loss.item(), full.item(), (w.grad - wf.grad).abs().max().item(), lo, hi)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_plumbing_gloo_world2():
+    world = 2
+    ret = mp.get_context("spawn").Manager().dict()
+    mp.spawn(_dp_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    assert all(ret.get(r) and ret[r][0] for r in range(world)), dict(ret)
+
+
+def test_single_process_collectives_are_identity():
+    x = torch.randn(3, 4, requires_grad=True)
+    assert dops.all_gather_rows(x) is x
+    assert dops.sum_over_ranks(x.sum()) is not None
+    assert dops.shard_bounds(10) == (0, 10)

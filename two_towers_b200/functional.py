@@ -1,18 +1,14 @@
 """Autograd-aware Python wrappers over the C ABI (include/tt_b200.h).  Each Function only allocates buffers,
 fills the argument struct and calls the library; there is no torch arithmetic on the hot path."""
 import ctypes as C
-import itertools
 
 import torch
 
 from . import _lib as L
 
-_seed_counter = itertools.count(1)
-
-
 def _next_seed():
     """Per-call Philox seed derived from torch's CPU generator so torch.manual_seed() makes runs repeatable."""
-    return int(torch.randint(0, 2 ** 62, (1,)).item()) ^ next(_seed_counter)
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
 
 
 def _arr2(tensors):
