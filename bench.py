@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py - train query-doc pairs/s (fwd + loss + hard-negative mining + bwd + optimizer) of the two_towers hot path.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (N>1: launched by torchrun)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port) on the host cores
+
+Workload (BASELINE.json configs[2] at N=1, configs[3] at N>1, weak scaling): EnhancedTwoTowerModel(300, 128)
+(bi-GRU hidden 256, 2 layers, LayerNorm projection head), MarginRankingLoss in-batch branch, row top-8 hard
+negatives, B = 4096 pairs per GPU, query length 32, doc length 128, synthetic token ids over a 3 000 000 x 300
+frozen table (the size of word2vec-google-news-300), random-init weights.  One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+E, HID, TQ, TD, TOPK = 300, 128, 32, 128, 8
+GRU_H = 2 * HID
+METRIC = "train query-doc pairs/sec (fwd+bwd)"
+# algorithmic GEMM flops per pair, fwd+bwd = 3 x fwd: 12*Hg*(300+4*Hg) per token per tower
+FLOPS_PER_PAIR = 3.0 * 12 * GRU_H * (E + 4 * GRU_H) * (TQ + TD)
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--batch", type=int, default=4096, help="pairs per GPU (4096 = the BASELINE config)")
+    p.add_argument("--vocab", type=int, default=3_000_000)
+    p.add_argument("--cpu-batch", type=int, default=256, help="pairs per step of the bounded CPU sample")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=d["hbm_gbs"], bf16_burst=d["bf16_tflops"], bf16_sustained=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, src="fallback")
+
+
+def make_ids(B, T, V, gen):
+    """Power-law (Zipf-like) ids in [1,V), length ~U[T/4,T], pad id 0 after the length (still processed)."""
+    u = torch.rand(B, T, generator=gen)
+    ids = torch.exp(u * torch.log(torch.tensor(float(V)))).long().clamp_(1, V - 1)
+    lens = torch.randint(max(1, T // 4), T + 1, (B, 1), generator=gen)
+    ids[torch.arange(T).unsqueeze(0) >= lens] = 0
+    return ids
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------- CPU reference arm
+def cpu_reference(steps, warmup, B, seed=1234):
+    """The reference's own CPU implementation of the path: its nn.Modules restated over stock torch CPU ops
+    (oracle/ref_port.py, pinned to the unmodified reference by tests/golden), fp32, train() mode, all host
+    threads; one step = fwd + MarginRankingLoss + bwd + Adam step on a bounded sample of B pairs
+    (pre-embedded float inputs, as the reference's Dataset hands them over).  Returns (pairs/s, ms/step, threads)."""
+    from oracle import ref_port as rp
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    model = rp.build_port("enhanced", E, HID).train()
+    opt = torch.optim.Adam(model.parameters())
+    gen = torch.Generator().manual_seed(seed)
+    V = 13085
+    table = torch.randn(V, E, generator=gen) * 0.1
+    table[0] = 0
+    batches = [(table[make_ids(B, TQ, V, gen)], table[make_ids(B, TD, V, gen)]) for _ in range(2)]
+    times = []
+    for i in range(warmup + steps):
+        q, d = batches[i % 2]
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        qv, dv = model(q, d)
+        loss = rp.margin_ce_inbatch(qv, dv, 0.2, 0.1)
+        with torch.no_grad():
+            rp.stable_topk(torch.nn.functional.cosine_similarity(qv.unsqueeze(1), dv.unsqueeze(0), dim=2)
+                           .masked_fill(torch.eye(B, dtype=torch.bool), -1.0), TOPK)
+        loss.backward()
+        opt.step()
+        loss.item()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    return B / (ms / 1e3), ms, threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    val, ms, threads = cpu_reference(args.steps, args.warmup, args.cpu_batch)
+    sample = (f"{args.cpu_batch} pairs/step (BASELINE batch is {args.batch}/GPU), Tq/Td {TQ}/{TD}, pre-embedded fp32 "
+              f"inputs, {args.steps} timed steps after {args.warmup} warm-up")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": dict(workload_config(args.batch, args.gpus, args.vocab), cpu_sample_batch=args.cpu_batch),
+        "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------- this repo's arm
+def top_kernel_roofline(dev, pk):
+    """Dominant kernel timed alone with CUDA events on its launch stream: the GEMM engine at the layer-1
+    input-projection shape of the doc tower ([B*Td, 2*Hg] x [2*Hg, 3*Hg], one direction).  Operands (1 GiB + 1.5 GiB
+    output) exceed the 126 MB L2, so every launch streams from HBM (no flush needed)."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    M, N, K = 4096 * TD, 3 * GRU_H, 2 * GRU_H
+    a = torch.randn(M, K, device=dev) * 0.1
+    b = torch.randn(N, K, device=dev) * 0.1
+    c = torch.empty(M, N, device=dev)
+    st = torch.cuda.current_stream()
+    run = lambda: L.check(lib.tt_gemm_nt(L.ptr(a), K, L.ptr(b), K, L.ptr(c), N, None, M, N, K, 1.0, 0.0, L.stream()), "gemm")
+    for _ in range(2):
+        run()
+    n = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(st)
+    for _ in range(n):
+        run()
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    achieved = 2.0 * M * N * K / (ms * 1e-3) / 1e12
+    return {"bound": "tensor", "achieved": achieved, "peak": pk["bf16_burst"], "unit": "TFLOP/s",
+            "frac": achieved / pk["bf16_burst"], "traffic": None,
+            "kernel": f"GEMM engine ({lib.tt_engine().decode()}) M={M} N={N} K={K}", "ms_per_launch": ms,
+            "peak_source": f"bf16 dense burst, {pk['src']} (kernel timed alone)"}
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    import two_towers_b200 as tt
+    from two_towers_b200 import _lib as L
+    from two_towers_b200 import distributed as dops
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: the product path has no CPU fallback"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+    lib = L.lib()
+    B, V = args.batch, args.vocab
+    torch.manual_seed(0)                                 # same weights on every rank
+    model = tt.EnhancedTwoTowerModel(E, HID).to(dev).train()
+    gen = torch.Generator().manual_seed(1234 + rank)
+    table = torch.empty(V, E, device=dev).normal_(0, 0.1, generator=torch.Generator(device=dev).manual_seed(7))
+    table[0] = 0
+    model.attach_embeddings(table, pad_id=0)
+    crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
+    opt = torch.optim.Adam(model.parameters(), fused=True)
+    reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None
+    nb = 4
+    host = [(make_ids(B, TQ, V, gen).pin_memory(), make_ids(B, TD, V, gen).pin_memory()) for _ in range(nb)]
+    resident = [(q.to(dev), d.to(dev)) for q, d in host]
+
+    def step(q, d):
+        opt.zero_grad(set_to_none=True)
+        qv, dv = model(q, d)
+        loss = crit(qv, dv)
+        d_all = dops.all_gather_rows(dv.detach(), group) if world > 1 else dv.detach()
+        hard = tt.get_hard_negatives_batch(qv.detach(), d_all, k=TOPK, pos_offset=rank * B)
+        loss.backward()
+        if reducer is not None:
+            reducer.finish()
+        opt.step()
+        return loss, hard
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(*resident[i % nb])
+    # ---- value: inputs resident in HBM, CUDA events on the launch stream, max over ranks
+    sampler = ClockSampler(local)
+    st = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.start()
+    k0 = lib.tt_kernel_launches()
+    e0.record(st)
+    for i in range(args.steps):
+        loss, _ = step(*resident[i % nb])
+    e1.record(st)
+    barrier()
+    launches = int(lib.tt_kernel_launches() - k0)
+    clocks = sampler.stop()
+    ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = ms_total.item() / args.steps
+    value = world * B / (ms_step * 1e-3)
+    # ---- e2e: pinned host ids -> device every step, loss read back every step, wall clock, max over ranks
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        q, d = host[i % nb]
+        loss, _ = step(q.to(dev, non_blocking=True), d.to(dev, non_blocking=True))
+        loss_val = loss.item()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * args.steps / e2e_s.item()
+    h2d = B * (TQ + TD) * 8
+    if rank == 0:
+        pk = peaks()
+        line = {
+            "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(B, world, V),
+            "e2e": {"value": e2e_val, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+            "gpu_launches": launches, "clocks": clocks, "loss": loss_val,
+            "engine": lib.tt_engine().decode(),
+            "step_tflops_per_gpu": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12,
+            "step_frac_of_bf16_sustained": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],
+        }
+        del resident[:], host[:]
+        torch.cuda.empty_cache()
+        line["roofline"] = top_kernel_roofline(dev, pk)
+        if world == 1 and not args.no_cpu_baseline:
+            val, ms, threads = cpu_reference(3, 1, args.cpu_batch)
+            line["cpu_baseline"] = {"value": val, "unit": "pairs/s", "cores": threads, "kind": "port",
+                                    "sample": f"{args.cpu_batch} pairs/step, same model/loss/mining/optimizer, "
+                                              f"pre-embedded fp32 inputs, 3 timed steps after 1 warm-up ({ms:.0f} ms/step)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def workload_config(B, world, V):
+    return {"workload": "enhanced_two_tower: EnhancedTwoTowerModel(300,128) bi-GRU h256 x2 layers + LayerNorm head, "
+                        "MarginRankingLoss in-batch (global negatives under DP), row top-8 hard negatives, Adam step "
+                        "(BASELINE configs[2] at 1 GPU, configs[3] at N GPUs)",
+            "batch_per_gpu": B, "global_batch": B * world, "query_len": TQ, "doc_len": TD, "vocab": V,
+            "parallelism": f"dp{world}", "l2": "activations per step (>10 GB) exceed the 126 MB L2; 4 rotating id batches"}
+
+
+if __name__ == "__main__":
+    a = parse()
+    run_reference(a) if a.impl == "reference" else run_ours(a)

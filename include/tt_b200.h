@@ -30,6 +30,8 @@ int tt_abi_version(void);
 const char* tt_last_error(void);
 /* which engine the GEMM-shaped ops run on: "simt-fp32" or "tcgen05-bf16x3" */
 const char* tt_engine(void);
+/* number of CUDA kernels this library has launched in this process (monotonic) */
+uint64_t tt_kernel_launches(void);
 
 /* ---------------------------------------------------------------------------------------------
  * K-A  embedding gather.  Replaces the per-word CPU lookup `self.word2vec[word]` + zero padding

@@ -62,6 +62,7 @@ SIGNATURES = {
     "tt_abi_version": (C.c_int, []),
     "tt_last_error": (C.c_char_p, []),
     "tt_engine": (C.c_char_p, []),
+    "tt_kernel_launches": (u64, []),
     "tt_embed_gather": (C.c_int, [P, C.c_int, i64, P, i64, i32, i64, P, P]),
     "tt_gru_layer_fwd_workspace": (u64, [C.POINTER(GruLayer)]),
     "tt_gru_layer_fwd": (C.c_int, [C.POINTER(GruLayer), P]),
@@ -86,7 +87,6 @@ SIGNATURES = {
 }
 
 _lib = None
-launch_count = 0          # C-ABI calls made (each launches >= 1 kernel); bench.py reports kernel counts from the library
 
 
 def lib():

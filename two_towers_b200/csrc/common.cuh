@@ -8,6 +8,8 @@
 namespace tt {
 
 void set_error(const char* fmt, ...);
+void note_launch();                 // counts kernel launches (bench.py reports them as gpu_launches)
+unsigned long long launches();
 
 #define TT_CHECK_ARG(cond, ...)                      \
   do {                                               \

@@ -17,6 +17,9 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* last_error() { return g_err; }
+static unsigned long long g_launches = 0;
+void note_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
+unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 template <bool A_RC, bool B_RC>
 __global__ void __launch_bounds__(NT) gemm_f32_kernel(GemmArgs g) {
@@ -106,13 +109,14 @@ int gemm_f32(const GemmArgs& gin, cudaStream_t s) {
     if (g.beta != 1.f) {
       for (int b = 0; b < g.nbatch; ++b) {
         int64_t n = (int64_t)g.M * g.N;
-        scale_rows_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
+        tt::note_launch(); scale_rows_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
       }
       TT_LAUNCH_CHECK();
     }
   }
   dim3 grid((unsigned)ceil_div(g.N, BN), (unsigned)ceil_div(g.M, BM), (unsigned)(g.nbatch * g.splitk));
   const bool arc = g.a_cs == 1, brc = g.b_cs == 1;
+  note_launch();
   if (arc && brc) gemm_f32_kernel<true, true><<<grid, NT, 0, s>>>(g);
   else if (arc && !brc) gemm_f32_kernel<true, false><<<grid, NT, 0, s>>>(g);
   else if (!arc && brc) gemm_f32_kernel<false, true><<<grid, NT, 0, s>>>(g);
@@ -142,7 +146,7 @@ int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cud
   if (M <= 0 || N <= 0) return TT_OK;
   int64_t gy = ceil_div(M, 64);
   if (gy > 128) gy = 128;
-  colsum_kernel<<<dim3((unsigned)ceil_div(N, 32), (unsigned)gy), dim3(32, 8), 0, s>>>(X, ld, M, N, out);
+  tt::note_launch(); colsum_kernel<<<dim3((unsigned)ceil_div(N, 32), (unsigned)gy), dim3(32, 8), 0, s>>>(X, ld, M, N, out);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -151,6 +155,7 @@ int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cud
 
 extern "C" {
 int tt_abi_version(void) { return 1; }
+uint64_t tt_kernel_launches(void) { return tt::launches(); }
 const char* tt_last_error(void) { return tt::last_error(); }
 
 int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,

@@ -47,6 +47,7 @@ static int launch_gather(const void* ids, int ids_are_i64, int64_t n_tokens, con
   int64_t blocks = ceil_div(n_tokens, 8);
   if (blocks > 148 * 16) blocks = 148 * 16;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  note_launch();
   if (ids_are_i64)
     gather_rows_kernel<int64_t><<<(unsigned)blocks, 256, 0, s>>>((const int64_t*)ids, n_tokens, table, vocab, E,
                                                                pad_id, out, p, inv_keep, seed, offset);
@@ -67,7 +68,7 @@ static int launch_dropout(const float* x, float* y, int64_t n, float p, uint64_t
   if (n <= 0) return TT_OK;
   int64_t blocks = ceil_div(n, 256);
   if (blocks > 148 * 32) blocks = 148 * 32;
-  dropout_kernel<<<(unsigned)blocks, 256, 0, s>>>(x, y, n, p, 1.f / (1.f - p), seed, offset);
+  tt::note_launch(); dropout_kernel<<<(unsigned)blocks, 256, 0, s>>>(x, y, n, p, 1.f / (1.f - p), seed, offset);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -222,7 +223,7 @@ int tt_gru_layer_fwd(const tt_gru_layer* a, void* stream) {
   const unsigned cb = ew_blocks((int64_t)nd * B * H);
   for (int step = 0; step < T; ++step) {
     TT_TRY(gemm_f32(r, s));
-    gru_cell_fwd_kernel<<<cb, 256, 0, s>>>(gi, gh, a->h_n, a->out, a->save_for_backward ? a->gates : nullptr,
+    tt::note_launch(); gru_cell_fwd_kernel<<<cb, 256, 0, s>>>(gi, gh, a->h_n, a->out, a->save_for_backward ? a->gates : nullptr,
                                            a->lengths, B, T, H, nd, step);
   }
   TT_LAUNCH_CHECK();
@@ -269,7 +270,7 @@ int tt_gru_layer_bwd(const tt_gru_layer_grad* a, void* stream) {
   r.M = B; r.N = H; r.K = 3 * H; r.nbatch = nd; r.splitk = 1; r.alpha = 1.f; r.beta = 1.f;
   const unsigned cb = ew_blocks((int64_t)nd * B * H);
   for (int step = T - 1; step >= 0; --step) {
-    gru_cell_bwd_kernel<<<cb, 256, 0, s>>>(dhs, a->d_out, f->gates, f->out, dG, f->lengths, B, T, H, nd, step);
+    tt::note_launch(); gru_cell_bwd_kernel<<<cb, 256, 0, s>>>(dhs, a->d_out, f->gates, f->out, dG, f->lengths, B, T, H, nd, step);
     if (step == 0) break;
     for (int d = 0; d < nd; ++d) {
       const int t = d == 0 ? step : T - 1 - step;

@@ -123,7 +123,7 @@ extern "C" {
 int tt_l2norm_fwd(const float* x, int32_t B, int32_t D, float eps, float* y, float* norm, void* stream) {
   TT_CHECK_ARG(x && y && B >= 0 && D > 0, "l2norm_fwd: bad args");
   if (B == 0) return TT_OK;
-  l2norm_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(x, y, norm, B, D, eps);
+  tt::note_launch(); l2norm_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(x, y, norm, B, D, eps);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -131,7 +131,7 @@ int tt_l2norm_bwd(const float* y, const float* norm, const float* dy, int32_t B,
                   void* stream) {
   TT_CHECK_ARG(y && norm && dy && dx && B >= 0 && D > 0, "l2norm_bwd: bad args");
   if (B == 0) return TT_OK;
-  l2norm_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(y, norm, dy, dx, B, D, eps);
+  tt::note_launch(); l2norm_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(y, norm, dy, dx, B, D, eps);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -143,7 +143,7 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   TT_TRY(gemm_f32(nt_gemm(a->v_lo, Hh, a->w1, In, a->y1, P, a->b1, B, P, Hh, 0.f), s));
   TT_TRY(gemm_f32(nt_gemm(a->v_hi, Hh, a->w1 + Hh, In, a->y1, P, nullptr, B, P, Hh, 1.f), s));
   const float pdrop = a->dropout_p;
-  ln_relu_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(a->y1, a->ln_w, a->ln_b, a->y2, a->stats, B, P, 1e-5f, pdrop,
+  tt::note_launch(); ln_relu_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(a->y1, a->ln_w, a->ln_b, a->y2, a->stats, B, P, 1e-5f, pdrop,
                                                               pdrop > 0.f ? 1.f / (1.f - pdrop) : 1.f, a->seed, a->offset);
   TT_LAUNCH_CHECK();
   const float* last = a->y2;
@@ -153,7 +153,7 @@ int tt_head_fwd(const tt_head* a, void* stream) {
     last = a->y3; Dl = D2;
   }
   if (a->normalize) {
-    l2norm_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(last, a->out, a->norm, B, Dl, 1e-12f);
+    tt::note_launch(); l2norm_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(last, a->out, a->norm, B, Dl, 1e-12f);
     TT_LAUNCH_CHECK();
   }
   return TT_OK;
@@ -188,7 +188,7 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
 
   const float* dlast = a->d_out;
   if (f->normalize) {
-    l2norm_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(f->out, f->norm, a->d_out, d_y, B, Dl, 1e-12f);
+    tt::note_launch(); l2norm_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(f->out, f->norm, a->d_out, d_y, B, Dl, 1e-12f);
     TT_LAUNCH_CHECK();
     dlast = d_y;
   }
@@ -199,7 +199,7 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
     TT_TRY(gemm_f32(nn_gemm(dlast, D2, f->w2, P, d_y2, P, B, P, D2, 0.f), s));
     dy2 = d_y2;
   }
-  ln_relu_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(f->y1, f->y2, f->stats, f->ln_w, dy2, d_y1, gm, gx, B, P,
+  tt::note_launch(); ln_relu_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(f->y1, f->y2, f->stats, f->ln_w, dy2, d_y1, gm, gx, B, P,
                                                               f->dropout_p > 0.f ? 1.f / (1.f - f->dropout_p) : 1.f);
   TT_LAUNCH_CHECK();
   TT_TRY(colsum_f32(gm, P, B, P, a->d_ln_b, s));

@@ -156,9 +156,9 @@ int tt_score_ce_fwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
     g.a_rs = D; g.a_cs = 1; g.b_rs = D; g.b_cs = 1; g.ldc = NC;
     g.M = Bl; g.N = nc; g.K = D; g.nbatch = 1; g.splitk = 1; g.alpha = inv_temp; g.beta = 0.f;
     TT_TRY(gemm_f32(g, s));
-    ce_rowstats_kernel<<<(unsigned)ceil_div(Bl, 8), 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, rmax, rsum, plog, c0 == 0);
+    tt::note_launch(); ce_rowstats_kernel<<<(unsigned)ceil_div(Bl, 8), 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, rmax, rsum, plog, c0 == 0);
   }
-  ce_finish_kernel<<<(unsigned)ceil_div(Bl, 256), 256, 0, s>>>(rmax, rsum, plog, row_loss, row_lse, Bl);
+  tt::note_launch(); ce_finish_kernel<<<(unsigned)ceil_div(Bl, 256), 256, 0, s>>>(rmax, rsum, plog, row_loss, row_lse, Bl);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -181,7 +181,7 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
     TT_TRY(gemm_f32(g, s));
     int64_t tot = (int64_t)Bl * nc, nb = ceil_div(tot, 256);
     if (nb > 148 * 16) nb = 148 * 16;
-    ce_grad_kernel<<<(unsigned)nb, 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, row_lse, gscale * inv_temp);
+    tt::note_launch(); ce_grad_kernel<<<(unsigned)nb, 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, row_lse, gscale * inv_temp);
     // dx[Bl,D] (+)= G[Bl,nc] Y[c0:c0+nc, D]
     GemmArgs gx{};
     gx.A[0] = S; gx.B[0] = y + (int64_t)c0 * D; gx.C[0] = dx;
@@ -202,7 +202,7 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
 int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D, float margin,
                  float* row_loss, void* stream) {
   TT_CHECK_ARG(q && pos && neg && row_loss && B > 0 && k > 0 && D > 0, "hinge_fwd: bad args");
-  hinge_kernel<false><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, 0.f,
+  tt::note_launch(); hinge_kernel<false><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, 0.f,
                                                                                 row_loss, nullptr, nullptr, nullptr);
   TT_LAUNCH_CHECK();
   return TT_OK;
@@ -210,7 +210,7 @@ int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, 
 int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D, float margin,
                  float gscale, float* dq, float* dpos, float* dneg, void* stream) {
   TT_CHECK_ARG(q && pos && neg && dq && dpos && dneg && B > 0 && k > 0 && D > 0, "hinge_bwd: bad args");
-  hinge_kernel<true><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, gscale,
+  tt::note_launch(); hinge_kernel<true><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, gscale,
                                                                                nullptr, dq, dpos, dneg);
   TT_LAUNCH_CHECK();
   return TT_OK;

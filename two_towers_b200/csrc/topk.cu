@@ -232,15 +232,15 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
   if (S > 1) { pv = w.take<float>((int64_t)S * Q * 32); pi = w.take<int64_t>((int64_t)S * Q * 32); }
   if (!w.ok()) { set_error("rows_topk: workspace too small"); return TT_ERR_WORKSPACE; }
   if (mode == 1) {
-    inv_norm_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, D, 1e-8f, invx);
-    if (N > 0) inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy);
+    tt::note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, D, 1e-8f, invx);
+    if (N > 0) { note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy); }
   }
   int64_t cps = ceil_div(N > 0 ? N : 1, S);
   cps = ceil_div(cps, BN) * BN;
   dim3 grid((unsigned)ceil_div(Q, BM), (unsigned)S);
-  rows_topk_kernel<<<grid, NT, 0, s>>>(x, Q, y, N, D, k, invx, invy, mask_pos_offset, index_base, cps,
+  tt::note_launch(); rows_topk_kernel<<<grid, NT, 0, s>>>(x, Q, y, N, D, k, invx, invy, mask_pos_offset, index_base, cps,
                                       S > 1 ? pv : out_val, S > 1 ? pi : out_idx);
-  if (S > 1) topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx);
+  if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx); }
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -248,7 +248,7 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
 int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k, float* out_val,
                   int64_t* out_idx, void* stream) {
   TT_CHECK_ARG(vals && idx && out_val && out_idx && S > 0 && Q > 0 && k >= 1 && k <= 32, "topk_merge: bad args");
-  topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx);
+  tt::note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -256,7 +256,7 @@ int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, i
 int tt_mrr_ranks(const int64_t* topk_idx, const int64_t* relevant, int32_t Q, int32_t k, int32_t* first_rank, float* rr,
                  void* stream) {
   TT_CHECK_ARG(topk_idx && relevant && first_rank && rr && Q > 0 && k > 0, "mrr_ranks: bad args");
-  mrr_ranks_kernel<<<(unsigned)ceil_div(Q, 256), 256, 0, (cudaStream_t)stream>>>(topk_idx, relevant, Q, k, first_rank, rr);
+  tt::note_launch(); mrr_ranks_kernel<<<(unsigned)ceil_div(Q, 256), 256, 0, (cudaStream_t)stream>>>(topk_idx, relevant, Q, k, first_rank, rr);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
