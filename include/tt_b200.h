@@ -188,6 +188,14 @@ int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, 
 int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                const float* bias, int32_t M, int32_t N, int32_t K, float alpha, float beta, void* stream);
 
+/* same product through the tcgen05 bf16x3 engine (operands split to bf16 hi/lo planes on the fly); exported for
+ * kernel-level tests and roofline measurement.  trans != 0: A is given as [K,M], B as [K,N] (MN-major operands,
+ * the wgrad form).  splitk 0 = automatic. */
+uint64_t tt_gemm_x3_workspace(int32_t M, int32_t N, int32_t K);
+int tt_gemm_x3(const float* A, const float* B, float* C, const float* bias, int32_t M, int32_t N, int32_t K,
+               float alpha, float beta, int32_t trans, int32_t splitk, void* workspace, uint64_t workspace_bytes,
+               void* stream);
+
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);
 

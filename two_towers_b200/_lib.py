@@ -84,6 +84,8 @@ SIGNATURES = {
     "tt_hinge_bwd": (C.c_int, [P, P, P, i32, i32, i32, F, F, P, P, P, P]),
     "tt_gemm_nt": (C.c_int, [P, i64, P, i64, P, i64, P, i32, i32, i32, F, F, P]),
     "tt_dropout": (C.c_int, [P, P, i64, F, u64, u64, P]),
+    "tt_gemm_x3_workspace": (u64, [i32, i32, i32]),
+    "tt_gemm_x3": (C.c_int, [P, P, P, P, i32, i32, i32, F, F, i32, i32, P, u64, P]),
 }
 
 _lib = None

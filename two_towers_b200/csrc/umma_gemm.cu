@@ -1,0 +1,419 @@
+// tcgen05 / TMA / TMEM GEMM engine with bf16x3 operands (see umma_gemm.cuh).
+//
+// Persistent, warp-specialised: warp 0 = TMA producer (one elected lane), warp 1 = tcgen05.mma issuer (one lane) and
+// TMEM owner, warps 2-5 = epilogue (TMEM -> registers -> global).  Tile 128 x BN x 64, operands staged in 128-byte
+// swizzled shared memory by TMA (hi and lo planes of A and B per stage), fp32 accumulators double-buffered in TMEM
+// so the epilogue of tile i overlaps the main loop of tile i+1.  Per k-block the issuer runs
+// 3 (hi*hi, lo*hi, hi*lo) x 4 (UMMA_K = 16) tcgen05.mma into the same accumulator.
+#include "umma.cuh"
+#include "umma_gemm.cuh"
+
+namespace tt {
+using namespace umma;
+
+constexpr int UBM = 128, UBK = 64;
+constexpr int kThreads = 192;
+
+struct alignas(64) UmmaParams {
+  CUtensorMap a_hi[2], a_lo[2], b_hi[2], b_lo[2];
+  float* C[2];
+  const float* bias[2];
+  int64_t ldc;
+  int32_t M, N, K, nbatch, splitk;
+  float alpha, beta;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int A_BYTES = UBM * UBK * 2;              // one plane of the A tile
+  static constexpr int B_BYTES = BN * UBK * 2;
+  static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
+  static constexpr int STAGES = (BN <= 128) ? 3 : 2;
+  static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
+  using C_ = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C_::STAGES * C_::STAGE_BYTES);
+  uint64_t* full = bars;                       // [STAGES]
+  uint64_t* empty = bars + C_::STAGES;         // [STAGES]
+  uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]
+  uint64_t* tempty = tfull + 2;                // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int MT = (p.M + UBM - 1) / UBM, NT = (p.N + BN - 1) / BN, KB = (p.K + UBK - 1) / UBK;
+  const int kb_per = (KB + p.splitk - 1) / p.splitk;
+  const int items = p.nbatch * p.splitk * MT * NT;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================================= TMA producer
+    if (lane == 0) {
+      for (int b = 0; b < p.nbatch; ++b) {
+        tma_prefetch_desc(&p.a_hi[b]); tma_prefetch_desc(&p.a_lo[b]);
+        tma_prefetch_desc(&p.b_hi[b]); tma_prefetch_desc(&p.b_lo[b]);
+      }
+      int stage = 0, phase = 0;
+      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+        const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
+        const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* st = smem + stage * C_::STAGE_BYTES;
+          uint8_t* sa_hi = st, *sa_lo = st + C_::A_BYTES, *sb_hi = st + 2 * C_::A_BYTES, *sb_lo = sb_hi + C_::B_BYTES;
+          mbar_arrive_expect_tx(&full[stage], C_::STAGE_BYTES);
+          if (!A_MN) {
+            tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi, kb * UBK, m_blk * UBM);
+            tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo, kb * UBK, m_blk * UBM);
+          } else {
+#pragma unroll
+            for (int h = 0; h < UBM / 64; ++h) {
+              tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi + h * 8192, m_blk * UBM + h * 64, kb * UBK);
+              tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo + h * 8192, m_blk * UBM + h * 64, kb * UBK);
+            }
+          }
+          if (!B_MN) {
+            tma_load_2d(&p.b_hi[bz], &full[stage], sb_hi, kb * UBK, n_blk * BN);
+            tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo, kb * UBK, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h) {
+              tma_load_2d(&p.b_hi[bz], &full[stage], sb_hi + h * 8192, n_blk * BN + h * 64, kb * UBK);
+              tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo + h * 8192, n_blk * BN + h * 64, kb * UBK);
+            }
+          }
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(UBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      // K-major: rows of 128 B, 8-row groups 1024 B apart.  MN-major: 64-element groups 8192 B apart (LBO),
+      // 8-k groups 1024 B apart (SBO).  One UMMA_K=16 step advances 32 B (K-major) or 2048 B (MN-major).
+      constexpr uint32_t a_lbo = A_MN ? 8192 : 16, a_step = A_MN ? 2048 : 32;
+      constexpr uint32_t b_lbo = B_MN ? 8192 : 16, b_step = B_MN ? 2048 : 32;
+      int stage = 0, phase = 0, tile = 0;
+      for (int it = blockIdx.x; it < items; it += gridDim.x, ++tile) {
+        const int sp = (it / (NT * MT)) % p.splitk;
+        const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
+        const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + stage * C_::STAGE_BYTES);
+          const uint32_t sa_hi = st, sa_lo = st + C_::A_BYTES, sb_hi = st + 2 * C_::A_BYTES, sb_lo = sb_hi + C_::B_BYTES;
+#pragma unroll
+          for (int term = 0; term < 3; ++term) {
+            const uint32_t sa = term == 1 ? sa_lo : sa_hi;
+            const uint32_t sb = term == 2 ? sb_lo : sb_hi;
+#pragma unroll
+            for (int k = 0; k < UBK / 16; ++k) {
+              const uint64_t ad = make_smem_desc(sa + k * a_step, a_lbo, 1024);
+              const uint64_t bd = make_smem_desc(sb + k * b_step, b_lbo, 1024);
+              mma_bf16_ss(d_tmem, ad, bd, idesc, (kb > kb0 || term > 0 || k > 0) ? 1u : 0u);
+            }
+          }
+          mma_commit(&empty[stage]);          // smem slot reusable once these MMAs have read it
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tfull[acc]);              // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ================================================================= epilogue (warps 2..5)
+    const int quarter = warp & 3;             // TMEM lanes this warp may touch: [32*quarter, 32*quarter+32)
+    const int row = quarter * 32 + lane;
+    int tile = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x, ++tile) {
+      const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
+      const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
+      const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const int gm = m_blk * UBM + row;
+      float* crow = p.C[bz] + (int64_t)gm * p.ldc;
+      const float* bias = p.bias[bz];
+      const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C[bz]) & 15) == 0);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
+        const int gn0 = n_blk * BN + c0;
+        if (gm < p.M && gn0 < p.N && kb0 < kb1) {
+          if (p.splitk > 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (gn0 + j < p.N) {
+                float x = p.alpha * v[j];
+                if (sp == 0 && bias) x += bias[gn0 + j];
+                atomicAdd(crow + gn0 + j, x);
+              }
+          } else if (vec_ok && gn0 + 32 <= p.N) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 o = make_float4(p.alpha * v[j], p.alpha * v[j + 1], p.alpha * v[j + 2], p.alpha * v[j + 3]);
+              if (p.beta != 0.f) {
+                const float4 c = *reinterpret_cast<const float4*>(crow + gn0 + j);
+                o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
+              }
+              if (bias) { o.x += bias[gn0 + j]; o.y += bias[gn0 + j + 1]; o.z += bias[gn0 + j + 2]; o.w += bias[gn0 + j + 3]; }
+              *reinterpret_cast<float4*>(crow + gn0 + j) = o;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (gn0 + j < p.N) {
+                float x = p.alpha * v[j];
+                if (p.beta != 0.f) x += p.beta * crow[gn0 + j];
+                if (bias) x += bias[gn0 + j];
+                crow[gn0 + j] = x;
+              }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, C_::TMEM_COLS);
+}
+
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+bool umma_available() { return encode_fn() != nullptr; }
+
+// 2-D bf16 map over a row-major [rows][pitch] plane exposing `cols` logical columns; box = {64 cols, box_rows};
+// 128-byte swizzle; out-of-bounds elements read as zero (this is what makes ragged M/N/K tiles correct).
+static int make_map(CUtensorMap* m, const bf16* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled not available"); return TT_ERR_CUDA; }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(bf16)};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (strides[0] & 15)) {
+    set_error("umma: plane base/pitch not 16-byte aligned");
+    return TT_ERR_INVALID;
+  }
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld pitch=%lld", (int)r, (long long)rows, (long long)cols, (long long)pitch); return TT_ERR_CUDA; }
+  return TT_OK;
+}
+
+__global__ void prescale_kernel(float* C, int64_t ldc, int M, int N, float beta) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)M * N) return;
+  float* q = C + (i / N) * ldc + (i % N);
+  *q = beta == 0.f ? 0.f : beta * *q;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
+  auto kern = umma_gemm_kernel<BN, A_MN, B_MN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    TT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    attr_done = true;
+  }
+  static int num_sms = 0;
+  if (!num_sms) {
+    int dev = 0;
+    TT_CUDA(cudaGetDevice(&dev));
+    TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int grid = items < num_sms ? items : num_sms;
+  note_launch();
+  kern<<<grid, kThreads, Cfg<BN>::SMEM_BYTES, s>>>(p);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+int umma_gemm(const UmmaGemm& g, cudaStream_t s) {
+  if (g.M <= 0 || g.N <= 0) return TT_OK;
+  TT_CHECK_ARG(g.nbatch >= 1 && g.nbatch <= 2 && g.K > 0, "umma_gemm: bad nbatch/K");
+  const int BN = g.N <= 128 ? 128 : 256;
+  UmmaParams p;
+  memset(&p, 0, sizeof(p));
+  for (int b = 0; b < g.nbatch; ++b) {
+    // K-major: plane [MN rows][K cols], box rows = tile MN extent.  MN-major: plane [K rows][MN cols], box 64x64.
+    if (!g.a_mn) {
+      TT_TRY(make_map(&p.a_hi[b], g.A[b].hi, g.M, g.K, g.A[b].pitch, UBM));
+      TT_TRY(make_map(&p.a_lo[b], g.A[b].lo, g.M, g.K, g.A[b].pitch, UBM));
+    } else {
+      TT_TRY(make_map(&p.a_hi[b], g.A[b].hi, g.K, g.M, g.A[b].pitch, 64));
+      TT_TRY(make_map(&p.a_lo[b], g.A[b].lo, g.K, g.M, g.A[b].pitch, 64));
+    }
+    if (!g.b_mn) {
+      TT_TRY(make_map(&p.b_hi[b], g.B[b].hi, g.N, g.K, g.B[b].pitch, BN));
+      TT_TRY(make_map(&p.b_lo[b], g.B[b].lo, g.N, g.K, g.B[b].pitch, BN));
+    } else {
+      TT_TRY(make_map(&p.b_hi[b], g.B[b].hi, g.K, g.N, g.B[b].pitch, 64));
+      TT_TRY(make_map(&p.b_lo[b], g.B[b].lo, g.K, g.N, g.B[b].pitch, 64));
+    }
+    p.C[b] = g.C[b]; p.bias[b] = g.bias[b];
+  }
+  p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K; p.nbatch = g.nbatch; p.alpha = g.alpha; p.beta = g.beta;
+  const int MT = (int)ceil_div(g.M, UBM), NT = (int)ceil_div(g.N, BN), KB = (int)ceil_div(g.K, UBK);
+  int splitk = g.splitk;
+  if (splitk <= 0) {
+    splitk = 1;
+    const int tiles = MT * NT * g.nbatch;
+    if (tiles < 74 && KB >= 32) {
+      splitk = (int)ceil_div(148, tiles);
+      if (splitk > KB / 8) splitk = KB / 8;
+      if (splitk < 1) splitk = 1;
+    }
+  }
+  if (splitk > KB) splitk = KB;
+  // no empty splits: shrink until ceil(KB/kb_per) == splitk
+  while (splitk > 1 && (int)ceil_div(KB, ceil_div(KB, splitk)) < splitk) --splitk;
+  p.splitk = splitk;
+  if (splitk > 1 && g.beta != 1.f) {
+    for (int b = 0; b < g.nbatch; ++b) {
+      const int64_t n = (int64_t)g.M * g.N;
+      note_launch();
+      prescale_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
+    }
+    TT_LAUNCH_CHECK();
+  }
+  const int items = MT * NT * g.nbatch * splitk;
+#define TT_UMMA_DISPATCH(BNV)                                                         \
+  do {                                                                                \
+    if (!g.a_mn && !g.b_mn) return launch_cfg<BNV, false, false>(p, items, s);        \
+    if (g.a_mn && g.b_mn) return launch_cfg<BNV, true, true>(p, items, s);            \
+    set_error("umma_gemm: mixed operand majors are not instantiated");                \
+    return TT_ERR_INVALID;                                                            \
+  } while (0)
+  if (BN == 128) TT_UMMA_DISPATCH(128);
+  TT_UMMA_DISPATCH(256);
+#undef TT_UMMA_DISPATCH
+}
+
+// ------------------------------------------------------------------------------------------ plane producers
+__global__ void split_planes_kernel(const float* __restrict__ x, int64_t ld, int64_t rows, int cols, bf16* __restrict__ hi,
+                                    bf16* __restrict__ lo, int64_t pitch, float p, float inv_keep, uint64_t seed,
+                                    uint64_t offset) {
+  const int64_t pairs_per_row = pitch >> 1;
+  const int64_t total = rows * pairs_per_row;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / pairs_per_row;
+    const int c = (int)(i % pairs_per_row) * 2;
+    float v0 = c < cols ? x[r * ld + c] : 0.f;
+    float v1 = c + 1 < cols ? x[r * ld + c + 1] : 0.f;
+    if (p > 0.f) {
+      if (c < cols) v0 *= dropout_scale(seed, offset, (uint64_t)(r * cols + c), p, inv_keep);
+      if (c + 1 < cols) v1 *= dropout_scale(seed, offset, (uint64_t)(r * cols + c + 1), p, inv_keep);
+    }
+    bf16 h0, l0, h1, l1;
+    split_bf16(v0, h0, l0);
+    split_bf16(v1, h1, l1);
+    *reinterpret_cast<__nv_bfloat162*>(hi + r * pitch + c) = __halves2bfloat162(h0, h1);
+    *reinterpret_cast<__nv_bfloat162*>(lo + r * pitch + c) = __halves2bfloat162(l0, l1);
+  }
+}
+int split_planes(const float* x, int64_t ld, int64_t rows, int32_t cols, bf16* hi, bf16* lo, int64_t pitch, float p,
+                 uint64_t seed, uint64_t offset, cudaStream_t s) {
+  if (rows <= 0) return TT_OK;
+  int64_t n = rows * (pitch >> 1), nb = ceil_div(n, 256);
+  if (nb > 148 * 32) nb = 148 * 32;
+  note_launch();
+  split_planes_kernel<<<(unsigned)nb, 256, 0, s>>>(x, ld, rows, cols, hi, lo, pitch, p, p > 0.f ? 1.f / (1.f - p) : 1.f,
+                                                 seed, offset);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+// out planes [cols][pitch >= rows] = x^T ; 32x32 smem transpose
+__global__ void split_planes_t_kernel(const float* __restrict__ x, int64_t ld, int rows, int cols, bf16* __restrict__ hi,
+                                      bf16* __restrict__ lo, int64_t pitch) {
+  __shared__ float t[32][33];
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    t[i][threadIdx.x] = (r < rows && c < cols) ? x[(int64_t)r * ld + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + threadIdx.x;      // output row = c, output col = r
+    if (c < cols && r < pitch) {
+      bf16 h, l;
+      split_bf16(t[threadIdx.x][i], h, l);
+      hi[(int64_t)c * pitch + r] = h;
+      lo[(int64_t)c * pitch + r] = l;
+    }
+  }
+}
+int split_planes_transposed(const float* x, int64_t ld, int64_t rows, int32_t cols, bf16* hi, bf16* lo, int64_t pitch,
+                            cudaStream_t s) {
+  if (rows <= 0 || cols <= 0) return TT_OK;
+  note_launch();
+  split_planes_t_kernel<<<dim3((unsigned)ceil_div(cols, 32), (unsigned)ceil_div(pitch, 32)), dim3(32, 8), 0, s>>>(
+      x, ld, (int)rows, cols, hi, lo, pitch);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+}  // namespace tt
+
+// test hook: C = alpha * A B^T + bias through the tcgen05 engine (A [M,K], B [N,K] fp32, split on the fly);
+// trans != 0 evaluates the same product with both operands given transposed ([K,M], [K,N]) -> MN-major path.
+extern "C" int tt_gemm_x3(const float* A, const float* B, float* C, const float* bias, int32_t M, int32_t N, int32_t K,
+                          float alpha, float beta, int32_t trans, int32_t splitk, void* workspace,
+                          uint64_t workspace_bytes, void* stream) {
+  using namespace tt;
+  TT_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0, "gemm_x3: bad args");
+  cudaStream_t s = (cudaStream_t)stream;
+  Workspace w(workspace, workspace_bytes);
+  const int64_t ar = trans ? K : M, ac = trans ? M : K, br = trans ? K : N, bc = trans ? N : K;
+  const int64_t pa = plane_pitch(ac), pb = plane_pitch(bc);
+  bf16* ahi = w.take<bf16>(ar * pa); bf16* alo = w.take<bf16>(ar * pa);
+  bf16* bhi = w.take<bf16>(br * pb); bf16* blo = w.take<bf16>(br * pb);
+  if (!w.ok()) { set_error("gemm_x3: workspace too small (%llu needed)", (unsigned long long)w.used); return TT_ERR_WORKSPACE; }
+  TT_TRY(split_planes(A, ac, ar, (int)ac, ahi, alo, pa, 0.f, 0, 0, s));
+  TT_TRY(split_planes(B, bc, br, (int)bc, bhi, blo, pb, 0.f, 0, 0, s));
+  UmmaGemm g{};
+  g.A[0] = {ahi, alo, pa}; g.B[0] = {bhi, blo, pb}; g.C[0] = C; g.bias[0] = bias; g.ldc = N;
+  g.M = M; g.N = N; g.K = K; g.nbatch = 1; g.a_mn = g.b_mn = trans != 0; g.alpha = alpha; g.beta = beta; g.splitk = splitk;
+  return umma_gemm(g, s);
+}
+extern "C" uint64_t tt_gemm_x3_workspace(int32_t M, int32_t N, int32_t K) {
+  return 4ull * ((uint64_t)(M + 8) * (K + 8) + (uint64_t)(N + 8) * (K + 8)) + 4096;
+}
