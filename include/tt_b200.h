@@ -30,6 +30,9 @@ int tt_abi_version(void);
 const char* tt_last_error(void);
 /* which engine the GEMM-shaped ops run on: "simt-fp32" or "tcgen05-bf16x3" */
 const char* tt_engine(void);
+/* select the engine for the GEMM-shaped GRU work: 1 = tcgen05-bf16x3 (default), 0 = simt-fp32 (exact fp32; also
+ * used automatically when the hidden size is not a multiple of 8).  Test / cross-check aid. */
+int tt_set_engine(int32_t mode);
 /* number of CUDA kernels this library has launched in this process (monotonic) */
 uint64_t tt_kernel_launches(void);
 

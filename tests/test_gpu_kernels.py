@@ -19,6 +19,15 @@ def _t(a):
     return torch.as_tensor(np.asarray(a), dtype=torch.float32, device=DEV)
 
 
+@pytest.fixture(params=["simt-fp32", "tcgen05-bf16x3"])
+def engine(request):
+    """Run GRU tests on both engines; the tcgen05 bf16x3 engine is held to 1e-4 (bound: 1e-3), exact fp32 to 2e-5."""
+    from two_towers_b200 import _lib as L
+    L.check(L.lib().tt_set_engine(1 if request.param.startswith("tcgen05") else 0), "set_engine")
+    yield 2e-5 if request.param == "simt-fp32" else 1e-4
+    L.check(L.lib().tt_set_engine(1), "set_engine")
+
+
 @pytest.mark.parametrize("M,N,K", [(1, 1, 1), (5, 7, 3), (128, 128, 16), (130, 257, 300), (513, 96, 77)])
 def test_gemm_nt(M, N, K):
     rng = np.random.default_rng(M * 1000 + N)
@@ -69,8 +78,9 @@ def _flat(p, L, nd):
 
 @pytest.mark.parametrize("B,T,In,H,L,nd,use_len", [
     (3, 5, 7, 4, 1, 1, False), (3, 5, 7, 4, 2, 2, False), (5, 9, 20, 10, 2, 2, True),
-    (130, 6, 300, 33, 2, 2, False), (2, 1, 5, 3, 2, 2, False), (4, 7, 12, 128, 1, 2, True)])
-def test_gru_stack_forward(B, T, In, H, L, nd, use_len):
+    (130, 6, 300, 33, 2, 2, False), (2, 1, 5, 3, 2, 2, False), (4, 7, 12, 128, 1, 2, True),
+    (300, 9, 300, 256, 2, 2, False), (70, 5, 44, 72, 2, 2, True), (9, 3, 16, 8, 2, 2, False), (129, 4, 300, 64, 1, 1, False)])
+def test_gru_stack_forward(engine, B, T, In, H, L, nd, use_len):
     rng = np.random.default_rng(B * 100 + T)
     p = _gru_params(rng, In, H, L, nd)
     x = rng.standard_normal((B, T, In)).astype(np.float32)
@@ -78,11 +88,12 @@ def test_gru_stack_forward(B, T, In, H, L, nd, use_len):
     out_ref, hn_ref = rn.gru_stack(x, p, "g", L, nd == 2, lengths=lens)
     out, hn = Fn.gru_stack(_t(x), _flat(p, L, nd), In, H, L, nd == 2,
                            lengths=None if lens is None else torch.as_tensor(lens))
-    assert rel_err(out, out_ref) < TOL and rel_err(hn, hn_ref) < TOL
+    assert rel_err(out, out_ref) < engine and rel_err(hn, hn_ref) < engine
 
 
-@pytest.mark.parametrize("B,T,In,H,use_len", [(3, 4, 6, 5, False), (6, 7, 20, 9, True), (131, 5, 40, 16, False)])
-def test_gru_stack_backward_vs_torch_autograd(B, T, In, H, use_len):
+@pytest.mark.parametrize("B,T,In,H,use_len", [(3, 4, 6, 5, False), (6, 7, 20, 9, True), (131, 5, 40, 16, False),
+                                               (140, 6, 300, 72, True), (260, 3, 52, 256, False), (5, 9, 12, 8, False)])
+def test_gru_stack_backward_vs_torch_autograd(engine, B, T, In, H, use_len):
     """Oracle: stock nn.GRU on CPU in float64 (same arithmetic the reference dispatches), incl. d/dx."""
     torch.manual_seed(B)
     ref = torch.nn.GRU(In, H, num_layers=2, batch_first=True, bidirectional=True).double()
@@ -99,14 +110,14 @@ def test_gru_stack_backward_vs_torch_autograd(B, T, In, H, use_len):
     ws = [p.detach().float().to(DEV).requires_grad_(True) for p in ref.parameters()]
     xg = x.detach().float().to(DEV).requires_grad_(True)
     o2, hn2 = Fn.gru_stack(xg, ws, In, H, 2, True, lengths=lens)
-    assert rel_err(o2, o.detach()) < TOL and rel_err(hn2, hn.detach()) < TOL
+    assert rel_err(o2, o.detach()) < engine and rel_err(hn2, hn.detach()) < engine
     ((o2 * go.float().to(DEV)).sum() + (hn2 * gh.float().to(DEV)).sum()).backward()
-    assert rel_err(xg.grad, x.grad) < 1e-4
+    assert rel_err(xg.grad, x.grad) < 2e-4
     for (n, p), w in zip(ref.named_parameters(), ws):
-        assert rel_err(w.grad, p.grad) < 1e-4, n
+        assert rel_err(w.grad, p.grad) < 2e-4, (n, rel_err(w.grad, p.grad))
 
 
-def test_gru_token_ids_equal_pregathered_floats():
+def test_gru_token_ids_equal_pregathered_floats(engine):
     torch.manual_seed(1)
     table = torch.randn(40, 12)
     table[0] = 0
@@ -122,7 +133,7 @@ def test_gru_token_ids_equal_pregathered_floats():
     ws2 = [w.detach().clone().requires_grad_(True) for w in ws]
     Fn.gru_stack(table[ids].to(DEV), ws2, 12, 8, 2, True)[1].sum().backward()
     for g1, g2 in zip(ws, ws2):
-        assert rel_err(g1.grad, g2.grad) < 1e-6
+        assert rel_err(g1.grad, g2.grad) < 1e-5
 
 
 def test_gru_interlayer_dropout_statistics_and_determinism():
@@ -346,3 +357,21 @@ def test_mrr_ranks_and_recall():
     out = retrieval.mrr_recall(top, rel, ks=(1, 3))
     ref = rp.mrr_recall(top.cpu(), rel.cpu(), ks=(1, 3))
     assert all(abs(out[k] - ref[k]) < 1e-12 for k in ref)
+
+
+# ------------------------------------------------------------------------------------------- tcgen05 engine alone
+@pytest.mark.parametrize("M,N,K,trans,splitk", [(128, 128, 64, 0, 1), (300, 200, 100, 0, 1), (5, 7, 3, 0, 1), (1000, 768, 300, 0, 1),
+                                                 (300, 200, 100, 1, 1), (768, 304, 5000, 1, 0), (256, 256, 4096, 0, 4), (64, 1536, 520, 0, 1)])
+def test_gemm_x3_engine(M, N, K, trans, splitk):
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    g = torch.Generator().manual_seed(M + N + K)
+    A, B, bias = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g), torch.randn(N, generator=g)
+    ref = 0.5 * A.double() @ B.double().t() + bias.double()
+    Ad = (A.t().contiguous() if trans else A).to(DEV)
+    Bd = (B.t().contiguous() if trans else B).to(DEV)
+    C = torch.empty(M, N, device=DEV)
+    ws = L.workspace(lib.tt_gemm_x3_workspace(M, N, K), DEV)
+    L.check(lib.tt_gemm_x3(L.ptr(Ad), L.ptr(Bd), L.ptr(C), L.ptr(bias.to(DEV)), M, N, K, 0.5, 0.0, trans, splitk,
+                           ws.data_ptr(), ws.numel(), L.stream()), "gemm_x3")
+    assert rel_err(C, ref) < 3e-5

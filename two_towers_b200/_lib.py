@@ -63,6 +63,7 @@ SIGNATURES = {
     "tt_last_error": (C.c_char_p, []),
     "tt_engine": (C.c_char_p, []),
     "tt_kernel_launches": (u64, []),
+    "tt_set_engine": (C.c_int, [i32]),
     "tt_embed_gather": (C.c_int, [P, C.c_int, i64, P, i64, i32, i64, P, P]),
     "tt_gru_layer_fwd_workspace": (u64, [C.POINTER(GruLayer)]),
     "tt_gru_layer_fwd": (C.c_int, [C.POINTER(GruLayer), P]),

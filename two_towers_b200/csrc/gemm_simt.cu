@@ -6,6 +6,7 @@
 #include <stdarg.h>
 #include "common.cuh"
 #include "simt_tile.cuh"
+#include "gru_umma.cuh"
 
 namespace tt {
 
@@ -18,6 +19,8 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 static unsigned long long g_launches = 0;
+int g_engine = 1;
+int engine_mode() { return g_engine; }
 void note_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
 unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
@@ -156,6 +159,12 @@ int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cud
 extern "C" {
 int tt_abi_version(void) { return 1; }
 uint64_t tt_kernel_launches(void) { return tt::launches(); }
+const char* tt_engine(void) { return tt::engine_mode() == 1 ? "tcgen05-bf16x3" : "simt-fp32"; }
+int tt_set_engine(int32_t mode) {
+  if (mode != 0 && mode != 1) { tt::set_error("tt_set_engine: mode must be 0 (simt-fp32) or 1 (tcgen05-bf16x3)"); return TT_ERR_INVALID; }
+  tt::g_engine = mode;
+  return TT_OK;
+}
 const char* tt_last_error(void) { return tt::last_error(); }
 
 int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,

@@ -1,6 +1,7 @@
 // GRU layer forward / BPTT (K-A gather, K-B input projection, K-C recurrence, K-C' backward).
 // Engine: exact fp32 (SIMT GEMM + fused cell kernels).  See DESIGN.md for the data layout.
 #include "common.cuh"
+#include "gru_umma.cuh"
 
 namespace tt {
 
@@ -155,6 +156,7 @@ static int check_layer(const tt_gru_layer* a) {
   return TT_OK;
 }
 
+static bool use_umma(const tt_gru_layer* a) { return engine_mode() == 1 && (a->H % 8) == 0; }
 static bool needs_xeff(const tt_gru_layer* a) { return a->ids != nullptr || a->dropout_p > 0.f; }
 
 // materialise the effective layer input (gathered and/or dropped-out) when it is not `x` itself
@@ -185,6 +187,7 @@ int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint
 
 uint64_t tt_gru_layer_fwd_workspace(const tt_gru_layer* a) {
   if (!a) return 0;
+  if (use_umma(a)) return gru_fwd_workspace_umma(a);
   Workspace w(nullptr, 0);
   const int64_t ntok = (int64_t)a->B * a->T;
   if (needs_xeff(a)) w.take<float>(ntok * a->In);
@@ -197,6 +200,7 @@ int tt_gru_layer_fwd(const tt_gru_layer* a, void* stream) {
   TT_TRY(check_layer(a));
   cudaStream_t s = (cudaStream_t)stream;
   TT_CHECK_ARG(!a->save_for_backward || a->gates, "gru fwd: save_for_backward without gates buffer");
+  if (use_umma(a)) return gru_layer_fwd_umma(a, s);
   const int B = a->B, T = a->T, In = a->In, H = a->H, nd = a->ndir;
   const int64_t ntok = (int64_t)B * T;
   Workspace w(a->workspace, a->workspace_bytes);
@@ -233,6 +237,7 @@ int tt_gru_layer_fwd(const tt_gru_layer* a, void* stream) {
 uint64_t tt_gru_layer_bwd_workspace(const tt_gru_layer_grad* a) {
   if (!a) return 0;
   const tt_gru_layer* f = &a->fwd;
+  if (use_umma(f)) return gru_bwd_workspace_umma(a);
   Workspace w(nullptr, 0);
   const int64_t ntok = (int64_t)f->B * f->T;
   if (needs_xeff(f)) w.take<float>(ntok * f->In);
@@ -252,6 +257,12 @@ int tt_gru_layer_bwd(const tt_gru_layer_grad* a, void* stream) {
   const int64_t ntok = (int64_t)B * T;
   for (int d = 0; d < nd; ++d)
     TT_CHECK_ARG(a->d_w_ih[d] && a->d_w_hh[d] && a->d_b_ih[d] && a->d_b_hh[d], "gru bwd: null grad buffer");
+  if (use_umma(f)) {
+    TT_TRY(gru_layer_bwd_umma(a, s));
+    if (a->d_x && f->dropout_p > 0.f && !f->ids)
+      TT_TRY(launch_dropout(a->d_x, a->d_x, ntok * In, f->dropout_p, f->seed, f->offset, s));
+    return TT_OK;
+  }
   Workspace w(a->workspace, a->workspace_bytes);
   float* xeff = needs_xeff(f) ? w.take<float>(ntok * In) : nullptr;
   float* dG = w.take<float>((int64_t)nd * ntok * 4 * H);

@@ -261,6 +261,6 @@ int tt_mrr_ranks(const int64_t* topk_idx, const int64_t* relevant, int32_t Q, in
   return TT_OK;
 }
 
-const char* tt_engine(void) { return "simt-fp32"; }
+
 
 }  // extern "C"
