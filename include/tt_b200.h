@@ -28,10 +28,13 @@ extern "C" {
 
 int tt_abi_version(void);
 const char* tt_last_error(void);
-/* which engine the GEMM-shaped ops run on: "simt-fp32" or "tcgen05-bf16x3" */
+/* which engine the GEMM-shaped ops run on: "simt-fp32", "tcgen05-bf16x3" or "tcgen05-f16x3-fwd/f16-bwd" */
 const char* tt_engine(void);
-/* select the engine for the GEMM-shaped GRU work: 1 = tcgen05-bf16x3 (default), 0 = simt-fp32 (exact fp32; also
- * used automatically when the hidden size is not a multiple of 8).  Test / cross-check aid. */
+/* select the engine for the GEMM-shaped GRU work:
+ *   2 (default) = tcgen05 "v2" stack pipeline: time-major fp16 hi/lo planes, 3-pass forward, 1-pass loss-scaled
+ *                 backward (hidden size multiple of 64, through tt_gru_stack_*; other shapes use engine 1)
+ *   1           = tcgen05 bf16x3, layer by layer (hidden size multiple of 8; other shapes use engine 0)
+ *   0           = simt-fp32 (exact fp32).  Test / cross-check aid. */
 int tt_set_engine(int32_t mode);
 /* number of CUDA kernels this library has launched in this process (monotonic) */
 uint64_t tt_kernel_launches(void);
@@ -98,6 +101,44 @@ typedef struct tt_gru_layer_grad {
 
 uint64_t tt_gru_layer_bwd_workspace(const tt_gru_layer_grad* a);
 int tt_gru_layer_bwd(const tt_gru_layer_grad* a, void* stream);
+
+/* The whole multi-layer (bi)directional GRU in one call == nn.GRU(batch_first=True, num_layers=L) with zero initial
+ * state (same reference lines as tt_gru_layer).  This is the entry point the Python host uses: between layers the
+ * activations stay in library-private layouts (time-major 16-bit operand planes), the state backward needs lives in
+ * the caller-owned opaque buffer `saved`.  weights / d_weights are HOST arrays of L*ndir*4 device pointers in nn.GRU's
+ * _flat_weights order (w_ih, w_hh, b_ih, b_hh per layer, per direction).  Inter-layer dropout (p, seed) as above.
+ * out may be NULL (the models only use h_n).  Shapes the fast pipeline does not cover run layer by layer. */
+typedef struct tt_gru_stack {
+  int32_t B, T, In, H, L, ndir;
+  int32_t save_for_backward, ids_are_i64;
+  const float* x;                  /* [B,T,In] or NULL when ids given */
+  const void* ids;                 /* [B,T] or NULL */
+  const float* table;              /* [vocab,In] */
+  int64_t vocab, pad_id;
+  float dropout_p;
+  int32_t _pad0;
+  uint64_t seed;
+  const float* const* weights;     /* host array [L*ndir*4] of device pointers */
+  const int32_t* lengths;          /* [B] or NULL */
+  float* out;                      /* [B,T,ndir*H] of the last layer, or NULL */
+  float* h_n;                      /* [L*ndir,B,H] */
+  void* saved; uint64_t saved_bytes;             /* tt_gru_stack_saved_bytes(); needed when save_for_backward */
+  void* workspace; uint64_t workspace_bytes;     /* tt_gru_stack_fwd_workspace() */
+} tt_gru_stack;
+uint64_t tt_gru_stack_saved_bytes(const tt_gru_stack* a);
+uint64_t tt_gru_stack_fwd_workspace(const tt_gru_stack* a);
+int tt_gru_stack_fwd(const tt_gru_stack* a, void* stream);
+
+typedef struct tt_gru_stack_grad {
+  tt_gru_stack fwd;                /* same arguments as the forward call (saved = the buffer it filled) */
+  const float* d_out;              /* [B,T,ndir*H] or NULL */
+  const float* d_h_n;              /* [L*ndir,B,H] or NULL */
+  float* d_x;                      /* [B,T,In] or NULL */
+  float* const* d_weights;         /* host array [L*ndir*4] of device pointers, WRITTEN */
+  void* workspace; uint64_t workspace_bytes;     /* tt_gru_stack_bwd_workspace() */
+} tt_gru_stack_grad;
+uint64_t tt_gru_stack_bwd_workspace(const tt_gru_stack_grad* a);
+int tt_gru_stack_bwd(const tt_gru_stack_grad* a, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K-D  projection head on the pooled state cat(h_n[-2], h_n[-1]):
@@ -195,6 +236,10 @@ int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* 
  * kernel-level tests and roofline measurement.  trans != 0: A is given as [K,M], B as [K,N] (MN-major operands,
  * the wgrad form).  splitk 0 = automatic. */
 uint64_t tt_gemm_x3_workspace(int32_t M, int32_t N, int32_t K);
+/* operand formats of the v2 pipeline: flags bit0 = fp16 planes (else bf16), bit1 = single pass (else 3), bit2 = A given
+ * as [K,M], bit3 = B given as [K,N].  Workspace as tt_gemm_x3_workspace. */
+int tt_gemm_test(const float* A, const float* B, float* C, int32_t M, int32_t N, int32_t K, float alpha, float beta,
+                 int32_t flags, void* workspace, uint64_t workspace_bytes, void* stream);
 int tt_gemm_x3(const float* A, const float* B, float* C, const float* bias, int32_t M, int32_t N, int32_t K,
                float alpha, float beta, int32_t trans, int32_t splitk, void* workspace, uint64_t workspace_bytes,
                void* stream);

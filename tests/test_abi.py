@@ -38,7 +38,7 @@ def test_binding_covers_every_declared_symbol():
 def test_library_reports_version_and_engine_without_gpu():
     lib = _lib.lib()
     assert lib.tt_abi_version() == 1
-    assert lib.tt_engine().decode() in ("simt-fp32", "tcgen05-bf16x3")
+    assert lib.tt_engine().decode() in ("simt-fp32", "tcgen05-bf16x3", "tcgen05-f16x3-fwd/f16-bwd")
 
 
 def test_struct_layouts_match_c_compiler():
@@ -52,6 +52,8 @@ int main(void){
          offsetof(tt_gru_layer,lengths), offsetof(tt_gru_layer,workspace_bytes));
   printf("%zu %zu %zu\n", offsetof(tt_head,seed), offsetof(tt_head,v_lo), offsetof(tt_head,norm));
   printf("%zu %zu\n", offsetof(tt_gru_layer_grad,d_out), offsetof(tt_head_grad,d_out));
+  printf("%zu %zu %zu %zu %zu %zu\n", sizeof(tt_gru_stack), sizeof(tt_gru_stack_grad), offsetof(tt_gru_stack,x),
+         offsetof(tt_gru_stack,seed), offsetof(tt_gru_stack,saved_bytes), offsetof(tt_gru_stack_grad,d_weights));
   return 0; }
 '''
     with tempfile.TemporaryDirectory() as d:
@@ -65,6 +67,8 @@ int main(void){
     exp = [ctypes.sizeof(G), ctypes.sizeof(GG), ctypes.sizeof(H), ctypes.sizeof(HG),
            G.x.offset, G.seed.offset, G.w_ih.offset, G.lengths.offset, G.workspace_bytes.offset,
            H.seed.offset, H.v_lo.offset, H.norm.offset, GG.d_out.offset, HG.d_out.offset]
+    S, SG = _lib.GruStack, _lib.GruStackGrad
+    exp += [ctypes.sizeof(S), ctypes.sizeof(SG), S.x.offset, S.seed.offset, S.saved_bytes.offset, SG.d_weights.offset]
     assert out == exp
 
 

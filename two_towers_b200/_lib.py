@@ -35,6 +35,24 @@ class GruLayerGrad(C.Structure):
     ]
 
 
+class GruStack(C.Structure):
+    _fields_ = [
+        ("B", i32), ("T", i32), ("In", i32), ("H", i32), ("L", i32), ("ndir", i32),
+        ("save_for_backward", i32), ("ids_are_i64", i32),
+        ("x", C.c_void_p), ("ids", C.c_void_p), ("table", C.c_void_p), ("vocab", i64), ("pad_id", i64),
+        ("dropout_p", C.c_float), ("_pad0", i32), ("seed", u64),
+        ("weights", C.POINTER(C.c_void_p)), ("lengths", C.c_void_p), ("out", C.c_void_p), ("h_n", C.c_void_p),
+        ("saved", C.c_void_p), ("saved_bytes", u64), ("workspace", C.c_void_p), ("workspace_bytes", u64),
+    ]
+
+
+class GruStackGrad(C.Structure):
+    _fields_ = [
+        ("fwd", GruStack), ("d_out", C.c_void_p), ("d_h_n", C.c_void_p), ("d_x", C.c_void_p),
+        ("d_weights", C.POINTER(C.c_void_p)), ("workspace", C.c_void_p), ("workspace_bytes", u64),
+    ]
+
+
 class Head(C.Structure):
     _fields_ = [
         ("B", i32), ("In", i32), ("P1", i32), ("D2", i32), ("normalize", i32), ("dropout_p", C.c_float),
@@ -69,6 +87,11 @@ SIGNATURES = {
     "tt_gru_layer_fwd": (C.c_int, [C.POINTER(GruLayer), P]),
     "tt_gru_layer_bwd_workspace": (u64, [C.POINTER(GruLayerGrad)]),
     "tt_gru_layer_bwd": (C.c_int, [C.POINTER(GruLayerGrad), P]),
+    "tt_gru_stack_saved_bytes": (u64, [C.POINTER(GruStack)]),
+    "tt_gru_stack_fwd_workspace": (u64, [C.POINTER(GruStack)]),
+    "tt_gru_stack_fwd": (C.c_int, [C.POINTER(GruStack), P]),
+    "tt_gru_stack_bwd_workspace": (u64, [C.POINTER(GruStackGrad)]),
+    "tt_gru_stack_bwd": (C.c_int, [C.POINTER(GruStackGrad), P]),
     "tt_head_fwd": (C.c_int, [C.POINTER(Head), P]),
     "tt_head_bwd_workspace": (u64, [C.POINTER(HeadGrad)]),
     "tt_head_bwd": (C.c_int, [C.POINTER(HeadGrad), P]),
@@ -87,6 +110,7 @@ SIGNATURES = {
     "tt_dropout": (C.c_int, [P, P, i64, F, u64, u64, P]),
     "tt_gemm_x3_workspace": (u64, [i32, i32, i32]),
     "tt_gemm_x3": (C.c_int, [P, P, P, P, i32, i32, i32, F, F, i32, i32, P, u64, P]),
+    "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
 }
 
 _lib = None

@@ -19,7 +19,7 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 static unsigned long long g_launches = 0;
-int g_engine = 1;
+int g_engine = 2;
 int engine_mode() { return g_engine; }
 void note_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
 unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
@@ -159,9 +159,11 @@ int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cud
 extern "C" {
 int tt_abi_version(void) { return 1; }
 uint64_t tt_kernel_launches(void) { return tt::launches(); }
-const char* tt_engine(void) { return tt::engine_mode() == 1 ? "tcgen05-bf16x3" : "simt-fp32"; }
+const char* tt_engine(void) {
+  return tt::engine_mode() == 2 ? "tcgen05-f16x3-fwd/f16-bwd" : tt::engine_mode() == 1 ? "tcgen05-bf16x3" : "simt-fp32";
+}
 int tt_set_engine(int32_t mode) {
-  if (mode != 0 && mode != 1) { tt::set_error("tt_set_engine: mode must be 0 (simt-fp32) or 1 (tcgen05-bf16x3)"); return TT_ERR_INVALID; }
+  if (mode < 0 || mode > 2) { tt::set_error("tt_set_engine: mode must be 0 (simt-fp32), 1 (tcgen05-bf16x3) or 2 (tcgen05 v2 stack)"); return TT_ERR_INVALID; }
   tt::g_engine = mode;
   return TT_OK;
 }

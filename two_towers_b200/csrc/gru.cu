@@ -156,7 +156,7 @@ static int check_layer(const tt_gru_layer* a) {
   return TT_OK;
 }
 
-static bool use_umma(const tt_gru_layer* a) { return engine_mode() == 1 && (a->H % 8) == 0; }
+static bool use_umma(const tt_gru_layer* a) { return engine_mode() >= 1 && (a->H % 8) == 0; }
 static bool needs_xeff(const tt_gru_layer* a) { return a->ids != nullptr || a->dropout_p > 0.f; }
 
 // materialise the effective layer input (gathered and/or dropped-out) when it is not `x` itself

@@ -18,24 +18,29 @@ struct alignas(64) UmmaParams {
   CUtensorMap a_hi[2], a_lo[2], b_hi[2], b_lo[2];
   float* C[2];
   const float* bias[2];
+  const float* alpha_ptr;
   int64_t ldc;
   int32_t M, N, K, nbatch, splitk;
   float alpha, beta;
+  uint32_t idesc;
+  int32_t a_row0[2], b_row0, a_seg, a_skip;
+  int32_t epi, rm_Bp, rm_B, rm_T, tl_Bp, tl_G, tl_Hc;
 };
 
-template <int BN>
+template <int BN, int NPASS>
 struct Cfg {
   static constexpr int A_BYTES = UBM * UBK * 2;              // one plane of the A tile
   static constexpr int B_BYTES = BN * UBK * 2;
-  static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;
-  static constexpr int STAGES = (BN <= 128) ? 3 : 2;
+  static constexpr int NPLANES = NPASS == 3 ? 2 : 1;
+  static constexpr int STAGE_BYTES = NPLANES * (A_BYTES + B_BYTES);
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 6 ? 6 : (200 * 1024) / STAGE_BYTES;
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int NPASS>
 __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
-  using C_ = Cfg<BN>;
+  using C_ = Cfg<BN, NPASS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C_::STAGES * C_::STAGE_BYTES);
@@ -65,8 +70,8 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     // ================================================================= TMA producer
     if (lane == 0) {
       for (int b = 0; b < p.nbatch; ++b) {
-        tma_prefetch_desc(&p.a_hi[b]); tma_prefetch_desc(&p.a_lo[b]);
-        tma_prefetch_desc(&p.b_hi[b]); tma_prefetch_desc(&p.b_lo[b]);
+        tma_prefetch_desc(&p.a_hi[b]); tma_prefetch_desc(&p.b_hi[b]);
+        if (NPASS == 3) { tma_prefetch_desc(&p.a_lo[b]); tma_prefetch_desc(&p.b_lo[b]); }
       }
       int stage = 0, phase = 0;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
@@ -75,26 +80,31 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + stage * C_::STAGE_BYTES;
-          uint8_t* sa_hi = st, *sa_lo = st + C_::A_BYTES, *sb_hi = st + 2 * C_::A_BYTES, *sb_lo = sb_hi + C_::B_BYTES;
+          uint8_t* sa_hi = st, *sb_hi = st + C_::A_BYTES;
+          uint8_t* sa_lo = st + C_::A_BYTES + C_::B_BYTES, *sb_lo = sa_lo + C_::A_BYTES;
           mbar_arrive_expect_tx(&full[stage], C_::STAGE_BYTES);
           if (!A_MN) {
-            tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi, kb * UBK, m_blk * UBM);
-            tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo, kb * UBK, m_blk * UBM);
+            int ka = kb * UBK;
+            if (p.a_seg > 0 && ka >= p.a_seg) ka += p.a_skip;
+            tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi, ka, m_blk * UBM + p.a_row0[bz]);
+            if (NPASS == 3) tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo, ka, m_blk * UBM + p.a_row0[bz]);
           } else {
+            int ma = m_blk * UBM;
+            if (p.a_seg > 0 && ma >= p.a_seg) ma += p.a_skip;
 #pragma unroll
             for (int h = 0; h < UBM / 64; ++h) {
-              tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi + h * 8192, m_blk * UBM + h * 64, kb * UBK);
-              tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo + h * 8192, m_blk * UBM + h * 64, kb * UBK);
+              tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi + h * 8192, ma + h * 64, kb * UBK);
+              if (NPASS == 3) tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo + h * 8192, ma + h * 64, kb * UBK);
             }
           }
           if (!B_MN) {
-            tma_load_2d(&p.b_hi[bz], &full[stage], sb_hi, kb * UBK, n_blk * BN);
-            tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo, kb * UBK, n_blk * BN);
+            tma_load_2d(&p.b_hi[bz], &full[stage], sb_hi, kb * UBK, n_blk * BN + p.b_row0);
+            if (NPASS == 3) tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo, kb * UBK, n_blk * BN + p.b_row0);
           } else {
 #pragma unroll
             for (int h = 0; h < BN / 64; ++h) {
               tma_load_2d(&p.b_hi[bz], &full[stage], sb_hi + h * 8192, n_blk * BN + h * 64, kb * UBK);
-              tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo + h * 8192, n_blk * BN + h * 64, kb * UBK);
+              if (NPASS == 3) tma_load_2d(&p.b_lo[bz], &full[stage], sb_lo + h * 8192, n_blk * BN + h * 64, kb * UBK);
             }
           }
           if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
@@ -104,7 +114,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   } else if (warp == 1) {
     // ================================================================= MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(UBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      const uint32_t idesc = p.idesc;
       // K-major: rows of 128 B, 8-row groups 1024 B apart.  MN-major: 64-element groups 8192 B apart (LBO),
       // 8-k groups 1024 B apart (SBO).  One UMMA_K=16 step advances 32 B (K-major) or 2048 B (MN-major).
       constexpr uint32_t a_lbo = A_MN ? 8192 : 16, a_step = A_MN ? 2048 : 32;
@@ -121,9 +131,10 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t st = smem_u32(smem + stage * C_::STAGE_BYTES);
-          const uint32_t sa_hi = st, sa_lo = st + C_::A_BYTES, sb_hi = st + 2 * C_::A_BYTES, sb_lo = sb_hi + C_::B_BYTES;
+          const uint32_t sa_hi = st, sb_hi = st + C_::A_BYTES;
+          const uint32_t sa_lo = st + C_::A_BYTES + C_::B_BYTES, sb_lo = sa_lo + C_::A_BYTES;
 #pragma unroll
-          for (int term = 0; term < 3; ++term) {
+          for (int term = 0; term < NPASS; ++term) {
             const uint32_t sa = term == 1 ? sa_lo : sa_hi;
             const uint32_t sb = term == 2 ? sb_lo : sb_hi;
 #pragma unroll
@@ -143,6 +154,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     // ================================================================= epilogue (warps 2..5)
     const int quarter = warp & 3;             // TMEM lanes this warp may touch: [32*quarter, 32*quarter+32)
     const int row = quarter * 32 + lane;
+    const float alpha = p.alpha * (p.alpha_ptr ? __ldg(p.alpha_ptr) : 1.f);
     int tile = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x, ++tile) {
       const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
@@ -151,27 +163,57 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const int gm = m_blk * UBM + row;
-      float* crow = p.C[bz] + (int64_t)gm * p.ldc;
       const float* bias = p.bias[bz];
+      bool row_ok = gm < p.M;
+      float* crow;
+      int64_t tl_base = 0;
+      if (p.epi == 1) {                        // tiled: 128-row tile == one batch tile of one timestep
+        const int t = gm / p.tl_Bp, mt = (gm % p.tl_Bp) >> 7;
+        tl_base = ((int64_t)t * (p.tl_Bp >> 7) + mt) * p.tl_G;
+        crow = p.C[bz] + (gm & 127) * 4;
+      } else if (p.rm_Bp > 0) {                // time-major rows -> batch-first C rows
+        const int t = gm / p.rm_Bp, b = gm % p.rm_Bp;
+        row_ok = row_ok && b < p.rm_B;
+        crow = p.C[bz] + ((int64_t)b * p.rm_T + t) * p.ldc;
+      } else {
+        crow = p.C[bz] + (int64_t)gm * p.ldc;
+      }
       const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C[bz]) & 15) == 0);
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
         const int gn0 = n_blk * BN + c0;
-        if (gm < p.M && gn0 < p.N && kb0 < kb1) {
-          if (p.splitk > 1) {
+        if (row_ok && gn0 < p.N && kb0 < kb1) {
+          if (p.epi == 1) {
+            const int hc4 = p.tl_Hc >> 2;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const int n = gn0 + j;
+              if (n < p.N) {
+                const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
+                float4* dst = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
+                float4 o = make_float4(alpha * v[j], alpha * v[j + 1], alpha * v[j + 2], alpha * v[j + 3]);
+                if (p.beta != 0.f) {
+                  const float4 c = *dst;
+                  o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
+                }
+                if (bias) { o.x += bias[n]; o.y += bias[n + 1]; o.z += bias[n + 2]; o.w += bias[n + 3]; }
+                *dst = o;
+              }
+            }
+          } else if (p.splitk > 1) {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (gn0 + j < p.N) {
-                float x = p.alpha * v[j];
+                float x = alpha * v[j];
                 if (sp == 0 && bias) x += bias[gn0 + j];
                 atomicAdd(crow + gn0 + j, x);
               }
           } else if (vec_ok && gn0 + 32 <= p.N) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
-              float4 o = make_float4(p.alpha * v[j], p.alpha * v[j + 1], p.alpha * v[j + 2], p.alpha * v[j + 3]);
+              float4 o = make_float4(alpha * v[j], alpha * v[j + 1], alpha * v[j + 2], alpha * v[j + 3]);
               if (p.beta != 0.f) {
                 const float4 c = *reinterpret_cast<const float4*>(crow + gn0 + j);
                 o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
@@ -183,7 +225,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (gn0 + j < p.N) {
-                float x = p.alpha * v[j];
+                float x = alpha * v[j];
                 if (p.beta != 0.f) x += p.beta * crow[gn0 + j];
                 if (bias) x += bias[gn0 + j];
                 crow[gn0 + j] = x;
@@ -218,22 +260,22 @@ static EncodeTiledFn encode_fn() {
 }
 bool umma_available() { return encode_fn() != nullptr; }
 
-// 2-D bf16 map over a row-major [rows][pitch] plane exposing `cols` logical columns; box = {64 cols, box_rows};
+// 2-D 16-bit map over a row-major [rows][pitch] plane exposing `cols` logical columns; box = {64 cols, box_rows};
 // 128-byte swizzle; out-of-bounds elements read as zero (this is what makes ragged M/N/K tiles correct).
-static int make_map(CUtensorMap* m, const bf16* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows) {
+int make_plane_map(CUtensorMap* m, const void* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows, int f16) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) { set_error("cuTensorMapEncodeTiled not available"); return TT_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(bf16)};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
   cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1u, 1u};
   if ((reinterpret_cast<uintptr_t>(base) & 15) || (strides[0] & 15)) {
     set_error("umma: plane base/pitch not 16-byte aligned");
     return TT_ERR_INVALID;
   }
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base),
+                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld pitch=%lld", (int)r, (long long)rows, (long long)cols, (long long)pitch); return TT_ERR_CUDA; }
   return TT_OK;
 }
@@ -245,12 +287,12 @@ __global__ void prescale_kernel(float* C, int64_t ldc, int M, int N, float beta)
   *q = beta == 0.f ? 0.f : beta * *q;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int NPASS>
 static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
-  auto kern = umma_gemm_kernel<BN, A_MN, B_MN>;
+  auto kern = umma_gemm_kernel<BN, A_MN, B_MN, NPASS>;
   static bool attr_done = false;
   if (!attr_done) {
-    TT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    TT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, NPASS>::SMEM_BYTES));
     attr_done = true;
   }
   static int num_sms = 0;
@@ -261,37 +303,55 @@ static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
   }
   const int grid = items < num_sms ? items : num_sms;
   note_launch();
-  kern<<<grid, kThreads, Cfg<BN>::SMEM_BYTES, s>>>(p);
+  kern<<<grid, kThreads, Cfg<BN, NPASS>::SMEM_BYTES, s>>>(p);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
 
-int umma_gemm(const UmmaGemm& g, cudaStream_t s) {
-  if (g.M <= 0 || g.N <= 0) return TT_OK;
+static_assert(sizeof(UmmaParams) <= sizeof(((UmmaPrepared*)0)->blob), "UmmaPrepared blob too small");
+
+int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
+  memset(out, 0, sizeof(*out));
+  if (g.M <= 0 || g.N <= 0) { out->kind = -1; return TT_OK; }
   TT_CHECK_ARG(g.nbatch >= 1 && g.nbatch <= 2 && g.K > 0, "umma_gemm: bad nbatch/K");
-  const int BN = g.N <= 128 ? 128 : 256;
-  UmmaParams p;
-  memset(&p, 0, sizeof(p));
+  const int npass = g.npass == 1 ? 1 : 3;
+  const int MT = (int)ceil_div(g.M, UBM), KB = (int)ceil_div(g.K, UBK);
+  // BN = 128 when N is small, or when 256-wide tiles would leave most SMs idle
+  int BN = g.N <= 128 ? 128 : 256;
+  if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0) BN = 128;
+  UmmaParams& p = *reinterpret_cast<UmmaParams*>(out->blob);
+  const int f16 = g.f16;
+  const int64_t skipA = g.a_seg > 0 ? g.a_skip : 0;
   for (int b = 0; b < g.nbatch; ++b) {
     // K-major: plane [MN rows][K cols], box rows = tile MN extent.  MN-major: plane [K rows][MN cols], box 64x64.
     if (!g.a_mn) {
-      TT_TRY(make_map(&p.a_hi[b], g.A[b].hi, g.M, g.K, g.A[b].pitch, UBM));
-      TT_TRY(make_map(&p.a_lo[b], g.A[b].lo, g.M, g.K, g.A[b].pitch, UBM));
+      const int64_t rows = g.a_rows > 0 ? g.a_rows : g.M;
+      TT_TRY(make_plane_map(&p.a_hi[b], g.A[b].hi, rows, g.K + skipA, g.A[b].pitch, UBM, f16));
+      if (npass == 3) TT_TRY(make_plane_map(&p.a_lo[b], g.A[b].lo, rows, g.K + skipA, g.A[b].pitch, UBM, f16));
     } else {
-      TT_TRY(make_map(&p.a_hi[b], g.A[b].hi, g.K, g.M, g.A[b].pitch, 64));
-      TT_TRY(make_map(&p.a_lo[b], g.A[b].lo, g.K, g.M, g.A[b].pitch, 64));
+      const int64_t rows = g.a_rows > 0 ? g.a_rows : g.K;
+      TT_TRY(make_plane_map(&p.a_hi[b], g.A[b].hi, rows, g.M + skipA, g.A[b].pitch, 64, f16));
+      if (npass == 3) TT_TRY(make_plane_map(&p.a_lo[b], g.A[b].lo, rows, g.M + skipA, g.A[b].pitch, 64, f16));
     }
     if (!g.b_mn) {
-      TT_TRY(make_map(&p.b_hi[b], g.B[b].hi, g.N, g.K, g.B[b].pitch, BN));
-      TT_TRY(make_map(&p.b_lo[b], g.B[b].lo, g.N, g.K, g.B[b].pitch, BN));
+      const int64_t rows = g.b_rows > 0 ? g.b_rows : g.N;
+      TT_TRY(make_plane_map(&p.b_hi[b], g.B[b].hi, rows, g.K, g.B[b].pitch, BN, f16));
+      if (npass == 3) TT_TRY(make_plane_map(&p.b_lo[b], g.B[b].lo, rows, g.K, g.B[b].pitch, BN, f16));
     } else {
-      TT_TRY(make_map(&p.b_hi[b], g.B[b].hi, g.K, g.N, g.B[b].pitch, 64));
-      TT_TRY(make_map(&p.b_lo[b], g.B[b].lo, g.K, g.N, g.B[b].pitch, 64));
+      const int64_t rows = g.b_rows > 0 ? g.b_rows : g.K;
+      TT_TRY(make_plane_map(&p.b_hi[b], g.B[b].hi, rows, g.N, g.B[b].pitch, 64, f16));
+      if (npass == 3) TT_TRY(make_plane_map(&p.b_lo[b], g.B[b].lo, rows, g.N, g.B[b].pitch, 64, f16));
     }
-    p.C[b] = g.C[b]; p.bias[b] = g.bias[b];
+    p.C[b] = g.C[b]; p.bias[b] = g.bias[b]; p.a_row0[b] = g.a_row0;
   }
   p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K; p.nbatch = g.nbatch; p.alpha = g.alpha; p.beta = g.beta;
-  const int MT = (int)ceil_div(g.M, UBM), NT = (int)ceil_div(g.N, BN), KB = (int)ceil_div(g.K, UBK);
+  p.alpha_ptr = g.alpha_ptr; p.b_row0 = g.b_row0; p.a_seg = g.a_seg; p.a_skip = g.a_skip;
+  p.epi = g.epi; p.rm_Bp = g.rm_Bp; p.rm_B = g.rm_B; p.rm_T = g.rm_T; p.tl_Bp = g.tl_Bp; p.tl_G = g.tl_G; p.tl_Hc = g.tl_Hc;
+  p.idesc = f16 ? make_idesc_f16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0) : make_idesc_bf16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0);
+  if (g.epi == 1)
+    TT_CHECK_ARG(g.splitk == 1 && (g.tl_Bp % 128) == 0 && (g.tl_Hc % 4) == 0 && (g.N % 4) == 0 && (g.M % 128) == 0,
+                 "umma_gemm: tiled epilogue needs splitk 1, Bp %% 128 == 0, Hc %% 4 == 0");
+  const int NT = (int)ceil_div(g.N, BN);
   int splitk = g.splitk;
   if (splitk <= 0) {
     splitk = 1;
@@ -306,25 +366,50 @@ int umma_gemm(const UmmaGemm& g, cudaStream_t s) {
   // no empty splits: shrink until ceil(KB/kb_per) == splitk
   while (splitk > 1 && (int)ceil_div(KB, ceil_div(KB, splitk)) < splitk) --splitk;
   p.splitk = splitk;
-  if (splitk > 1 && g.beta != 1.f) {
-    for (int b = 0; b < g.nbatch; ++b) {
-      const int64_t n = (int64_t)g.M * g.N;
+  out->items = MT * NT * g.nbatch * splitk;
+  const int major = (!g.a_mn && !g.b_mn) ? 0 : (g.a_mn && g.b_mn) ? 1 : (!g.a_mn && g.b_mn) ? 2 : 3;
+  if (major == 3 || (major == 2 && npass == 3)) {
+    set_error("umma_gemm: operand major / pass combination not instantiated");
+    return TT_ERR_INVALID;
+  }
+  out->kind = (BN == 128 ? 0 : 8) + (npass == 1 ? 4 : 0) + major;
+  return TT_OK;
+}
+
+int umma_gemm_launch(const UmmaPrepared& prep, const int* a_row0, cudaStream_t s) {
+  if (prep.kind < 0) return TT_OK;
+  UmmaParams p = *reinterpret_cast<const UmmaParams*>(prep.blob);
+  if (a_row0)
+    for (int b = 0; b < p.nbatch; ++b) p.a_row0[b] = a_row0[b];
+  if (p.splitk > 1 && p.beta != 1.f) {
+    for (int b = 0; b < p.nbatch; ++b) {
+      const int64_t n = (int64_t)p.M * p.N;
       note_launch();
-      prescale_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
+      prescale_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(p.C[b], p.ldc, p.M, p.N, p.beta);
     }
     TT_LAUNCH_CHECK();
   }
-  const int items = MT * NT * g.nbatch * splitk;
-#define TT_UMMA_DISPATCH(BNV)                                                         \
-  do {                                                                                \
-    if (!g.a_mn && !g.b_mn) return launch_cfg<BNV, false, false>(p, items, s);        \
-    if (g.a_mn && g.b_mn) return launch_cfg<BNV, true, true>(p, items, s);            \
-    set_error("umma_gemm: mixed operand majors are not instantiated");                \
-    return TT_ERR_INVALID;                                                            \
-  } while (0)
-  if (BN == 128) TT_UMMA_DISPATCH(128);
-  TT_UMMA_DISPATCH(256);
-#undef TT_UMMA_DISPATCH
+  const int items = prep.items;
+  switch (prep.kind) {
+    case 0: return launch_cfg<128, false, false, 3>(p, items, s);
+    case 1: return launch_cfg<128, true, true, 3>(p, items, s);
+    case 4: return launch_cfg<128, false, false, 1>(p, items, s);
+    case 5: return launch_cfg<128, true, true, 1>(p, items, s);
+    case 6: return launch_cfg<128, false, true, 1>(p, items, s);
+    case 8: return launch_cfg<256, false, false, 3>(p, items, s);
+    case 9: return launch_cfg<256, true, true, 3>(p, items, s);
+    case 12: return launch_cfg<256, false, false, 1>(p, items, s);
+    case 13: return launch_cfg<256, true, true, 1>(p, items, s);
+    case 14: return launch_cfg<256, false, true, 1>(p, items, s);
+  }
+  set_error("umma_gemm: bad prepared kind %d", prep.kind);
+  return TT_ERR_INVALID;
+}
+
+int umma_gemm(const UmmaGemm& g, cudaStream_t s) {
+  UmmaPrepared prep;
+  TT_TRY(umma_gemm_prepare(g, &prep));
+  return umma_gemm_launch(prep, nullptr, s);
 }
 
 // ------------------------------------------------------------------------------------------ plane producers
@@ -414,6 +499,46 @@ extern "C" int tt_gemm_x3(const float* A, const float* B, float* C, const float*
   g.M = M; g.N = N; g.K = K; g.nbatch = 1; g.a_mn = g.b_mn = trans != 0; g.alpha = alpha; g.beta = beta; g.splitk = splitk;
   return umma_gemm(g, s);
 }
+// test hook for the v2 operand formats: flags bit0 = fp16 planes, bit1 = single pass, bit2 = A given as [K,M]
+// (MN-major), bit3 = B given as [K,N] (MN-major).  C = alpha * A B^T (+ beta C).
+__global__ void split_f16_kernel(const float* __restrict__ x, int64_t rows, int cols, __half* __restrict__ hi,
+                                 __half* __restrict__ lo, int64_t pitch) {
+  const int64_t total = rows * pitch;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % pitch);
+    const float v = c < cols ? x[(i / pitch) * cols + c] : 0.f;
+    __half a, b;
+    tt::umma::split_f16(v, a, b);
+    hi[i] = a; lo[i] = b;
+  }
+}
+extern "C" int tt_gemm_test(const float* A, const float* B, float* C, int32_t M, int32_t N, int32_t K, float alpha,
+                            float beta, int32_t flags, void* workspace, uint64_t workspace_bytes, void* stream) {
+  using namespace tt;
+  TT_CHECK_ARG(A && B && C && M > 0 && N > 0 && K > 0, "gemm_test: bad args");
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool f16 = flags & 1, one = flags & 2, amn = flags & 4, bmn = flags & 8;
+  Workspace w(workspace, workspace_bytes);
+  const int64_t ar = amn ? K : M, ac = amn ? M : K, br = bmn ? K : N, bc = bmn ? N : K;
+  const int64_t pa = plane_pitch(ac), pb = plane_pitch(bc);
+  bf16* ahi = w.take<bf16>(ar * pa); bf16* alo = w.take<bf16>(ar * pa);
+  bf16* bhi = w.take<bf16>(br * pb); bf16* blo = w.take<bf16>(br * pb);
+  if (!w.ok()) { set_error("gemm_test: workspace too small"); return TT_ERR_WORKSPACE; }
+  if (f16) {
+    note_launch(); split_f16_kernel<<<592, 256, 0, s>>>(A, ar, (int)ac, (__half*)ahi, (__half*)alo, pa);
+    note_launch(); split_f16_kernel<<<592, 256, 0, s>>>(B, br, (int)bc, (__half*)bhi, (__half*)blo, pb);
+    TT_LAUNCH_CHECK();
+  } else {
+    TT_TRY(split_planes(A, ac, ar, (int)ac, ahi, alo, pa, 0.f, 0, 0, s));
+    TT_TRY(split_planes(B, bc, br, (int)bc, bhi, blo, pb, 0.f, 0, 0, s));
+  }
+  UmmaGemm g{};
+  g.A[0] = {ahi, alo, pa}; g.B[0] = {bhi, blo, pb}; g.C[0] = C; g.ldc = N;
+  g.M = M; g.N = N; g.K = K; g.nbatch = 1; g.a_mn = amn; g.b_mn = bmn; g.alpha = alpha; g.beta = beta; g.splitk = 1;
+  g.f16 = f16; g.npass = one ? 1 : 3;
+  return umma_gemm(g, s);
+}
+
 extern "C" uint64_t tt_gemm_x3_workspace(int32_t M, int32_t N, int32_t K) {
   return 4ull * ((uint64_t)(M + 8) * (K + 8) + (uint64_t)(N + 8) * (K + 8)) + 4096;
 }

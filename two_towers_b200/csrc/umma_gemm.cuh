@@ -5,7 +5,9 @@
 // error vs fp32 ~1e-5) at 3 tensor-core passes.  Single-pass bf16 (3.5e-3) and TF32 (5e-4 fwd, 3e-2
 // on gradients through the margin loss) both miss the 1e-3 parity bound.
 #pragma once
+#include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace tt {
@@ -34,8 +36,25 @@ struct UmmaGemm {
   bool a_mn, b_mn;
   float alpha, beta;
   int32_t splitk;      // 0 = choose; >1 accumulates with atomics (C is pre-scaled by beta)
+  // ---- extensions (all default 0 = the plain bf16 x3 row-major GEMM)
+  int32_t f16;         // planes hold IEEE fp16 instead of bf16
+  int32_t npass;       // 0/3: hi*hi + lo*hi + hi*lo ; 1: hi*hi only (lo planes unused)
+  int64_t a_rows, b_rows;   // rows of the plane arrays the tensor maps cover (0: derived from M/N/K)
+  int32_t a_row0, b_row0;   // K-major operands: first plane row of the problem (e.g. t*Bp for one timestep)
+  int32_t a_seg, a_skip;    // A column remap: logical index i >= a_seg reads plane column i + a_skip
+                            //   (K-major A: i = k ; MN-major A: i = m).  Both multiples of 64 (128 for MN-major).
+  const float* alpha_ptr;   // optional device scalar multiplied into alpha (loss-scale undo)
+  int32_t epi;              // 0 row-major C ; 1 tiled C (see TiledOut)
+  int32_t rm_Bp, rm_B, rm_T;  // row-major epilogue: rows are time-major m = t*Bp + b -> C row b*T + t; b >= rm_B skipped
+  int32_t tl_Bp, tl_G, tl_Hc; // tiled epilogue: C[(((t*MT + mt)*G + g)*(Hc/4) + u/4)*512 + row*4 + u%4],
+                              //   t = m / Bp, mt = (m % Bp) / 128, row = m % 128, g = n / Hc, u = n % Hc, MT = Bp / 128
 };
 int umma_gemm(const UmmaGemm& g, cudaStream_t s);
+// encode the tensor maps / pick the configuration once, launch many times (per-timestep GEMMs only change the first
+// plane row of A, given per batched problem)
+struct UmmaPrepared { alignas(64) unsigned char blob[1408]; int kind, items; };
+int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out);
+int umma_gemm_launch(const UmmaPrepared& p, const int* a_row0, cudaStream_t s);
 
 // fp32 [rows, cols] (row stride ld) -> hi/lo planes [rows, pitch]; optional inverted dropout (p, seed, offset over
 // the logical index row*cols+col) fused in; columns [cols, pitch) are written as zeros.
@@ -44,6 +63,9 @@ int split_planes(const float* x, int64_t ld, int64_t rows, int32_t cols, bf16* h
 // transpose + split: x [rows, cols] -> planes [cols, pitch(rows)]   (weights for dgrad: W^T)
 int split_planes_transposed(const float* x, int64_t ld, int64_t rows, int32_t cols, bf16* hi, bf16* lo, int64_t pitch,
                             cudaStream_t s);
+
+// 2-D tensor map over a 16-bit plane [rows][pitch] exposing `cols` columns, box {64, box_rows}, 128-byte swizzle
+int make_plane_map(CUtensorMap* m, const void* base, int64_t rows, int64_t cols, int64_t pitch, int box_rows, int f16);
 
 bool umma_available();   // false if the driver entry point for tensor maps is missing
 

@@ -52,10 +52,35 @@ def _fill_layer(cfg, l, x, ids, weights, out, h_n, gates, seed, ws, B, T):
     return a
 
 
+def _ptr_array(tensors):
+    a = (C.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        a[i] = L.ptr(t)
+    return a
+
+
+def _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, saved, B, T):
+    a = L.GruStack()
+    a.B, a.T, a.In, a.H, a.L, a.ndir = B, T, cfg.input_size, cfg.hidden_size, cfg.num_layers, cfg.ndir
+    a.save_for_backward = 1 if saved is not None else 0
+    a.ids_are_i64 = 1 if (is_ids and x.dtype == torch.int64) else 0
+    if is_ids:
+        a.ids, a.table, a.vocab, a.pad_id = L.ptr(x), L.ptr(cfg.table), cfg.table.shape[0], cfg.pad_id
+    else:
+        a.x = L.ptr(x)
+    a.dropout_p, a.seed = cfg.dropout_p, seed
+    a.weights = C.cast(warr, C.POINTER(C.c_void_p))
+    a.lengths, a.out, a.h_n = L.ptr(cfg.lengths), L.ptr(out), L.ptr(h_n)
+    if saved is not None:
+        a.saved, a.saved_bytes = saved.data_ptr(), saved.numel()
+    return a
+
+
 class GRUStackFunction(torch.autograd.Function):
     """Multi-layer (bi)directional GRU == nn.GRU(batch_first=True) (reference: simple_two_tower.py:17-32,
-    margin_two_tower.py:12-28, enhanced_two_tower.py:17-33).  Inputs: cfg, x ([B,T,In] fp32 or [B,T] ids),
-    then the flat nn.GRU weight list.  Returns (output of the last layer, h_n [L*ndir,B,H])."""
+    margin_two_tower.py:12-28, enhanced_two_tower.py:17-33) through tt_gru_stack_fwd / tt_gru_stack_bwd.
+    Inputs: cfg, x ([B,T,In] fp32 or [B,T] ids), then the flat nn.GRU weight list.
+    Returns (output of the last layer or an empty tensor when cfg.need_out is False, h_n [L*ndir,B,H])."""
 
     @staticmethod
     def forward(ctx, cfg, x, *weights):
@@ -63,72 +88,59 @@ class GRUStackFunction(torch.autograd.Function):
         is_ids = not torch.is_floating_point(x)
         if is_ids and cfg.table is None:
             raise RuntimeError("token ids given but the GRU has no embedding table")
+        if is_ids and x.dtype not in (torch.int32, torch.int64):
+            x = x.long()
         x = x.contiguous() if is_ids else L.f32c(x)
         weights = [L.f32c(w) for w in weights]
         B, T = x.shape[0], x.shape[1]
         H, nd, dev = cfg.hidden_size, cfg.ndir, x.device
-        outs, gates_l, seeds = [], [], []
         h_n = torch.empty(cfg.num_layers * nd, B, H, device=dev, dtype=torch.float32)
-        inp = x
-        for l in range(cfg.num_layers):
-            out = torch.empty(B, T, nd * H, device=dev, dtype=torch.float32)
-            gates = torch.empty(nd, B, T, 4 * H, device=dev, dtype=torch.float32) if cfg.need_grad else None
-            seed = _next_seed() if (l > 0 and cfg.dropout_p > 0) else 0
-            a = _fill_layer(cfg, l, None if (l == 0 and is_ids) else inp, inp if (l == 0 and is_ids) else None,
-                            weights, out, h_n[l * nd:(l + 1) * nd], gates, seed, None, B, T)
-            ws = L.workspace(lib.tt_gru_layer_fwd_workspace(C.byref(a)), dev)
-            a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
-            L.check(lib.tt_gru_layer_fwd(C.byref(a), L.stream()), "tt_gru_layer_fwd")
-            outs.append(out); gates_l.append(gates); seeds.append(seed)
-            inp = out
+        out = torch.empty(B, T, nd * H, device=dev, dtype=torch.float32) if cfg.need_out else None
+        seed = _next_seed() if (cfg.num_layers > 1 and cfg.dropout_p > 0) else 0
+        warr = _ptr_array(weights)
+        a = _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, None, B, T)
+        saved = None
         if cfg.need_grad:
-            ctx.cfg, ctx.is_ids, ctx.seeds, ctx.nw = cfg, is_ids, seeds, len(weights)
-            ctx.save_for_backward(x, *weights, *outs, *gates_l)
-        return outs[-1], h_n
+            a.save_for_backward = 1
+            saved = L.workspace(lib.tt_gru_stack_saved_bytes(C.byref(a)), dev)
+            a.saved, a.saved_bytes = saved.data_ptr(), saved.numel()
+        ws = L.workspace(lib.tt_gru_stack_fwd_workspace(C.byref(a)), dev)
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        L.check(lib.tt_gru_stack_fwd(C.byref(a), L.stream()), "tt_gru_stack_fwd")
+        if cfg.need_grad:
+            ctx.cfg, ctx.is_ids, ctx.seed, ctx.nw = cfg, is_ids, seed, len(weights)
+            ctx.save_for_backward(x, saved, *weights)
+        if out is None:
+            out = torch.empty(0, device=dev, dtype=torch.float32)
+            ctx.mark_non_differentiable(out)
+        return out, h_n
 
     @staticmethod
     def backward(ctx, d_out, d_h_n):
         lib = L.lib()
-        cfg, nw = ctx.cfg, ctx.nw
-        saved = ctx.saved_tensors
-        x, weights = saved[0], list(saved[1:1 + nw])
-        nl, nd, H = cfg.num_layers, cfg.ndir, cfg.hidden_size
-        outs, gates_l = saved[1 + nw:1 + nw + nl], saved[1 + nw + nl:1 + nw + 2 * nl]
+        cfg = ctx.cfg
+        x, saved = ctx.saved_tensors[0], ctx.saved_tensors[1]
+        weights = list(ctx.saved_tensors[2:])
         B, T, dev = x.shape[0], x.shape[1], x.device
-        d_out = L.f32c(d_out) if d_out is not None else None
+        d_out = L.f32c(d_out) if (d_out is not None and cfg.need_out) else None
         d_h_n = L.f32c(d_h_n) if d_h_n is not None else None
         grads = [torch.empty_like(w) for w in weights]
         need_dx0 = (not ctx.is_ids) and ctx.needs_input_grad[1]
-        d_above, d_x0 = d_out, None
-        for l in reversed(range(nl)):
-            inp = x if l == 0 else outs[l - 1]
-            ids_l = l == 0 and ctx.is_ids
-            g = L.GruLayerGrad()
-            g.fwd = _fill_layer(cfg, l, None if ids_l else inp, inp if ids_l else None, weights, outs[l],
-                                None, gates_l[l], ctx.seeds[l], None, B, T)
-            g.fwd.h_n = L.ptr(outs[l])  # not read by backward; any valid pointer satisfies the arg check
-            g.d_out = L.ptr(d_above)
-            g.d_h_n = L.ptr(d_h_n[l * nd:(l + 1) * nd].contiguous()) if d_h_n is not None else None
-            d_x = None
-            if l > 0 or need_dx0:
-                d_x = torch.empty(B, T, g.fwd.In, device=dev, dtype=torch.float32)
-            g.d_x = L.ptr(d_x)
-            gw = grads[l * nd * 4:(l + 1) * nd * 4]
-            g.d_w_ih = _arr2([gw[4 * d + 0] for d in range(nd)])
-            g.d_w_hh = _arr2([gw[4 * d + 1] for d in range(nd)])
-            g.d_b_ih = _arr2([gw[4 * d + 2] for d in range(nd)])
-            g.d_b_hh = _arr2([gw[4 * d + 3] for d in range(nd)])
-            ws = L.workspace(lib.tt_gru_layer_bwd_workspace(C.byref(g)), dev)
-            g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
-            L.check(lib.tt_gru_layer_bwd(C.byref(g), L.stream()), "tt_gru_layer_bwd")
-            d_above = d_x
-            if l == 0:
-                d_x0 = d_x
-        return (None, d_x0 if need_dx0 else None, *grads)
+        d_x = torch.empty_like(x) if need_dx0 else None
+        warr, garr = _ptr_array(weights), _ptr_array(grads)
+        g = L.GruStackGrad()
+        g.fwd = _fill_stack(cfg, x, ctx.is_ids, weights, warr, None, d_h_n if d_h_n is not None else grads[0], ctx.seed,
+                            saved, B, T)
+        g.d_out, g.d_h_n, g.d_x = L.ptr(d_out), L.ptr(d_h_n), L.ptr(d_x)
+        g.d_weights = C.cast(garr, C.POINTER(C.c_void_p))
+        ws = L.workspace(lib.tt_gru_stack_bwd_workspace(C.byref(g)), dev)
+        g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
+        L.check(lib.tt_gru_stack_bwd(C.byref(g), L.stream()), "tt_gru_stack_bwd")
+        return (None, d_x, *grads)
 
 
 def gru_stack(x, weights, input_size, hidden_size, num_layers=2, bidirectional=True, dropout_p=0.0, training=False,
-              lengths=None, table=None, pad_id=-1):
+              lengths=None, table=None, pad_id=-1, need_out=True):
     need_grad = torch.is_grad_enabled() and (any(w.requires_grad for w in weights) or
                                              (torch.is_floating_point(x) and x.requires_grad))
     if lengths is not None:
@@ -137,6 +149,7 @@ def gru_stack(x, weights, input_size, hidden_size, num_layers=2, bidirectional=T
         table = L.f32c(table.detach())
     cfg = GRUConfig(input_size, hidden_size, num_layers, 2 if bidirectional else 1, dropout_p, training, lengths,
                     table, pad_id, need_grad)
+    cfg.need_out = bool(need_out)
     return GRUStackFunction.apply(cfg, x, *weights)
 
 

@@ -38,12 +38,13 @@ class GRU(nn.Module):
     def flat_weights(self):
         return [getattr(self, n) for n in self._names]
 
-    def forward(self, x, lengths=None, table=None, pad_id=-1):
+    def forward(self, x, lengths=None, table=None, pad_id=-1, need_output=True):
         """x: float [B,T,input_size] or integer ids [B,T] (needs `table` [V,input_size]).
-        Returns (output [B,T,ndir*H], h_n [num_layers*ndir,B,H]) like nn.GRU(batch_first=True)."""
+        Returns (output [B,T,ndir*H], h_n [num_layers*ndir,B,H]) like nn.GRU(batch_first=True); with
+        need_output=False (what the towers use: they only read h_n) output is an empty tensor and is never written."""
         return Fn.gru_stack(x, self.flat_weights(), self.input_size, self.hidden_size, self.num_layers,
                             self.bidirectional, self.dropout, self.training, lengths=lengths, table=table,
-                            pad_id=pad_id)
+                            pad_id=pad_id, need_out=need_output)
 
     def extra_repr(self):
         return (f"{self.input_size}, {self.hidden_size}, num_layers={self.num_layers}, batch_first=True, "

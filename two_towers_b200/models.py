@@ -49,7 +49,7 @@ class _TwoTowerBase(nn.Module):
         if not x.is_cuda:
             raise RuntimeError("two_towers_b200 models run on CUDA only (no CPU fallback); call .to('cuda')")
         table = self._emb_table if not torch.is_floating_point(x) else None
-        _, h_n = encoder(x, lengths=lengths, table=table, pad_id=self._pad_id)
+        _, h_n = encoder(x, lengths=lengths, table=table, pad_id=self._pad_id, need_output=False)
         lin1, ln, lin2, drop = _head_modules(proj)
         p = drop.p if (drop is not None and self.training) else 0.0
         return Fn.head(h_n[-2], h_n[-1], lin1.weight, lin1.bias, ln.weight, ln.bias,
@@ -157,7 +157,7 @@ class TokenTwoTowerModel(nn.Module):
     def _enc(self, ids, enc, lengths=None):
         if not ids.is_cuda:
             raise RuntimeError("two_towers_b200 models run on CUDA only (no CPU fallback)")
-        return enc(ids, lengths=lengths, table=self.embedding_weight, pad_id=self.padding_idx)[1][-1]
+        return enc(ids, lengths=lengths, table=self.embedding_weight, pad_id=self.padding_idx, need_output=False)[1][-1]
 
     def encode_query(self, query, lengths=None):
         return self._enc(query, self.query_encoder, lengths)
