@@ -100,9 +100,9 @@ int gemm_f32(const GemmArgs& gin, cudaStream_t s) {
   const int64_t tiles = ceil_div(g.M, BM) * ceil_div(g.N, BN) * g.nbatch;
   if (g.splitk <= 0) {
     g.splitk = 1;
-    if (tiles < 148 && g.K >= 4096) {
+    if (tiles < 148 && g.K >= 1024) {
       int64_t want = ceil_div(2 * 148, tiles);
-      int64_t maxs = g.K / 1024;
+      int64_t maxs = g.K / 256;
       g.splitk = (int)(want < maxs ? want : maxs);
       if (g.splitk < 1) g.splitk = 1;
     }

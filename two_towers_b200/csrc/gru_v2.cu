@@ -147,7 +147,7 @@ constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
 constexpr int S_A_BYTES = S_BM * S_BK * 2, S_B_BYTES = S_BN * S_BK * 2;
 constexpr int S_STAGE = 2 * S_A_BYTES + 2 * S_B_BYTES;   // 81920
 constexpr int S_STAGES = 2;
-constexpr int S_SMEM = S_STAGES * S_STAGE + 1024 + 128;
+constexpr int S_SMEM = S_STAGES * S_STAGE + 1024 + 512;   // + barriers, tmem slot, b_hn slice
 constexpr int S_TMEM_COLS = 256;
 constexpr int S_THREADS = 320;                           // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 
@@ -157,7 +157,6 @@ struct alignas(64) Step2Params {
   CUtensorMap x_hi, x_lo;            // next layer's input planes [T*Bp][ndir*H], box 64 x 128 (store)
   const float* gi;                   // tiled [ndir][T][MT][3][H/4][128][4], biases folded
   const float* b_hh[2];              // only the n-gate third is read
-  float* hs;                         // tiled running state [ndir][MT][H/4][128][4]
   uint4* g16;                        // saved gates [ndir][T][MT][H/4][128][16 x 16 bit] or null
   float* hn;                         // saved h W_hn^T + b_hn, tiled [ndir][T][MT][H/4][128][4] or null
   float* out;                        // fp32 [B,T,ndir*H] or null
@@ -176,9 +175,13 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
   uint64_t* empty = bars + S_STAGES;
   uint64_t* tfull = bars + 2 * S_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
+  float* bhn_s = reinterpret_cast<float*>(bars + 8);                 // [64] b_hn of this CTA's units
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.z, mt = blockIdx.y, m0 = mt * S_BM, u0 = blockIdx.x * S_UN;
   const int H = p.H, T = p.T, KB = H / S_BK, MT = p.Bp >> 7;
+  // k-blocks are consumed in rotated order so that this CTA's OWN 64 units (= h_{t-1} of the units it updates) are
+  // the last A tile to land: it is still in shared memory when the epilogue needs h_prev (no fp32 state in HBM)
+  const int own_kb = blockIdx.x, own_stage = (KB - 1) % S_STAGES;
   const int t = dir == 0 ? p.step : T - 1 - p.step;
   const int rslot = dir == 0 ? t : t + 1, wslot = dir == 0 ? t + 1 : t;
 
@@ -201,12 +204,13 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
         uint8_t* st = smem + stage * S_STAGE;
         uint8_t* sa_hi = st, *sa_lo = st + S_A_BYTES, *sb_hi = st + 2 * S_A_BYTES, *sb_lo = sb_hi + S_B_BYTES;
         mbar_arrive_expect_tx(&full[stage], S_STAGE);
-        tma_load_2d(&p.h_hi[dir], &full[stage], sa_hi, kb * S_BK, rslot * p.Bp + m0);
-        tma_load_2d(&p.h_lo[dir], &full[stage], sa_lo, kb * S_BK, rslot * p.Bp + m0);
+        const int kk = (own_kb + 1 + kb) % KB;
+        tma_load_2d(&p.h_hi[dir], &full[stage], sa_hi, kk * S_BK, rslot * p.Bp + m0);
+        tma_load_2d(&p.h_lo[dir], &full[stage], sa_lo, kk * S_BK, rslot * p.Bp + m0);
 #pragma unroll
         for (int g = 0; g < 3; ++g) {       // gate g rows [g*H + u0, +64) of W_hh -> tile columns [64 g, 64 g + 64)
-          tma_load_2d(&p.w_hi[dir], &full[stage], sb_hi + g * (S_UN * 128), kb * S_BK, g * H + u0);
-          tma_load_2d(&p.w_lo[dir], &full[stage], sb_lo + g * (S_UN * 128), kb * S_BK, g * H + u0);
+          tma_load_2d(&p.w_hi[dir], &full[stage], sb_hi + g * (S_UN * 128), kk * S_BK, g * H + u0);
+          tma_load_2d(&p.w_lo[dir], &full[stage], sb_lo + g * (S_UN * 128), kk * S_BK, g * H + u0);
         }
         if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
       }
@@ -253,11 +257,17 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
         gi_n[i] = __ldg(g + ((int64_t)2 * h4 + i) * 128);
       }
     }
-    float4* hs = reinterpret_cast<float4*>(p.hs) + (((int64_t)dir * MT + mt) * h4 + (uh >> 2)) * 128 + row;
-    const float4* bhn = reinterpret_cast<const float4*>(p.b_hh[dir] + 2 * H + uh);
+    {
+      const int e = threadIdx.x - 64;
+      if (e < S_UN) bhn_s[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
+    }
     const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
-    uint8_t* stg = smem;                                       // 4 x 16 KB staging tiles (operand stage 0 is free after tfull)
+    // 4 x 16 KB staging tiles in the operand stage that does NOT hold the own A tile (free once tfull has fired)
+    uint8_t* stg = smem + (own_stage == 0 ? S_STAGE : 0);
+    const uint8_t* own_hi = smem + own_stage * S_STAGE, *own_lo = own_hi + S_A_BYTES;
+    named_bar_sync(2, 256);                                    // bhn_s visible
     mbar_wait(tfull, 0);
+    mbar_wait(&full[own_stage], ((KB - 1) / S_STAGES) & 1);   // already complete: orders the TMA-written tile before our reads
     tc_fence_after();
     const uint32_t tl = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(32 * half);
 #pragma unroll
@@ -266,10 +276,21 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
       tmem_ld8(tl + 8 * c, ar);
       tmem_ld8(tl + S_UN + 8 * c, az);
       tmem_ld8(tl + 2 * S_UN + 8 * c, an);
-      const float4 hp0 = hs[(2 * c) * 128], hp1 = hs[(2 * c + 1) * 128];
-      const float4 bn0 = __ldg(bhn + 2 * c), bn1 = __ldg(bhn + 2 * c + 1);
+      const uint32_t off = sw128_off(row, 4 * half + c);
+      const uint4 ph = *reinterpret_cast<const uint4*>(own_hi + off), pl = *reinterpret_cast<const uint4*>(own_lo + off);
+      const float4 bn0 = *reinterpret_cast<const float4*>(bhn_s + 32 * half + 8 * c);
+      const float4 bn1 = *reinterpret_cast<const float4*>(bhn_s + 32 * half + 8 * c + 4);
       tmem_wait_ld();
-      const float hp[8] = {hp0.x, hp0.y, hp0.z, hp0.w, hp1.x, hp1.y, hp1.z, hp1.w};
+      float hp[8];
+      {
+        const uint32_t hw[4] = {ph.x, ph.y, ph.z, ph.w}, lw[4] = {pl.x, pl.y, pl.z, pl.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&hw[i]));
+          const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&lw[i]));
+          hp[2 * i] = a.x + b2.x; hp[2 * i + 1] = a.y + b2.y;
+        }
+      }
       const float bn[8] = {bn0.x, bn0.y, bn0.z, bn0.w, bn1.x, bn1.y, bn1.z, bn1.w};
       const float gr[8] = {gi_r[2 * c].x, gi_r[2 * c].y, gi_r[2 * c].z, gi_r[2 * c].w,
                            gi_r[2 * c + 1].x, gi_r[2 * c + 1].y, gi_r[2 * c + 1].z, gi_r[2 * c + 1].w};
@@ -294,8 +315,6 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
           xo[j] = 0.f;
         }
       }
-      hs[(2 * c) * 128] = make_float4(h[0], h[1], h[2], h[3]);
-      hs[(2 * c + 1) * 128] = make_float4(h[4], h[5], h[6], h[7]);
       if (p.g16) {
 #pragma unroll
         for (int g4 = 0; g4 < 2; ++g4) {
@@ -316,7 +335,6 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
       {
         uint4 hi, lo;
         split8(h, hi, lo);
-        const uint32_t off = sw128_off(row, 4 * half + c);
         *reinterpret_cast<uint4*>(stg + off) = hi;
         *reinterpret_cast<uint4*>(stg + 16384 + off) = lo;
         if (p.has_next) {
@@ -379,14 +397,14 @@ struct alignas(64) CellBwdParams {
 };
 constexpr int CB_SMEM = 4 * 16384 + 1024;
 
-__global__ void __launch_bounds__(256) cell_bwd2_kernel(const __grid_constant__ CellBwdParams p) {
+__global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ CellBwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stg = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int dir = blockIdx.z, mt = blockIdx.y, m0 = mt * 128, u0 = blockIdx.x * 64;
-  const int row = threadIdx.x & 127, half = threadIdx.x >> 7, b = m0 + row;
+  const int row = threadIdx.x & 127, qtr = threadIdx.x >> 7, b = m0 + row;      // thread = (batch row, 16 units)
   const int H = p.H, T = p.T, MT = p.Bp >> 7, h4 = H >> 2;
   const int t = dir == 0 ? p.step : T - 1 - p.step;
-  const int uh = u0 + 32 * half;
+  const int uh = u0 + 16 * qtr;
   const bool row_ok = b < p.B;
   const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
   const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
@@ -394,53 +412,59 @@ __global__ void __launch_bounds__(256) cell_bwd2_kernel(const __grid_constant__ 
   const float4* dab = p.d_above ? reinterpret_cast<const float4*>(p.d_above) +
                                       (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H + uh) >> 2)) * 128 + row
                                 : nullptr;
+  float dr[16], dz[16], dnr[16], dn[16];
+  if (live) {
+    // all loads of the 4 unit groups first (independent addresses -> one memory round trip)
+    uint4 ga[4], gb[4];
+    float4 hn4[4], dh4[4], da4[4];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    float dr[8], dz[8], dnr[8], dn[8];
-#pragma unroll
-    for (int g4 = 0; g4 < 2; ++g4) {
-      const int i = 2 * c + g4, o = 4 * g4;
-      if (live) {
-        const uint4 a = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2), bq = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2 + 1);
-        const float4 hn4 = __ldg(reinterpret_cast<const float4*>(p.hn) + gbase + (int64_t)i * 128);
-        float4 dh4 = dhs[i * 128];
-        if (dab) {
-          float4 da = __ldg(dab + (int64_t)i * 128);
-          if (p.drop_p > 0.f) {
-            const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 4 * i);
-            float s[4];
-            dropout_scale4(p.seed, e >> 2, p.drop_p, p.inv_keep, s);
-            da.x *= s[0]; da.y *= s[1]; da.z *= s[2]; da.w *= s[3];
-          }
-          dh4.x += da.x; dh4.y += da.y; dh4.z += da.z; dh4.w += da.w;
-        }
-        const float dh[4] = {dh4.x, dh4.y, dh4.z, dh4.w};
-        const float hnv[4] = {hn4.x, hn4.y, hn4.z, hn4.w};
-        const uint32_t rw[2] = {a.x, a.y}, zw[2] = {a.z, a.w}, nw[2] = {bq.x, bq.y}, qw[2] = {bq.z, bq.w};
-        float nd[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int sh = (j & 1) * 16;
-          const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw[j >> 1] >> sh);
-          const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);
-          const float dn_pre = dh[j] * (1.f - z) * (1.f - n * n);
-          dn[o + j] = dn_pre;
-          dnr[o + j] = dn_pre * r;
-          dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);
-          dz[o + j] = dh[j] * q * (1.f - z);          // == dh (h_prev - n) z (1 - z) with q = h_t - n = z (h_prev - n)
-          nd[j] = dh[j] * z;
-        }
-        dhs[i * 128] = make_float4(nd[0], nd[1], nd[2], nd[3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { dr[o + j] = 0.f; dz[o + j] = 0.f; dnr[o + j] = 0.f; dn[o + j] = 0.f; }
-      }
+    for (int i = 0; i < 4; ++i) {
+      ga[i] = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2);
+      gb[i] = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2 + 1);
+      hn4[i] = __ldg(reinterpret_cast<const float4*>(p.hn) + gbase + (int64_t)i * 128);
+      dh4[i] = dhs[i * 128];
+      da4[i] = dab ? __ldg(dab + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const uint32_t off = sw128_off(row, 4 * half + c);
-    *reinterpret_cast<uint4*>(stg + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7]));
-    *reinterpret_cast<uint4*>(stg + 16384 + off) = make_uint4(pack_h2(dz[0], dz[1]), pack_h2(dz[2], dz[3]), pack_h2(dz[4], dz[5]), pack_h2(dz[6], dz[7]));
-    *reinterpret_cast<uint4*>(stg + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7]));
-    *reinterpret_cast<uint4*>(stg + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7]));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int o = 4 * i;
+      float4 da = da4[i];
+      if (dab && p.drop_p > 0.f) {
+        const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 4 * i);
+        float s[4];
+        dropout_scale4(p.seed, e >> 2, p.drop_p, p.inv_keep, s);
+        da.x *= s[0]; da.y *= s[1]; da.z *= s[2]; da.w *= s[3];
+      }
+      const float dh[4] = {dh4[i].x + da.x, dh4[i].y + da.y, dh4[i].z + da.z, dh4[i].w + da.w};
+      const float hnv[4] = {hn4[i].x, hn4[i].y, hn4[i].z, hn4[i].w};
+      const uint32_t rw[2] = {ga[i].x, ga[i].y}, zw[2] = {ga[i].z, ga[i].w}, nw[2] = {gb[i].x, gb[i].y}, qw[2] = {gb[i].z, gb[i].w};
+      float nd[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int sh = (j & 1) * 16;
+        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw[j >> 1] >> sh);
+        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);
+        const float dn_pre = dh[j] * (1.f - z) * (1.f - n * n);
+        dn[o + j] = dn_pre;
+        dnr[o + j] = dn_pre * r;
+        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);
+        dz[o + j] = dh[j] * q * (1.f - z);            // == dh (h_prev - n) z (1 - z) with q = h_t - n = z (h_prev - n)
+        nd[j] = dh[j] * z;
+      }
+      dhs[i * 128] = make_float4(nd[0], nd[1], nd[2], nd[3]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { dr[j] = 0.f; dz[j] = 0.f; dnr[j] = 0.f; dn[j] = 0.f; }
+  }
+#pragma unroll
+  for (int cc = 0; cc < 2; ++cc) {
+    const int o = 8 * cc;
+    const uint32_t off = sw128_off(row, 2 * qtr + cc);
+    *reinterpret_cast<uint4*>(stg + off) = make_uint4(pack_h2(dr[o], dr[o + 1]), pack_h2(dr[o + 2], dr[o + 3]), pack_h2(dr[o + 4], dr[o + 5]), pack_h2(dr[o + 6], dr[o + 7]));
+    *reinterpret_cast<uint4*>(stg + 16384 + off) = make_uint4(pack_h2(dz[o], dz[o + 1]), pack_h2(dz[o + 2], dz[o + 3]), pack_h2(dz[o + 4], dz[o + 5]), pack_h2(dz[o + 6], dz[o + 7]));
+    *reinterpret_cast<uint4*>(stg + 32768 + off) = make_uint4(pack_h2(dnr[o], dnr[o + 1]), pack_h2(dnr[o + 2], dnr[o + 3]), pack_h2(dnr[o + 4], dnr[o + 5]), pack_h2(dnr[o + 6], dnr[o + 7]));
+    *reinterpret_cast<uint4*>(stg + 49152 + off) = make_uint4(pack_h2(dn[o], dn[o + 1]), pack_h2(dn[o + 2], dn[o + 3]), pack_h2(dn[o + 4], dn[o + 5]), pack_h2(dn[o + 6], dn[o + 7]));
   }
   fence_proxy_async();
   __syncthreads();
@@ -671,8 +695,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
       g.f16 = 1; g.npass = 3; g.epi = 1; g.tl_Bp = Bp; g.tl_G = 3; g.tl_Hc = H;
       TT_TRY(umma_gemm(g, s));
     }
-    // zero initial state: running fp32 state and the h_{-1} slot of each direction's planes
-    TT_CUDA(cudaMemsetAsync(f.hs, 0, sizeof(float) * nd * Bp * H, s));
+    // zero initial state: the h_{-1} slot of each direction's planes
     for (int dd = 0; dd < nd; ++dd) {
       const int64_t slot = dd == 0 ? 0 : T;
       TT_CUDA(cudaMemsetAsync(sv.hhi[l][dd] + slot * Bp * H, 0, sizeof(f16) * Bp * H, s));
@@ -691,7 +714,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
       TT_TRY(make_plane_map(&p.x_hi, sv.xhi[l + 1], d.ntok, nd * H, d.kp_l(l + 1), S_BM, 1));
       TT_TRY(make_plane_map(&p.x_lo, f.xlo[(l + 1) & 1], d.ntok, nd * H, d.kp_l(l + 1), S_BM, 1));
     }
-    p.gi = f.gi; p.hs = f.hs;
+    p.gi = f.gi;
     p.g16 = save ? sv.g16[l] : nullptr; p.hn = save ? sv.hn[l] : nullptr;
     p.out = (a->out && !has_next) ? a->out : nullptr;
     p.h_n = a->h_n + (int64_t)l * nd * B * H;
@@ -796,7 +819,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     for (int step = T - 1; step >= 0; --step) {
       cp.step = step;
       note_launch();
-      cell_bwd2_kernel<<<cgrid, 256, CB_SMEM, s>>>(cp);
+      cell_bwd2_kernel<<<cgrid, 512, CB_SMEM, s>>>(cp);
       if (step == 0) break;
       const int row0[2] = {step * Bp, (T - 1 - step) * Bp};
       TT_TRY(umma_gemm_launch(prep, row0, s));

@@ -186,13 +186,13 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
     GemmArgs gx{};
     gx.A[0] = S; gx.B[0] = y + (int64_t)c0 * D; gx.C[0] = dx;
     gx.a_rs = NC; gx.a_cs = 1; gx.b_rs = 1; gx.b_cs = D; gx.ldc = D;
-    gx.M = Bl; gx.N = D; gx.K = nc; gx.nbatch = 1; gx.splitk = 1; gx.alpha = 1.f; gx.beta = c0 == 0 ? 0.f : 1.f;
+    gx.M = Bl; gx.N = D; gx.K = nc; gx.nbatch = 1; gx.splitk = 0; gx.alpha = 1.f; gx.beta = c0 == 0 ? 0.f : 1.f;
     TT_TRY(gemm_f32(gx, s));
     // dy[c0:c0+nc, D] = G^T X
     GemmArgs gy{};
     gy.A[0] = S; gy.B[0] = x; gy.C[0] = dy + (int64_t)c0 * D;
     gy.a_rs = 1; gy.a_cs = NC; gy.b_rs = 1; gy.b_cs = D; gy.ldc = D;
-    gy.M = nc; gy.N = D; gy.K = Bl; gy.nbatch = 1; gy.splitk = 1; gy.alpha = 1.f; gy.beta = 0.f;
+    gy.M = nc; gy.N = D; gy.K = Bl; gy.nbatch = 1; gy.splitk = 0; gy.alpha = 1.f; gy.beta = 0.f;
     TT_TRY(gemm_f32(gy, s));
   }
   TT_LAUNCH_CHECK();

@@ -187,19 +187,23 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         if (row_ok && gn0 < p.N && kb0 < kb1) {
           if (p.epi == 1) {
             const int hc4 = p.tl_Hc >> 2;
+            float4* dst[8];
+            float4 cv[8];
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const int n = gn0 + j;
+            for (int j = 0; j < 8; ++j) {          // all read-modify-write loads first: one L2 round trip, not eight
+              const int n = gn0 + 4 * j;
+              const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
+              dst[j] = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
+              cv[j] = (p.beta != 0.f && n < p.N) ? *dst[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int n = gn0 + 4 * j;
               if (n < p.N) {
-                const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
-                float4* dst = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
-                float4 o = make_float4(alpha * v[j], alpha * v[j + 1], alpha * v[j + 2], alpha * v[j + 3]);
-                if (p.beta != 0.f) {
-                  const float4 c = *dst;
-                  o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
-                }
+                float4 o = make_float4(alpha * v[4 * j] + p.beta * cv[j].x, alpha * v[4 * j + 1] + p.beta * cv[j].y,
+                                       alpha * v[4 * j + 2] + p.beta * cv[j].z, alpha * v[4 * j + 3] + p.beta * cv[j].w);
                 if (bias) { o.x += bias[n]; o.y += bias[n + 1]; o.z += bias[n + 2]; o.w += bias[n + 3]; }
-                *dst = o;
+                *dst[j] = o;
               }
             }
           } else if (p.splitk > 1) {
