@@ -244,6 +244,14 @@ int tt_gemm_x3(const float* A, const float* B, float* C, const float* bias, int3
                float alpha, float beta, int32_t trans, int32_t splitk, void* workspace, uint64_t workspace_bytes,
                void* stream);
 
+/* profiling aid: device buffer of 8 x uint64 %globaltimer marks per CTA of the most recent recurrence-step launch
+ * (NULL = off): start, MMA thread ready, first operand tile landed, all MMAs issued, accumulator ready, epilogue
+ * math done, TMA store drained, CTA end.  See tools/step_phases.py. */
+int tt_debug_step_buffer(void* buf);
+/* forward recurrence of the v2 pipeline: 4 (default) / 2 = ONE persistent cooperative kernel for all timesteps of a
+ * layer with 4 / 2 epilogue warps per TMEM lane quarter; 0 = one launch per timestep.  Test / measurement aid. */
+int tt_debug_seq_mode(int32_t mode);
+
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);
 

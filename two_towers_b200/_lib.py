@@ -110,6 +110,8 @@ SIGNATURES = {
     "tt_dropout": (C.c_int, [P, P, i64, F, u64, u64, P]),
     "tt_gemm_x3_workspace": (u64, [i32, i32, i32]),
     "tt_gemm_x3": (C.c_int, [P, P, P, P, i32, i32, i32, F, F, i32, i32, P, u64, P]),
+    "tt_debug_step_buffer": (C.c_int, [P]),
+    "tt_debug_seq_mode": (C.c_int, [i32]),
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
 }
 

@@ -143,6 +143,9 @@ __global__ void fold_bias_kernel(const float* __restrict__ b_ih, const float* __
 }
 
 // ------------------------------------------------------------------------------------------ K-C forward step
+unsigned long long* g_step_dbg = nullptr;
+static int g_seq_mode = 4;                    // 0: one launch per timestep; 2 / 4: persistent kernel, epilogue warps per quarter
+static int seq_mode() { return g_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
 constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
 constexpr int S_A_BYTES = S_BM * S_BK * 2, S_B_BYTES = S_BN * S_BK * 2;
 constexpr int S_STAGE = 2 * S_A_BYTES + 2 * S_B_BYTES;   // 81920
@@ -165,7 +168,18 @@ struct alignas(64) Step2Params {
   int32_t B, Bp, T, H, ndir, step, has_next;
   float drop_p, inv_keep;
   uint64_t seed;
+  unsigned long long* dbg;           // optional phase timestamps, 8 per CTA (tools/step_phases.py)
 };
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define DBG_MARK(slot)                                                                                   \
+  do {                                                                                                   \
+    if (p.dbg) p.dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtimer(); \
+  } while (0)
 
 __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_constant__ Step2Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -219,8 +233,10 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_f16(S_BM, S_BN, 0, 0);
       int stage = 0, phase = 0;
+      DBG_MARK(1);
       for (int kb = 0; kb < KB; ++kb) {
         mbar_wait(&full[stage], phase);
+        if (kb == 0) DBG_MARK(2);
         tc_fence_after();
         const uint32_t st = smem_u32(smem + stage * S_STAGE);
         const uint32_t sa_hi = st, sa_lo = st + S_A_BYTES, sb_hi = st + 2 * S_A_BYTES, sb_lo = sb_hi + S_B_BYTES;
@@ -236,6 +252,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
         if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
       }
       mma_commit(tfull);
+      DBG_MARK(3);
     }
   } else {
     // ------------------------------------------------------------------ fused GRU cell: thread = (batch row, 32 units)
@@ -269,6 +286,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
     mbar_wait(tfull, 0);
     mbar_wait(&full[own_stage], ((KB - 1) / S_STAGES) & 1);   // already complete: orders the TMA-written tile before our reads
     tc_fence_after();
+    if (threadIdx.x == 64) DBG_MARK(4);
     const uint32_t tl = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(32 * half);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {                              // 8 units per chunk
@@ -367,6 +385,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
     fence_proxy_async();
     named_bar_sync(1, 256);
     if (warp == 2 && lane == 0) {
+      DBG_MARK(5);
       tma_store_2d(&p.h_hi[dir], stg, u0, wslot * p.Bp + m0);
       tma_store_2d(&p.h_lo[dir], stg + 16384, u0, wslot * p.Bp + m0);
       if (p.has_next) {
@@ -375,11 +394,316 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
       }
       bulk_commit();
       bulk_wait_read0();
+      DBG_MARK(6);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, S_TMEM_COLS);
+  if (threadIdx.x == 0) DBG_MARK(7);
+}
+
+// ------------------------------------------------------------------------------------------ K-C persistent recurrence
+// One cooperative launch runs ALL T timesteps of one layer (both directions).  Every CTA owns a fixed set of
+// (64-unit slice, batch tile, direction) tiles and walks them step by step; the step-s tile of (mt, dir) may start
+// once the H/64 CTAs that produce h_{s-1} of that batch tile have published it (release counter per (dir, mt),
+// written after their TMA stores completed).  H-plane slots, X planes and gates are distinct per timestep, so RAW
+// through the counters is the only inter-CTA dependency.  Inside a CTA three roles run a software pipeline over
+// (step, tile) items: warp 0 = TMA producer (operand ring), warp 1 = tcgen05.mma issuer (two TMEM accumulators),
+// warps 2.. = fused GRU-cell epilogue, so the cell math of one tile overlaps the operand traffic of the next.
+constexpr int Q_STAGING = 4 * 16384;
+constexpr int Q_SMEM = S_STAGES * S_STAGE + Q_STAGING + 1024 /*align*/ + 1024 /*barriers, b_hn*/;
+constexpr int Q_TMEM_COLS = 512;
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+struct alignas(64) SeqParams {
+  Step2Params s;
+  int* ready;                        // [ndir][MT] counters, zero before the launch
+  int32_t tiles;                     // (H/64) * MT * ndir
+};
+
+#define SEQ_MARK(item, slot)                                                              \
+  do {                                                                                    \
+    if (p.dbg && blockIdx.x == 0 && (item) < 256) p.dbg[(item) * 8 + (slot)] = gtimer(); \
+  } while (0)
+
+template <int EWQ>                                              // epilogue warps per TMEM lane quarter (2 or 4)
+__global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid_constant__ SeqParams sp) {
+  constexpr int UT = S_UN / EWQ;                                // hidden units per epilogue thread (32 or 16)
+  constexpr int NCH = UT / 8;                                   // 8-unit chunks per thread
+  constexpr int EPI_THREADS = 128 * EWQ;
+  const Step2Params& p = sp.s;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stg = smem + S_STAGES * S_STAGE;                     // 4 x 16 KB staging tiles (epilogue -> TMA store)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + Q_STAGING);
+  uint64_t* full = bars;                                        // [S_STAGES]
+  uint64_t* empty = bars + S_STAGES;                            // [S_STAGES], 2 arrivals per use
+  uint64_t* tfull = bars + 2 * S_STAGES;                        // [2]
+  uint64_t* tempty = tfull + 2;                                 // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* bhn_s = reinterpret_cast<float*>(bars + 16);           // [2][64]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int H = p.H, T = p.T, KB = H / S_BK, MT = p.Bp >> 7, US = H / S_UN;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 2); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 1); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Q_TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================================= TMA producer
+    if (lane == 0) {
+      int stage = 0, phase = 0, pitem = 0;
+      for (int step = 0; step < T; ++step) {
+        for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++pitem) {
+          const int us = tile % US, mt = (tile / US) % MT, dir = tile / (US * MT);
+          const int t = dir == 0 ? step : T - 1 - step;
+          const int rslot = dir == 0 ? t : t + 1;
+          const int m0 = mt * S_BM, u0 = us * S_UN;
+          for (int kb = 0; kb < KB; ++kb) {
+            const int kk = (us + 1 + kb) % KB;                  // own k-block last (the epilogue reads h_prev from it)
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* st = smem + stage * S_STAGE;
+            uint8_t* sa_hi = st, *sa_lo = st + S_A_BYTES, *sb_hi = st + 2 * S_A_BYTES, *sb_lo = sb_hi + S_B_BYTES;
+            mbar_arrive_expect_tx(&full[stage], S_STAGE);
+#pragma unroll
+            for (int g = 0; g < 3; ++g) {
+              tma_load_2d(&p.w_hi[dir], &full[stage], sb_hi + g * (S_UN * 128), kk * S_BK, g * H + u0);
+              tma_load_2d(&p.w_lo[dir], &full[stage], sb_lo + g * (S_UN * 128), kk * S_BK, g * H + u0);
+            }
+            if (kb == 0) SEQ_MARK(pitem, 0);
+            if (kb == 0 && step > 0) {                           // h_{step-1} of this batch tile published by all US producers?
+              const int* flag = sp.ready + dir * MT + mt;
+              const int need = US * step;
+              while (ld_acquire_gpu(flag) < need) __nanosleep(40);
+              fence_proxy_async_global();
+            }
+            if (kb == 0) SEQ_MARK(pitem, 1);
+            if (kb == KB - 1) SEQ_MARK(pitem, 2);
+            tma_load_2d(&p.h_hi[dir], &full[stage], sa_hi, kk * S_BK, rslot * p.Bp + m0);
+            tma_load_2d(&p.h_lo[dir], &full[stage], sa_lo, kk * S_BK, rslot * p.Bp + m0);
+            if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(S_BM, S_BN, 0, 0);
+      int stage = 0, phase = 0, item = 0;
+      for (int step = 0; step < T; ++step) {
+        for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++item) {
+          const int acc = item & 1, acc_phase = (item >> 1) & 1;
+          mbar_wait(&tempty[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * 256;
+          for (int kb = 0; kb < KB; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            const uint32_t st = smem_u32(smem + stage * S_STAGE);
+            const uint32_t sa_hi = st, sa_lo = st + S_A_BYTES, sb_hi = st + 2 * S_A_BYTES, sb_lo = sb_hi + S_B_BYTES;
+#pragma unroll
+            for (int term = 0; term < 3; ++term) {
+              const uint32_t sa = term == 1 ? sa_lo : sa_hi, sb = term == 2 ? sb_lo : sb_hi;
+#pragma unroll
+              for (int k = 0; k < S_BK / 16; ++k)
+                mma_bf16_ss(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                            (kb > 0 || term > 0 || k > 0) ? 1u : 0u);
+            }
+            mma_commit(&empty[stage]);                           // arrival 1 of 2: the MMAs have read the stage
+            if (kb != KB - 1) mbar_arrive(&empty[stage]);        // arrival 2 of 2 (the own tile is released by the epilogue)
+            if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+          }
+          mma_commit(&tfull[acc]);
+        }
+      }
+    }
+  } else {
+    // ================================================================= fused GRU cell: thread = (batch row, UT units)
+    const int e = threadIdx.x - 64;
+    const int quarter = warp & 3, sub = (warp - 2) >> 2;
+    const int row = quarter * 32 + lane;
+    const int h4 = H >> 2;
+    int item = 0;
+    for (int step = 0; step < T; ++step) {
+      for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++item) {
+        const int us = tile % US, mt = (tile / US) % MT, dir = tile / (US * MT);
+        const int t = dir == 0 ? step : T - 1 - step;
+        const int wslot = dir == 0 ? t + 1 : t;
+        const int m0 = mt * S_BM, u0 = us * S_UN, b = m0 + row;
+        const int uh = u0 + UT * sub;
+        const bool row_ok = b < p.B;
+        const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
+        const int acc = item & 1, acc_phase = (item >> 1) & 1;
+        // input-projection terms of this (step, tile): independent of the recurrence -> in flight during the MMA
+        float4 gi_r[UT / 4], gi_z[UT / 4], gi_n[UT / 4];
+        {
+          const float4* g = reinterpret_cast<const float4*>(p.gi) +
+                            ((((int64_t)dir * T + t) * MT + mt) * 3 * h4 + (uh >> 2)) * 128 + row;
+#pragma unroll
+          for (int i = 0; i < UT / 4; ++i) {
+            gi_r[i] = __ldg(g + (int64_t)i * 128);
+            gi_z[i] = __ldg(g + ((int64_t)h4 + i) * 128);
+            gi_n[i] = __ldg(g + ((int64_t)2 * h4 + i) * 128);
+          }
+        }
+        float* bh = bhn_s + (item & 1) * S_UN;
+        if (e < S_UN) bh[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
+        const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
+        // ring position of the own A tile (last k-block of this item)
+        const int own_pos = (item + 1) * KB - 1, own_stage = own_pos % S_STAGES;
+        const uint8_t* own_hi = smem + own_stage * S_STAGE, *own_lo = own_hi + S_A_BYTES;
+        if (e == 0) SEQ_MARK(item, 3);
+        mbar_wait(&tfull[acc], acc_phase);
+        if (e == 0) SEQ_MARK(item, 4);
+        mbar_wait(&full[own_stage], (own_pos / S_STAGES) & 1);  // already complete: orders the TMA-written tile before our reads
+        tc_fence_after();
+        // h_prev of this thread's units out of the operand tile, then hand the ring stage back to the producer
+        uint4 ph[NCH], pl[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          const uint32_t off = sw128_off(row, NCH * sub + c);
+          ph[c] = *reinterpret_cast<const uint4*>(own_hi + off);
+          pl[c] = *reinterpret_cast<const uint4*>(own_lo + off);
+        }
+        named_bar_sync(1, EPI_THREADS);      // all h_prev reads done, bhn_s written, previous item's staging drained
+        if (e == 0) mbar_arrive(&empty[own_stage]);
+        const uint32_t tl = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 256 + UT * sub);
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {                          // 8 units per chunk
+          float ar[8], az[8], an[8];
+          tmem_ld8(tl + 8 * c, ar);
+          tmem_ld8(tl + S_UN + 8 * c, az);
+          tmem_ld8(tl + 2 * S_UN + 8 * c, an);
+          const float4 bn0 = *reinterpret_cast<const float4*>(bh + UT * sub + 8 * c);
+          const float4 bn1 = *reinterpret_cast<const float4*>(bh + UT * sub + 8 * c + 4);
+          tmem_wait_ld();
+          float hp[8];
+          {
+            const uint32_t hw[4] = {ph[c].x, ph[c].y, ph[c].z, ph[c].w}, lw[4] = {pl[c].x, pl[c].y, pl[c].z, pl[c].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&hw[i]));
+              const float2 b2 = __half22float2(*reinterpret_cast<const __half2*>(&lw[i]));
+              hp[2 * i] = a.x + b2.x; hp[2 * i + 1] = a.y + b2.y;
+            }
+          }
+          const float bn[8] = {bn0.x, bn0.y, bn0.z, bn0.w, bn1.x, bn1.y, bn1.z, bn1.w};
+          const float gr[8] = {gi_r[2 * c].x, gi_r[2 * c].y, gi_r[2 * c].z, gi_r[2 * c].w,
+                               gi_r[2 * c + 1].x, gi_r[2 * c + 1].y, gi_r[2 * c + 1].z, gi_r[2 * c + 1].w};
+          const float gz[8] = {gi_z[2 * c].x, gi_z[2 * c].y, gi_z[2 * c].z, gi_z[2 * c].w,
+                               gi_z[2 * c + 1].x, gi_z[2 * c + 1].y, gi_z[2 * c + 1].z, gi_z[2 * c + 1].w};
+          const float gn[8] = {gi_n[2 * c].x, gi_n[2 * c].y, gi_n[2 * c].z, gi_n[2 * c].w,
+                               gi_n[2 * c + 1].x, gi_n[2 * c + 1].y, gi_n[2 * c + 1].z, gi_n[2 * c + 1].w};
+          float h[8], xo[8], r[8], z[8], n[8], q[8], hn[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (live) {
+              r[j] = fast_sigmoid(gr[j] + ar[j]);
+              z[j] = fast_sigmoid(gz[j] + az[j]);
+              hn[j] = an[j] + bn[j];
+              n[j] = fast_tanh(gn[j] + r[j] * hn[j]);
+              h[j] = (1.f - z[j]) * n[j] + z[j] * hp[j];
+              q[j] = h[j] - n[j];
+              xo[j] = h[j];
+            } else {                                           // padded step / pad row: state carries, output is zero
+              r[j] = 0.f; z[j] = 1.f; hn[j] = 0.f; n[j] = 0.f; q[j] = 0.f;
+              h[j] = row_ok ? hp[j] : 0.f;
+              xo[j] = 0.f;
+            }
+          }
+          if (p.g16) {
+#pragma unroll
+            for (int g4 = 0; g4 < 2; ++g4) {
+              const int o = 4 * g4;
+              uint4 a, bq;
+              a.x = q_u16(r[o]) | (q_u16(r[o + 1]) << 16); a.y = q_u16(r[o + 2]) | (q_u16(r[o + 3]) << 16);
+              a.z = q_u16(z[o]) | (q_u16(z[o + 1]) << 16); a.w = q_u16(z[o + 2]) | (q_u16(z[o + 3]) << 16);
+              bq.x = q_s16(n[o], kNScale) | (q_s16(n[o + 1], kNScale) << 16);
+              bq.y = q_s16(n[o + 2], kNScale) | (q_s16(n[o + 3], kNScale) << 16);
+              bq.z = q_s16(q[o], kQScale) | (q_s16(q[o + 1], kQScale) << 16);
+              bq.w = q_s16(q[o + 2], kQScale) | (q_s16(q[o + 3], kQScale) << 16);
+              uint4* gp = p.g16 + (gbase + (int64_t)(2 * c + g4) * 128) * 2;
+              gp[0] = a; gp[1] = bq;
+              reinterpret_cast<float4*>(p.hn)[gbase + (int64_t)(2 * c + g4) * 128] = make_float4(hn[o], hn[o + 1], hn[o + 2], hn[o + 3]);
+            }
+          }
+          {
+            const uint32_t off = sw128_off(row, NCH * sub + c);
+            uint4 hi, lo;
+            split8(h, hi, lo);
+            *reinterpret_cast<uint4*>(stg + off) = hi;
+            *reinterpret_cast<uint4*>(stg + 16384 + off) = lo;
+            if (p.has_next) {
+              if (p.drop_p > 0.f && row_ok) {
+                const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 8 * c);
+                float s0[4], s1[4];
+                dropout_scale4(p.seed, el >> 2, p.drop_p, p.inv_keep, s0);
+                dropout_scale4(p.seed, (el >> 2) + 1, p.drop_p, p.inv_keep, s1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { xo[j] *= s0[j]; xo[4 + j] *= s1[j]; }
+              }
+              split8(xo, hi, lo);
+              *reinterpret_cast<uint4*>(stg + 32768 + off) = hi;
+              *reinterpret_cast<uint4*>(stg + 49152 + off) = lo;
+            }
+          }
+          if (row_ok) {
+            if (p.out) {
+              float4* o = reinterpret_cast<float4*>(p.out + ((int64_t)b * T + t) * (p.ndir * H) + dir * H + uh + 8 * c);
+              o[0] = live ? make_float4(h[0], h[1], h[2], h[3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+              o[1] = live ? make_float4(h[4], h[5], h[6], h[7]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            if (step == T - 1) {
+              float4* o = reinterpret_cast<float4*>(p.h_n + ((int64_t)dir * p.B + b) * H + uh + 8 * c);
+              o[0] = make_float4(h[0], h[1], h[2], h[3]);
+              o[1] = make_float4(h[4], h[5], h[6], h[7]);
+            }
+          }
+        }
+        // accumulator drained -> the MMA warp may start the item after next; staging -> global through TMA
+        tc_fence_before();
+        fence_proxy_async();
+        named_bar_sync(2, EPI_THREADS);
+        if (e == 0) {
+          SEQ_MARK(item, 5);
+          mbar_arrive(&tempty[acc]);
+          tma_store_2d(&p.h_hi[dir], stg, u0, wslot * p.Bp + m0);
+          tma_store_2d(&p.h_lo[dir], stg + 16384, u0, wslot * p.Bp + m0);
+          if (p.has_next) {
+            tma_store_2d(&p.x_hi, stg + 32768, dir * H + u0, t * p.Bp + m0);
+            tma_store_2d(&p.x_lo, stg + 49152, dir * H + u0, t * p.Bp + m0);
+          }
+          bulk_commit();
+          bulk_wait0();                                        // writes complete (not only the smem reads)
+          fence_proxy_async_global();
+          __threadfence();
+          atomicAdd(sp.ready + dir * MT + mt, 1);              // publish h_t of (us, mt, dir)
+          SEQ_MARK(item, 6);
+        }
+        // (the staging tiles are reused by the next item only after named barrier 1, which thread e == 0 reaches
+        //  after its stores have been read out)
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Q_TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------ K-C' gate gradients
@@ -609,7 +933,7 @@ uint64_t gru_stack_saved_bytes_v2(const tt_gru_stack* a) {
 }
 
 struct V2FwdWs {
-  f16* xlo[2]; f16* hlo[2]; float* gi; float* hs; float* bias; f16* wih_hi[2]; f16* wih_lo[2]; f16* whh_hi[2]; f16* whh_lo[2];
+  f16* xlo[2]; f16* hlo[2]; float* gi; float* hs; float* bias; int* ready; f16* wih_hi[2]; f16* wih_lo[2]; f16* whh_hi[2]; f16* whh_lo[2];
   V2Saved sv;                          // only used when the caller gave no saved buffer
 };
 static uint64_t carve_fwd_ws(const V2Dims& d, void* base, uint64_t size, V2FwdWs* out, bool own_saved) {
@@ -622,6 +946,7 @@ static uint64_t carve_fwd_ws(const V2Dims& d, void* base, uint64_t size, V2FwdWs
   f.gi = w.take<float>((int64_t)d.nd * d.ntok * 3 * d.H);
   f.hs = w.take<float>((int64_t)d.nd * d.Bp * d.H);
   f.bias = w.take<float>((int64_t)d.nd * 3 * d.H);
+  f.ready = w.take<int>((int64_t)d.nd * d.MT + 4);
   for (int i = 0; i < d.nd; ++i) {
     f.wih_hi[i] = w.take<f16>((int64_t)3 * d.H * kpmax); f.wih_lo[i] = w.take<f16>((int64_t)3 * d.H * kpmax);
     f.whh_hi[i] = w.take<f16>((int64_t)3 * d.H * d.H); f.whh_lo[i] = w.take<f16>((int64_t)3 * d.H * d.H);
@@ -723,11 +1048,42 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     p.drop_p = has_next ? a->dropout_p : 0.f;
     p.inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
     p.seed = a->seed + (uint64_t)(l + 1) * 0x9E3779B97F4A7C15ull;     // per-layer stream (layer l+1's input mask)
-    dim3 grid((unsigned)(H / S_UN), (unsigned)MT, (unsigned)nd);
-    for (int step = 0; step < T; ++step) {
-      p.step = step;
+    p.dbg = g_step_dbg;
+    const int tiles = (H / S_UN) * MT * nd;
+    if (seq_mode() != 0) {
+      // persistent cooperative launch: all T steps, one CTA per SM at most
+      static int num_sms = 0, coop = -1;
+      if (!num_sms) {
+        int dev = 0;
+        TT_CUDA(cudaGetDevice(&dev));
+        TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+        TT_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+      }
+      TT_CHECK_ARG(coop == 1, "gru stack fwd (v2): device lacks cooperative launch");
+      const int tpc = (int)ceil_div(tiles, num_sms);
+      const int ncta = (int)ceil_div(tiles, tpc);
+      SeqParams sp;
+      memset(&sp, 0, sizeof(sp));
+      sp.s = p; sp.ready = f.ready; sp.tiles = tiles;
+      TT_CUDA(cudaMemsetAsync(f.ready, 0, sizeof(int) * nd * MT, s));
+      void* args[] = {&sp};
       note_launch();
-      gru_step2_kernel<<<grid, S_THREADS, S_SMEM, s>>>(p);
+      if (seq_mode() == 2) {
+        static bool a2 = false;
+        if (!a2) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a2 = true; }
+        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<2>, dim3(ncta), dim3(64 + 256), args, Q_SMEM, s));
+      } else {
+        static bool a4 = false;
+        if (!a4) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a4 = true; }
+        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<4>, dim3(ncta), dim3(64 + 512), args, Q_SMEM, s));
+      }
+    } else {
+      dim3 grid((unsigned)(H / S_UN), (unsigned)MT, (unsigned)nd);
+      for (int step = 0; step < T; ++step) {
+        p.step = step;
+        note_launch();
+        gru_step2_kernel<<<grid, S_THREADS, S_SMEM, s>>>(p);
+      }
     }
     TT_LAUNCH_CHECK();
   }
@@ -874,3 +1230,14 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
 }
 
 }  // namespace tt
+
+extern "C" int tt_debug_seq_mode(int32_t mode) {
+  if (mode != 0 && mode != 2 && mode != 4) { tt::set_error("tt_debug_seq_mode: 0, 2 or 4"); return TT_ERR_INVALID; }
+  tt::g_seq_mode = mode;
+  return TT_OK;
+}
+
+extern "C" int tt_debug_step_buffer(void* buf) {
+  tt::g_step_dbg = (unsigned long long*)buf;
+  return TT_OK;
+}
