@@ -251,6 +251,9 @@ int tt_debug_step_buffer(void* buf);
 /* forward recurrence of the v2 pipeline: 4 (default) / 2 = ONE persistent cooperative kernel for all timesteps of a
  * layer with 4 / 2 epilogue warps per TMEM lane quarter; 0 = one launch per timestep.  Test / measurement aid. */
 int tt_debug_seq_mode(int32_t mode);
+/* BPTT of the v2 pipeline: 1 (default) = fused persistent kernel (dL/dh resident in tensor memory, hidden size <= 256),
+ * 0 = gate-gradient kernel + dh GEMM per timestep. */
+int tt_debug_bwd_seq_mode(int32_t mode);
 
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);

@@ -112,6 +112,7 @@ SIGNATURES = {
     "tt_gemm_x3": (C.c_int, [P, P, P, P, i32, i32, i32, F, F, i32, i32, P, u64, P]),
     "tt_debug_step_buffer": (C.c_int, [P]),
     "tt_debug_seq_mode": (C.c_int, [i32]),
+    "tt_debug_bwd_seq_mode": (C.c_int, [i32]),
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
 }
 

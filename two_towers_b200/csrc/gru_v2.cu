@@ -24,15 +24,24 @@ using namespace umma;
 typedef __half f16;
 
 // ------------------------------------------------------------------------------------------ small device helpers
-__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
-__device__ __forceinline__ float fast_tanh(float x) { return 1.f - __fdividef(2.f, 1.f + __expf(2.f * x)); }
+// MUFU-only transcendental paths (ex2.approx.ftz / rcp.approx.ftz: 2 ulp / 1 ulp, no denormal fix-up code):
+// sigmoid(x) = 1 / (1 + 2^(-x log2 e)),  tanh(x) = 1 - 2 / (1 + 2^(2 x log2 e));  saturate correctly at +-inf.
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float fast_sigmoid(float x) { return rcp_ftz(1.f + ex2_ftz(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float fast_tanh(float x) { return fmaf(-2.f, rcp_ftz(1.f + ex2_ftz(2.8853900817779268f * x)), 1.f); }
 
-// keep-mask scales of 4 consecutive logical elements e4*4 .. e4*4+3 (one Philox call; same stream as dropout_scale)
-__device__ __forceinline__ void dropout_scale4(uint64_t seed, uint64_t e4, float p, float inv_keep, float (&s)[4]) {
+// keep-mask scales of the 8 consecutive logical elements 8*e8 .. 8*e8+7: one Philox4x32-10 call, 16 random bits per
+// element (keep iff bits >= round(p * 65536)); forward (layer output) and backward (d_above) use the same function.
+__device__ __forceinline__ void dropout_scale8(uint64_t seed, uint64_t e8, float p, float inv_keep, float (&s)[8]) {
   uint32_t r[4];
-  philox4x32(seed, e4, r);
+  philox4x32(seed, e8, r);
+  const uint32_t thr = (uint32_t)__float2uint_rn(p * 65536.f);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) s[i] = ((float)(r[i] >> 8) * (1.0f / 16777216.0f)) >= p ? inv_keep : 0.f;
+  for (int i = 0; i < 4; ++i) {
+    s[2 * i] = (r[i] & 0xFFFFu) >= thr ? inv_keep : 0.f;
+    s[2 * i + 1] = (r[i] >> 16) >= thr ? inv_keep : 0.f;
+  }
 }
 
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
@@ -145,7 +154,9 @@ __global__ void fold_bias_kernel(const float* __restrict__ b_ih, const float* __
 // ------------------------------------------------------------------------------------------ K-C forward step
 unsigned long long* g_step_dbg = nullptr;
 static int g_seq_mode = 4;                    // 0: one launch per timestep; 2 / 4: persistent kernel, epilogue warps per quarter
-static int seq_mode() { return g_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
+static int seq_mode() { return g_seq_mode; }
+static int g_bwd_seq_mode = 1;                // 1: fused persistent BPTT kernel (H <= 256); 0: two launches per timestep
+static int bwd_seq_mode() { return g_bwd_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
 constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
 constexpr int S_A_BYTES = S_BM * S_BK * 2, S_B_BYTES = S_BN * S_BK * 2;
 constexpr int S_STAGE = 2 * S_A_BYTES + 2 * S_B_BYTES;   // 81920
@@ -358,11 +369,10 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
         if (p.has_next) {
           if (p.drop_p > 0.f && row_ok) {
             const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 8 * c);
-            float s0[4], s1[4];
-            dropout_scale4(p.seed, e >> 2, p.drop_p, p.inv_keep, s0);
-            dropout_scale4(p.seed, (e >> 2) + 1, p.drop_p, p.inv_keep, s1);
+            float s8[8];
+            dropout_scale8(p.seed, e >> 3, p.drop_p, p.inv_keep, s8);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { xo[j] *= s0[j]; xo[4 + j] *= s1[j]; }
+            for (int j = 0; j < 8; ++j) xo[j] *= s8[j];
           }
           split8(xo, hi, lo);
           *reinterpret_cast<uint4*>(stg + 32768 + off) = hi;
@@ -652,11 +662,10 @@ __global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid
             if (p.has_next) {
               if (p.drop_p > 0.f && row_ok) {
                 const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 8 * c);
-                float s0[4], s1[4];
-                dropout_scale4(p.seed, el >> 2, p.drop_p, p.inv_keep, s0);
-                dropout_scale4(p.seed, (el >> 2) + 1, p.drop_p, p.inv_keep, s1);
+                float s8[8];
+                dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) { xo[j] *= s0[j]; xo[4 + j] *= s1[j]; }
+                for (int j = 0; j < 8; ++j) xo[j] *= s8[j];
               }
               split8(xo, hi, lo);
               *reinterpret_cast<uint4*>(stg + 32768 + off) = hi;
@@ -755,9 +764,10 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
       float4 da = da4[i];
       if (dab && p.drop_p > 0.f) {
         const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 4 * i);
-        float s[4];
-        dropout_scale4(p.seed, e >> 2, p.drop_p, p.inv_keep, s);
-        da.x *= s[0]; da.y *= s[1]; da.z *= s[2]; da.w *= s[3];
+        float s8[8];
+        dropout_scale8(p.seed, e >> 3, p.drop_p, p.inv_keep, s8);
+        const int o8 = (i & 1) * 4;
+        da.x *= s8[o8]; da.y *= s8[o8 + 1]; da.z *= s8[o8 + 2]; da.w *= s8[o8 + 3];
       }
       const float dh[4] = {dh4[i].x + da.x, dh4[i].y + da.y, dh4[i].z + da.z, dh4[i].w + da.w};
       const float hnv[4] = {hn4[i].x, hn4[i].y, hn4[i].z, hn4[i].w};
@@ -798,6 +808,312 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
     bulk_commit();
     bulk_wait_read0();
   }
+}
+
+// ------------------------------------------------------------------------------------------ K-C' persistent BPTT
+// One launch runs the whole reverse-time recurrence of one layer.  A CTA owns ALL hidden units of one
+// (128-row batch tile, direction), so consecutive steps only depend on the CTA itself: no inter-CTA traffic at all.
+// The running gradient dL/dh lives in TENSOR MEMORY for the entire sequence: two 256-column buffers alternate,
+//   buf[cur] = dL/dh_t  ->  pass 1: dht = buf[cur] (+ d_above[t]);  buf[cur] <- dht;  buf[nxt] <- dht * z_t
+//                           pass 2: per 64-unit chunk, gate gradients (dr, dz, dn*r, dn) -> fp16 swizzled smem tiles
+//                                   -> (a) TMA store to the dG planes (wgrad / dX GEMMs later), (b) A operand of
+//                                   buf[nxt] += dGH_chunk W_hh[chunk rows]   (tcgen05, single fp16 pass, W_hh streamed
+//                                   from L2 through a TMA ring; the operand never touches HBM on its way to the MMA)
+// so after the 12 k-blocks buf[nxt] = dL/dh_{t-1} and the roles of the buffers swap.
+constexpr int R_WSTAGE = 64 * 256 * 2;             // one k-block of W_hh: [64 k][256 n] fp16 = 32 KB
+constexpr int R_WSTAGES = 3;
+constexpr int R_STG = 4 * 16384;                   // one staging buffer: tiles dr | dz | dn*r | dn, [128][64] fp16 each
+constexpr int R_SMEM = R_WSTAGES * R_WSTAGE + 2 * R_STG + 1024 + 512;
+constexpr int R_THREADS = 64 + 512;
+
+struct alignas(64) BwdSeqParams {
+  CUtensorMap dg[2];                 // store maps over the dG planes [T*Bp][4H], box 64 x 128
+  CUtensorMap w[2];                  // load maps over W_hh hi planes [3H][H], box 64 x 64
+  const uint4* g16;
+  const float* hn;
+  const float* dhs0;                 // tiled initial dL/dh [ndir][MT][H/4][128][4] (scaled)
+  const float* d_above;              // tiled [T][MT][ndir*H/4][128][4] (scaled) or null
+  const int32_t* lengths;
+  int32_t B, Bp, T, H, ndir, tiles;
+  float drop_p, inv_keep;
+  uint64_t seed;
+};
+
+__device__ __forceinline__ void tmem_ld16v(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n" ::"r"(taddr),
+      "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+      "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+      "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+      "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+
+// requires H in {64, 128, 256} (one <=256-column accumulator holds every hidden unit of the tile)
+__global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_constant__ BwdSeqParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* wring = smem;
+  uint8_t* stg = smem + R_WSTAGES * R_WSTAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + 2 * R_STG);
+  uint64_t* wfull = bars;                 // [3]
+  uint64_t* wempty = bars + 3;            // [3]
+  uint64_t* sfull = bars + 6;             // [2] staging written (cell threads -> MMA)
+  uint64_t* sempty = bars + 8;            // [2] staging consumed (MMA commit -> cell threads)
+  uint64_t* init_done = bars + 10;        // buf[nxt] holds dht * z
+  uint64_t* acc_full = bars + 11;         // all MMAs of the step complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int H = p.H, T = p.T, MT = p.Bp >> 7, h4 = H >> 2;
+  const int NCHUNK = H >> 6;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < R_WSTAGES; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 1); mbar_init(&sempty[i], 1); }
+    mbar_init(init_done, 1);
+    mbar_init(acc_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  int ntiles_mine = 0;
+  for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) ++ntiles_mine;
+
+  if (warp == 0) {
+    // ================================================================= W_hh producer (same 12 k-blocks every step)
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        const int dir = tile / MT;
+        for (int step = 0; step < T; ++step)
+          for (int c = 0; c < NCHUNK; ++c)
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wempty[stage], phase ^ 1);
+              uint8_t* sb = wring + stage * R_WSTAGE;
+              mbar_arrive_expect_tx(&wfull[stage], 64 * H * 2);
+              for (int hh = 0; hh < NCHUNK; ++hh) tma_load_2d(&p.w[dir], &wfull[stage], sb + hh * 8192, hh * 64, g * H + c * 64);
+              if (++stage == R_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_f16(128, H, 0, 1);
+      int stage = 0, phase = 0, it = 0, use = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        for (int step = 0; step < T; ++step, ++it) {
+          const uint32_t d_tmem = tmem_base + ((it & 1) ^ 1) * 256;        // buf[nxt]
+          mbar_wait(init_done, it & 1);
+          tc_fence_after();
+          for (int c = 0; c < NCHUNK; ++c, ++use) {
+            const int sb = use & 1;
+            mbar_wait(&sfull[sb], (use >> 1) & 1);
+            tc_fence_after();
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wfull[stage], phase);
+              tc_fence_after();
+              const uint32_t sa = smem_u32(stg + sb * R_STG + g * 16384), sw = smem_u32(wring + stage * R_WSTAGE);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                mma_bf16_ss(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sw + k * 2048, 8192, 1024), idesc, 1u);
+              mma_commit(&wempty[stage]);
+              if (++stage == R_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+            mma_commit(&sempty[sb]);
+          }
+          mma_commit(acc_full);
+        }
+      }
+    }
+  } else {
+    // ================================================================= gate gradients: thread = (batch row, 16 units per chunk)
+    const int e = threadIdx.x - 64;
+    const int quarter = warp & 3, sub = (warp - 2) >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    int it = 0, use = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+      const int mt = tile % MT, dir = tile / MT, m0 = mt * 128, b = m0 + row;
+      const bool row_ok = b < p.B;
+      // ---- dL/dh at the end of the sequence -> buf[cur of this tile's first step]
+      if (it > 0) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+      {
+        const float4* src = reinterpret_cast<const float4*>(p.dhs0) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll 1
+        for (int c = 0; c < NCHUNK; ++c) {
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = __ldg(src + (int64_t)(16 * c + 4 * sub + i) * 128);
+            v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+          }
+          tmem_st16(lane_base + (it & 1) * 256 + 64 * c + 16 * sub, v);
+        }
+        tmem_wait_st();
+      }
+      for (int step = T - 1; step >= 0; --step, ++it) {
+        const int t = dir == 0 ? step : T - 1 - step;
+        const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
+        const uint32_t cur = lane_base + (it & 1) * 256, nxt = lane_base + ((it & 1) ^ 1) * 256;
+        const int64_t gtile = (((int64_t)dir * T + t) * MT + mt) * h4;                       // float4 / record index base
+        // pull the NEXT step's gate records (and d_above rows) of this thread into L2 while this step computes: the
+        // per-chunk loads below then see L2 latency instead of HBM latency (the kernel is latency-, not bandwidth-bound)
+        if (step > 0 && row_ok) {
+          const int tn = dir == 0 ? step - 1 : T - step;
+          const int64_t gn = (((int64_t)dir * T + tn) * MT + mt) * h4;
+#pragma unroll 1
+          for (int c = 0; c < NCHUNK; ++c) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int64_t rec = (gn + 16 * c + 4 * sub + i) * 128 + row;
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(p.g16 + rec * 2));
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float4*>(p.hn) + rec));
+              if (p.d_above)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float4*>(p.d_above) +
+                                                              (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 16 * c + 4 * sub + i) * 128 + row));
+            }
+          }
+        }
+        if (step != T - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+        // ---------------- pass 1: dht = dh (+ d_above); buf[cur] <- dht; buf[nxt] <- dht * z
+#pragma unroll 1
+        for (int c = 0; c < NCHUNK; ++c) {
+          const int u4 = 16 * c + 4 * sub;                                                  // first 4-unit group of this thread
+          float dh[16], dz_[16];
+          tmem_ld16v(cur + 64 * c + 16 * sub, dh);
+          // (tcgen05.ld / .st are warp-collective: every lane executes them; only the VALUES depend on `live`)
+          uint4 ga[4];
+          if (live) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ga[i] = __ldg(p.g16 + ((gtile + u4 + i) * 128 + row) * 2);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ga[i] = make_uint4(0u, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);      // z = 1: gradient passes through
+          }
+          if (p.d_above) {
+            if (live) {
+              const float4* dab = reinterpret_cast<const float4*>(p.d_above) +
+                                  (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + u4) * 128 + row;
+              float4 da[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) da[i] = __ldg(dab + (int64_t)i * 128);
+              if (p.drop_p > 0.f) {
+                const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 4 * u4);
+                float s8[8];
+                dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+                da[0].x *= s8[0]; da[0].y *= s8[1]; da[0].z *= s8[2]; da[0].w *= s8[3];
+                da[1].x *= s8[4]; da[1].y *= s8[5]; da[1].z *= s8[6]; da[1].w *= s8[7];
+                dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+                da[2].x *= s8[0]; da[2].y *= s8[1]; da[2].z *= s8[2]; da[2].w *= s8[3];
+                da[3].x *= s8[4]; da[3].y *= s8[5]; da[3].z *= s8[6]; da[3].w *= s8[7];
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i) { dh[4 * i] += da[i].x; dh[4 * i + 1] += da[i].y; dh[4 * i + 2] += da[i].z; dh[4 * i + 3] += da[i].w; }
+            }
+            tmem_st16(cur + 64 * c + 16 * sub, dh);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            dz_[4 * i] = dh[4 * i] * dq_u16(ga[i].z);
+            dz_[4 * i + 1] = dh[4 * i + 1] * dq_u16(ga[i].z >> 16);
+            dz_[4 * i + 2] = dh[4 * i + 2] * dq_u16(ga[i].w);
+            dz_[4 * i + 3] = dh[4 * i + 3] * dq_u16(ga[i].w >> 16);
+          }
+          tmem_st16(nxt + 64 * c + 16 * sub, dz_);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        named_bar_sync(1, 512);
+        if (e == 0) mbar_arrive(init_done);
+        // ---------------- pass 2: gate gradients of 64-unit chunks -> staging tiles -> MMA operand + dG planes
+#pragma unroll 1
+        for (int c = 0; c < NCHUNK; ++c, ++use) {
+          const int sb = use & 1, u4 = 16 * c + 4 * sub;
+          uint4 ga[4], gb[4];
+          float4 hn4[4];
+          if (live) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int64_t rec = (gtile + u4 + i) * 128 + row;
+              ga[i] = __ldg(p.g16 + rec * 2);
+              gb[i] = __ldg(p.g16 + rec * 2 + 1);
+              hn4[i] = __ldg(reinterpret_cast<const float4*>(p.hn) + rec);
+            }
+          }
+          float dh[16];
+          tmem_ld16v(cur + 64 * c + 16 * sub, dh);
+          if (e == 0 && use >= 2) {                              // staging buffer free: MMAs and the TMA store of its last use are done
+            mbar_wait(&sempty[sb], ((use >> 1) - 1) & 1);
+            bulk_wait_read1();
+          }
+          named_bar_sync(2, 512);
+          uint8_t* sbuf = stg + sb * R_STG;
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            float dr[8], dzv[8], dnr[8], dn[8];
+#pragma unroll
+            for (int g2 = 0; g2 < 2; ++g2) {
+              const int i = 2 * cc + g2, o = 4 * g2;
+              if (live) {
+                const float hnv[4] = {hn4[i].x, hn4[i].y, hn4[i].z, hn4[i].w};
+                const uint32_t rw[2] = {ga[i].x, ga[i].y}, zw[2] = {ga[i].z, ga[i].w}, nw[2] = {gb[i].x, gb[i].y}, qw[2] = {gb[i].z, gb[i].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const int sh = (j & 1) * 16;
+                  const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw[j >> 1] >> sh);
+                  const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);
+                  const float d = dh[4 * i + j];
+                  const float dn_pre = d * (1.f - z) * (1.f - n * n);
+                  dn[o + j] = dn_pre;
+                  dnr[o + j] = dn_pre * r;
+                  dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);
+                  dzv[o + j] = d * q * (1.f - z);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { dr[o + j] = 0.f; dzv[o + j] = 0.f; dnr[o + j] = 0.f; dn[o + j] = 0.f; }
+              }
+            }
+            const uint32_t off = sw128_off(row, 2 * sub + cc);
+            *reinterpret_cast<uint4*>(sbuf + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7]));
+            *reinterpret_cast<uint4*>(sbuf + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7]));
+            *reinterpret_cast<uint4*>(sbuf + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7]));
+            *reinterpret_cast<uint4*>(sbuf + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7]));
+          }
+          fence_proxy_async();
+          named_bar_sync(3, 512);
+          if (e == 0) {
+            mbar_arrive(&sfull[sb]);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) tma_store_2d(&p.dg[dir], sbuf + g * 16384, g * H + 64 * c, t * p.Bp + m0);
+            bulk_commit();
+          }
+        }
+      }
+    }
+    if (e == 0) bulk_wait_read0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
 // ------------------------------------------------------------------------------------------ backward helpers
@@ -1169,6 +1485,26 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }
     r.M = Bp; r.N = H; r.K = 3 * H; r.nbatch = nd; r.a_mn = false; r.b_mn = true; r.alpha = 1.f; r.beta = 1.f; r.splitk = 1;
     r.f16 = 1; r.npass = 1; r.a_rows = d.ntok; r.epi = 1; r.tl_Bp = Bp; r.tl_G = 1; r.tl_Hc = H;
+    if (H <= 256 && bwd_seq_mode() != 0) {
+      // fused persistent BPTT: dL/dh stays in tensor memory for the whole sequence
+      static bool battr = false;
+      if (!battr) { TT_CUDA(cudaFuncSetAttribute(gru_bwd_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM)); battr = true; }
+      static int num_sms = 0;
+      if (!num_sms) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev)); }
+      BwdSeqParams bp;
+      memset(&bp, 0, sizeof(bp));
+      for (int dd = 0; dd < nd; ++dd) {
+        bp.dg[dd] = cp.dg[dd];
+        TT_TRY(make_plane_map(&bp.w[dd], f.whh_hi[dd], 3 * H, H, H, 64, 1));
+      }
+      bp.g16 = sv.g16[l]; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
+      bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
+      bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed;
+      const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
+      note_launch();
+      gru_bwd_seq_kernel<<<grid, R_THREADS, R_SMEM, s>>>(bp);
+      TT_LAUNCH_CHECK();
+    } else {
     UmmaPrepared prep;
     TT_TRY(umma_gemm_prepare(r, &prep));
     dim3 cgrid((unsigned)(H / 64), (unsigned)MT, (unsigned)nd);
@@ -1181,6 +1517,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       TT_TRY(umma_gemm_launch(prep, row0, s));
     }
     TT_LAUNCH_CHECK();
+    }
 
     float* d_below = nullptr;                            // tiled dX for the layer below
     for (int dd = 0; dd < nd; ++dd) {
@@ -1234,6 +1571,10 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
 extern "C" int tt_debug_seq_mode(int32_t mode) {
   if (mode != 0 && mode != 2 && mode != 4) { tt::set_error("tt_debug_seq_mode: 0, 2 or 4"); return TT_ERR_INVALID; }
   tt::g_seq_mode = mode;
+  return TT_OK;
+}
+extern "C" int tt_debug_bwd_seq_mode(int32_t mode) {
+  tt::g_bwd_seq_mode = mode ? 1 : 0;
   return TT_OK;
 }
 
