@@ -824,7 +824,7 @@ constexpr int R_WSTAGE = 64 * 256 * 2;             // one k-block of W_hh: [64 k
 constexpr int R_WSTAGES = 3;
 constexpr int R_STG = 4 * 16384;                   // one staging buffer: tiles dr | dz | dn*r | dn, [128][64] fp16 each
 constexpr int R_SMEM = R_WSTAGES * R_WSTAGE + 2 * R_STG + 1024 + 512;
-constexpr int R_THREADS = 64 + 512;
+constexpr int R_THREADS = 64 + 512 + 32;          // TMA producer, MMA issuer, 16 gate-gradient warps, dG writer
 
 struct alignas(64) BwdSeqParams {
   CUtensorMap dg[2];                 // store maps over the dG planes [T*Bp][4H], box 64 x 128
@@ -837,7 +837,12 @@ struct alignas(64) BwdSeqParams {
   int32_t B, Bp, T, H, ndir, tiles;
   float drop_p, inv_keep;
   uint64_t seed;
+  unsigned long long* dbg;
 };
+#define BWD_MARK(itv, slot)                                                              \
+  do {                                                                                   \
+    if (p.dbg && blockIdx.x == 0 && (itv) < 64) p.dbg[(itv) * 16 + (slot)] = gtimer(); \
+  } while (0)
 
 __device__ __forceinline__ void tmem_ld16v(uint32_t taddr, float (&v)[16]) {
   uint32_t r[16];
@@ -863,7 +868,11 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) 
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 
-// requires H in {64, 128, 256} (one <=256-column accumulator holds every hidden unit of the tile)
+// requires H in {64, 128, 256} (one <=256-column accumulator holds every hidden unit of the tile); NCH = H / 64.
+// The gate-gradient threads are latency-bound on the saved-gate records, so every global load is issued one
+// pipeline stage ahead of its use: all z words of a step before the accumulator wait, d_above one chunk ahead,
+// the (r,z,n,q,hn) records one half-chunk (8 units) ahead - across the chunk barriers.
+template <int NCH, bool HAS_DAB>
 __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_constant__ BwdSeqParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -876,14 +885,15 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
   uint64_t* sempty = bars + 8;            // [2] staging consumed (MMA commit -> cell threads)
   uint64_t* init_done = bars + 10;        // buf[nxt] holds dht * z
   uint64_t* acc_full = bars + 11;         // all MMAs of the step complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* sstored = bars + 12;          // [2] TMA store has read the staging buffer (store warp -> cell threads)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int H = p.H, T = p.T, MT = p.Bp >> 7, h4 = H >> 2;
-  const int NCHUNK = H >> 6;
+  constexpr int H = 64 * NCH, h4 = H >> 2;
+  const int T = p.T, MT = p.Bp >> 7;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < R_WSTAGES; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 1); mbar_init(&sempty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 1); mbar_init(&sempty[i], 1); mbar_init(&sstored[i], 1); }
     mbar_init(init_done, 1);
     mbar_init(acc_full, 1);
     fence_barrier_init();
@@ -893,22 +903,21 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  int ntiles_mine = 0;
-  for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) ++ntiles_mine;
 
   if (warp == 0) {
-    // ================================================================= W_hh producer (same 12 k-blocks every step)
+    // ================================================================= W_hh producer (same 3*NCH k-blocks every step)
     if (lane == 0) {
       int stage = 0, phase = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
         const int dir = tile / MT;
         for (int step = 0; step < T; ++step)
-          for (int c = 0; c < NCHUNK; ++c)
+          for (int c = 0; c < NCH; ++c)
             for (int g = 0; g < 3; ++g) {
               mbar_wait(&wempty[stage], phase ^ 1);
               uint8_t* sb = wring + stage * R_WSTAGE;
               mbar_arrive_expect_tx(&wfull[stage], 64 * H * 2);
-              for (int hh = 0; hh < NCHUNK; ++hh) tma_load_2d(&p.w[dir], &wfull[stage], sb + hh * 8192, hh * 64, g * H + c * 64);
+#pragma unroll
+              for (int hh = 0; hh < NCH; ++hh) tma_load_2d(&p.w[dir], &wfull[stage], sb + hh * 8192, hh * 64, g * H + c * 64);
               if (++stage == R_WSTAGES) { stage = 0; phase ^= 1; }
             }
       }
@@ -916,14 +925,14 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
   } else if (warp == 1) {
     // ================================================================= MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_f16(128, H, 0, 1);
+      constexpr uint32_t idesc = make_idesc_f16(128, H, 0, 1);
       int stage = 0, phase = 0, it = 0, use = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
         for (int step = 0; step < T; ++step, ++it) {
           const uint32_t d_tmem = tmem_base + ((it & 1) ^ 1) * 256;        // buf[nxt]
           mbar_wait(init_done, it & 1);
           tc_fence_after();
-          for (int c = 0; c < NCHUNK; ++c, ++use) {
+          for (int c = 0; c < NCH; ++c, ++use) {
             const int sb = use & 1;
             mbar_wait(&sfull[sb], (use >> 1) & 1);
             tc_fence_after();
@@ -940,6 +949,28 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             mma_commit(&sempty[sb]);
           }
           mma_commit(acc_full);
+          BWD_MARK(it, 15);
+        }
+      }
+    }
+  } else if (warp == 18) {
+    // ================================================================= dG plane writer (off the cell threads' critical path)
+    if (lane == 0) {
+      int use = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        const int mt = tile % MT, dir = tile / MT, m0 = mt * 128;
+        for (int step = T - 1; step >= 0; --step) {
+          const int t = dir == 0 ? step : T - 1 - step;
+          for (int c = 0; c < NCH; ++c, ++use) {
+            const int sb = use & 1;
+            mbar_wait(&sfull[sb], (use >> 1) & 1);
+            const uint8_t* sbuf = stg + sb * R_STG;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) tma_store_2d(&p.dg[dir], sbuf + g * 16384, g * H + 64 * c, t * p.Bp + m0);
+            bulk_commit();
+            bulk_wait_read0();
+            mbar_arrive(&sstored[sb]);
+          }
         }
       }
     }
@@ -957,8 +988,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
       if (it > 0) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
       {
         const float4* src = reinterpret_cast<const float4*>(p.dhs0) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
-#pragma unroll 1
-        for (int c = 0; c < NCHUNK; ++c) {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
           float v[16];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
@@ -970,146 +1001,140 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         tmem_wait_st();
       }
       for (int step = T - 1; step >= 0; --step, ++it) {
+        if (e == 0) BWD_MARK(it, 14);
         const int t = dir == 0 ? step : T - 1 - step;
         const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
         const uint32_t cur = lane_base + (it & 1) * 256, nxt = lane_base + ((it & 1) ^ 1) * 256;
-        const int64_t gtile = (((int64_t)dir * T + t) * MT + mt) * h4;                       // float4 / record index base
-        // pull the NEXT step's gate records (and d_above rows) of this thread into L2 while this step computes: the
-        // per-chunk loads below then see L2 latency instead of HBM latency (the kernel is latency-, not bandwidth-bound)
-        if (step > 0 && row_ok) {
-          const int tn = dir == 0 ? step - 1 : T - step;
-          const int64_t gn = (((int64_t)dir * T + tn) * MT + mt) * h4;
-#pragma unroll 1
-          for (int c = 0; c < NCHUNK; ++c) {
+        // record (4-unit group) index of this thread's first group; group (c, i) is at rec0 + (16 c + i) * 128
+        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * h4 + 4 * sub) * 128 + row;
+        const float4* dab0 = HAS_DAB ? reinterpret_cast<const float4*>(p.d_above) +
+                                           (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 4 * sub) * 128 + row
+                                     : nullptr;
+        // ---------------- all z words of the step: in flight while the previous step's MMAs finish
+        uint2 zw[NCH * 4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int64_t rec = (gn + 16 * c + 4 * sub + i) * 128 + row;
-              asm volatile("prefetch.global.L2 [%0];" ::"l"(p.g16 + rec * 2));
-              asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float4*>(p.hn) + rec));
-              if (p.d_above)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float4*>(p.d_above) +
-                                                              (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 16 * c + 4 * sub + i) * 128 + row));
-            }
-          }
+        for (int g = 0; g < NCH * 4; ++g)
+          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + (rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) * 2) + 1)
+                       : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);                             // z = 1: gradient passes through
+        float4 da[2][4];
+        if (HAS_DAB) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) da[0][i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        if (e == 0) BWD_MARK(it, 0);
         if (step != T - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+        if (e == 0) BWD_MARK(it, 1);
         // ---------------- pass 1: dht = dh (+ d_above); buf[cur] <- dht; buf[nxt] <- dht * z
-#pragma unroll 1
-        for (int c = 0; c < NCHUNK; ++c) {
-          const int u4 = 16 * c + 4 * sub;                                                  // first 4-unit group of this thread
-          float dh[16], dz_[16];
+        // (tcgen05.ld / .st are warp-collective: every lane executes them; only the VALUES depend on `live`)
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float dh[16];
           tmem_ld16v(cur + 64 * c + 16 * sub, dh);
-          // (tcgen05.ld / .st are warp-collective: every lane executes them; only the VALUES depend on `live`)
-          uint4 ga[4];
-          if (live) {
+          if (HAS_DAB) {
+            if (c + 1 < NCH) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) ga[i] = __ldg(p.g16 + ((gtile + u4 + i) * 128 + row) * 2);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) ga[i] = make_uint4(0u, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);      // z = 1: gradient passes through
-          }
-          if (p.d_above) {
-            if (live) {
-              const float4* dab = reinterpret_cast<const float4*>(p.d_above) +
-                                  (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + u4) * 128 + row;
-              float4 da[4];
-#pragma unroll
-              for (int i = 0; i < 4; ++i) da[i] = __ldg(dab + (int64_t)i * 128);
-              if (p.drop_p > 0.f) {
-                const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 4 * u4);
-                float s8[8];
-                dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
-                da[0].x *= s8[0]; da[0].y *= s8[1]; da[0].z *= s8[2]; da[0].w *= s8[3];
-                da[1].x *= s8[4]; da[1].y *= s8[5]; da[1].z *= s8[6]; da[1].w *= s8[7];
-                dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
-                da[2].x *= s8[0]; da[2].y *= s8[1]; da[2].z *= s8[2]; da[2].w *= s8[3];
-                da[3].x *= s8[4]; da[3].y *= s8[5]; da[3].z *= s8[6]; da[3].w *= s8[7];
-              }
-#pragma unroll
-              for (int i = 0; i < 4; ++i) { dh[4 * i] += da[i].x; dh[4 * i + 1] += da[i].y; dh[4 * i + 2] += da[i].z; dh[4 * i + 3] += da[i].w; }
+              for (int i = 0; i < 4; ++i)
+                da[(c + 1) & 1][i] = live ? __ldg(dab0 + (int64_t)(16 * (c + 1) + i) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
+            float4* d4 = da[c & 1];
+            if (p.drop_p > 0.f && live) {
+              const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * c + 16 * sub);
+              float s8[8];
+              dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+              d4[0].x *= s8[0]; d4[0].y *= s8[1]; d4[0].z *= s8[2]; d4[0].w *= s8[3];
+              d4[1].x *= s8[4]; d4[1].y *= s8[5]; d4[1].z *= s8[6]; d4[1].w *= s8[7];
+              dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+              d4[2].x *= s8[0]; d4[2].y *= s8[1]; d4[2].z *= s8[2]; d4[2].w *= s8[3];
+              d4[3].x *= s8[4]; d4[3].y *= s8[5]; d4[3].z *= s8[6]; d4[3].w *= s8[7];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { dh[4 * i] += d4[i].x; dh[4 * i + 1] += d4[i].y; dh[4 * i + 2] += d4[i].z; dh[4 * i + 3] += d4[i].w; }
             tmem_st16(cur + 64 * c + 16 * sub, dh);
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            dz_[4 * i] = dh[4 * i] * dq_u16(ga[i].z);
-            dz_[4 * i + 1] = dh[4 * i + 1] * dq_u16(ga[i].z >> 16);
-            dz_[4 * i + 2] = dh[4 * i + 2] * dq_u16(ga[i].w);
-            dz_[4 * i + 3] = dh[4 * i + 3] * dq_u16(ga[i].w >> 16);
+            const uint2 z2 = zw[4 * c + i];
+            dh[4 * i] *= dq_u16(z2.x);
+            dh[4 * i + 1] *= dq_u16(z2.x >> 16);
+            dh[4 * i + 2] *= dq_u16(z2.y);
+            dh[4 * i + 3] *= dq_u16(z2.y >> 16);
           }
-          tmem_st16(nxt + 64 * c + 16 * sub, dz_);
+          tmem_st16(nxt + 64 * c + 16 * sub, dh);
         }
+        // first half-chunk of gate records for pass 2 (in flight across the barrier)
+        uint4 ga0[2], gb0[2], ga1[2], gb1[2];
+        float4 hn0[2], hn1[2];
+#define TT_LOAD_HALF(GA, GB, HN, HCV)                                                                          \
+  _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                              \
+    const int64_t rec = rec0 + (int64_t)(((HCV) >> 1) * 16 + ((HCV) & 1) * 2 + i) * 128;                       \
+    GA[i] = live ? __ldg(p.g16 + rec * 2) : make_uint4(0u, 0u, 0u, 0u);                                        \
+    GB[i] = live ? __ldg(p.g16 + rec * 2 + 1) : make_uint4(0u, 0u, 0u, 0u);                                    \
+    HN[i] = live ? __ldg(reinterpret_cast<const float4*>(p.hn) + rec) : make_float4(0.f, 0.f, 0.f, 0.f);       \
+  }
+#define TT_GRAD_HALF(GA, GB, HN, CV, CCV, SBUF)                                                                \
+  {                                                                                                            \
+    float dh[8];                                                                                               \
+    tmem_ld8(cur + 64 * (CV) + 16 * sub + 8 * (CCV), dh);                                                      \
+    tmem_wait_ld();                                                                                            \
+    float dr[8], dzv[8], dnr[8], dn[8];                                                                        \
+    _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                            \
+      const int o = 4 * i;                                                                                     \
+      const float hnv[4] = {HN[i].x, HN[i].y, HN[i].z, HN[i].w};                                               \
+      const uint32_t rw[2] = {GA[i].x, GA[i].y}, zw2[2] = {GA[i].z, GA[i].w};                                  \
+      const uint32_t nw[2] = {GB[i].x, GB[i].y}, qw[2] = {GB[i].z, GB[i].w};                                   \
+      _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                          \
+        const int sh = (j & 1) * 16;                                                                           \
+        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw2[j >> 1] >> sh);                               \
+        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);  \
+        const float d = live ? dh[o + j] : 0.f;                                                                \
+        const float dn_pre = d * (1.f - z) * (1.f - n * n);                                                    \
+        dn[o + j] = dn_pre;                                                                                    \
+        dnr[o + j] = dn_pre * r;                                                                               \
+        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);                                                           \
+        dzv[o + j] = d * q * (1.f - z); /* == dh (h_prev - n) z (1 - z), q = h_t - n = z (h_prev - n) */       \
+      }                                                                                                        \
+    }                                                                                                          \
+    const uint32_t off = sw128_off(row, 2 * sub + (CCV));                                                      \
+    *reinterpret_cast<uint4*>(SBUF + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7])); \
+  }
+        TT_LOAD_HALF(ga0, gb0, hn0, 0)
         tmem_wait_st();
         tc_fence_before();
         named_bar_sync(1, 512);
         if (e == 0) mbar_arrive(init_done);
-        // ---------------- pass 2: gate gradients of 64-unit chunks -> staging tiles -> MMA operand + dG planes
+        if (e == 0) BWD_MARK(it, 2);
+        // ---------------- pass 2: gate gradients, half-chunk (8 units) at a time, loads one half-chunk ahead.
+        // NOT unrolled over chunks: the loop body must stay inside the instruction cache (the unrolled version spent
+        // ~6 us per timestep refetching 65 KB of straight-line code)
 #pragma unroll 1
-        for (int c = 0; c < NCHUNK; ++c, ++use) {
-          const int sb = use & 1, u4 = 16 * c + 4 * sub;
-          uint4 ga[4], gb[4];
-          float4 hn4[4];
-          if (live) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int64_t rec = (gtile + u4 + i) * 128 + row;
-              ga[i] = __ldg(p.g16 + rec * 2);
-              gb[i] = __ldg(p.g16 + rec * 2 + 1);
-              hn4[i] = __ldg(reinterpret_cast<const float4*>(p.hn) + rec);
-            }
-          }
-          float dh[16];
-          tmem_ld16v(cur + 64 * c + 16 * sub, dh);
-          if (e == 0 && use >= 2) {                              // staging buffer free: MMAs and the TMA store of its last use are done
-            mbar_wait(&sempty[sb], ((use >> 1) - 1) & 1);
-            bulk_wait_read1();
+        for (int c = 0; c < NCH; ++c) {
+          const int sb = (use + c) & 1;
+          uint8_t* sbuf = stg + sb * R_STG;
+          TT_LOAD_HALF(ga1, gb1, hn1, 2 * c + 1)
+          if (e == 0 && use + c >= 2) {                          // staging buffer free: MMAs and the TMA store of its last use are done
+            mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);
+            mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1);
           }
           named_bar_sync(2, 512);
-          uint8_t* sbuf = stg + sb * R_STG;
-#pragma unroll
-          for (int cc = 0; cc < 2; ++cc) {
-            float dr[8], dzv[8], dnr[8], dn[8];
-#pragma unroll
-            for (int g2 = 0; g2 < 2; ++g2) {
-              const int i = 2 * cc + g2, o = 4 * g2;
-              if (live) {
-                const float hnv[4] = {hn4[i].x, hn4[i].y, hn4[i].z, hn4[i].w};
-                const uint32_t rw[2] = {ga[i].x, ga[i].y}, zw[2] = {ga[i].z, ga[i].w}, nw[2] = {gb[i].x, gb[i].y}, qw[2] = {gb[i].z, gb[i].w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const int sh = (j & 1) * 16;
-                  const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw[j >> 1] >> sh);
-                  const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);
-                  const float d = dh[4 * i + j];
-                  const float dn_pre = d * (1.f - z) * (1.f - n * n);
-                  dn[o + j] = dn_pre;
-                  dnr[o + j] = dn_pre * r;
-                  dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);
-                  dzv[o + j] = d * q * (1.f - z);
-                }
-              } else {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) { dr[o + j] = 0.f; dzv[o + j] = 0.f; dnr[o + j] = 0.f; dn[o + j] = 0.f; }
-              }
-            }
-            const uint32_t off = sw128_off(row, 2 * sub + cc);
-            *reinterpret_cast<uint4*>(sbuf + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7]));
-            *reinterpret_cast<uint4*>(sbuf + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7]));
-            *reinterpret_cast<uint4*>(sbuf + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7]));
-            *reinterpret_cast<uint4*>(sbuf + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7]));
-          }
+          if (e == 0) BWD_MARK(it, 3 + 3 * c);
+          TT_GRAD_HALF(ga0, gb0, hn0, c, 0, sbuf)
+          if (c + 1 < NCH) { TT_LOAD_HALF(ga0, gb0, hn0, 2 * c + 2) }
+          TT_GRAD_HALF(ga1, gb1, hn1, c, 1, sbuf)
           fence_proxy_async();
           named_bar_sync(3, 512);
           if (e == 0) {
+            BWD_MARK(it, 4 + 3 * c);
             mbar_arrive(&sfull[sb]);
-#pragma unroll
-            for (int g = 0; g < 4; ++g) tma_store_2d(&p.dg[dir], sbuf + g * 16384, g * H + 64 * c, t * p.Bp + m0);
-            bulk_commit();
           }
         }
+#undef TT_LOAD_HALF
+#undef TT_GRAD_HALF
+        use += NCH;
       }
     }
-    if (e == 0) bulk_wait_read0();
   }
   tc_fence_before();
   __syncthreads();
@@ -1485,10 +1510,8 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }
     r.M = Bp; r.N = H; r.K = 3 * H; r.nbatch = nd; r.a_mn = false; r.b_mn = true; r.alpha = 1.f; r.beta = 1.f; r.splitk = 1;
     r.f16 = 1; r.npass = 1; r.a_rows = d.ntok; r.epi = 1; r.tl_Bp = Bp; r.tl_G = 1; r.tl_Hc = H;
-    if (H <= 256 && bwd_seq_mode() != 0) {
+    if ((H == 64 || H == 128 || H == 256) && bwd_seq_mode() != 0) {
       // fused persistent BPTT: dL/dh stays in tensor memory for the whole sequence
-      static bool battr = false;
-      if (!battr) { TT_CUDA(cudaFuncSetAttribute(gru_bwd_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM)); battr = true; }
       static int num_sms = 0;
       if (!num_sms) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev)); }
       BwdSeqParams bp;
@@ -1499,10 +1522,23 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       }
       bp.g16 = sv.g16[l]; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
       bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
-      bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed;
+      bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
       note_launch();
-      gru_bwd_seq_kernel<<<grid, R_THREADS, R_SMEM, s>>>(bp);
+#define TT_BWD_SEQ(NCHV, DABV)                                                                                        \
+  do {                                                                                                                \
+    static bool attr = false;                                                                                         \
+    if (!attr) {                                                                                                      \
+      TT_CUDA(cudaFuncSetAttribute(gru_bwd_seq_kernel<NCHV, DABV>, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM)); \
+      attr = true;                                                                                                    \
+    }                                                                                                                 \
+    gru_bwd_seq_kernel<NCHV, DABV><<<grid, R_THREADS, R_SMEM, s>>>(bp);                                               \
+  } while (0)
+      const bool dab = d_above != nullptr;
+      if (H == 256) { if (dab) TT_BWD_SEQ(4, true); else TT_BWD_SEQ(4, false); }
+      else if (H == 128) { if (dab) TT_BWD_SEQ(2, true); else TT_BWD_SEQ(2, false); }
+      else { if (dab) TT_BWD_SEQ(1, true); else TT_BWD_SEQ(1, false); }
+#undef TT_BWD_SEQ
       TT_LAUNCH_CHECK();
     } else {
     UmmaPrepared prep;
