@@ -38,6 +38,13 @@ const char* tt_engine(void);
 int tt_set_engine(int32_t mode);
 /* number of CUDA kernels this library has launched in this process (monotonic) */
 uint64_t tt_kernel_launches(void);
+/* CUDA-event timing of the dominant kernel families, recorded on each launch's own stream (off by default; measurement
+ * aid for bench.py's roofline object).  Families: 0 persistent forward recurrence, 1 persistent fused BPTT, 2 tcgen05
+ * GEMM engine.  tt_prof_enable(on) clears the totals; tt_prof_read waits for the recorded events and returns the summed
+ * device time and the number of launches since enable; tt_prof_family names a family (NULL past the last). */
+int tt_prof_enable(int32_t on);
+int tt_prof_read(int32_t family, double* total_ms, uint64_t* launches);
+const char* tt_prof_family(int32_t family);
 
 /* ---------------------------------------------------------------------------------------------
  * K-A  embedding gather.  Replaces the per-word CPU lookup `self.word2vec[word]` + zero padding

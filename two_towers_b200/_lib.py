@@ -81,6 +81,9 @@ SIGNATURES = {
     "tt_last_error": (C.c_char_p, []),
     "tt_engine": (C.c_char_p, []),
     "tt_kernel_launches": (u64, []),
+    "tt_prof_enable": (C.c_int, [i32]),
+    "tt_prof_read": (C.c_int, [i32, C.POINTER(C.c_double), C.POINTER(u64)]),
+    "tt_prof_family": (C.c_char_p, [i32]),
     "tt_set_engine": (C.c_int, [i32]),
     "tt_embed_gather": (C.c_int, [P, C.c_int, i64, P, i64, i32, i64, P, P]),
     "tt_gru_layer_fwd_workspace": (u64, [C.POINTER(GruLayer)]),

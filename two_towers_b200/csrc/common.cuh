@@ -10,6 +10,15 @@ namespace tt {
 void set_error(const char* fmt, ...);
 void note_launch();                 // counts kernel launches (bench.py reports them as gpu_launches)
 unsigned long long launches();
+// CUDA-event timing of a kernel family on its launch stream (off unless tt_prof_enable(1)): bench.py's roofline leg.
+enum ProfFamily { PROF_GRU_SEQ_FWD = 0, PROF_GRU_SEQ_BWD = 1, PROF_GEMM_TC = 2, PROF_FAMILIES = 3 };
+void prof_begin(int family, cudaStream_t s);
+void prof_end(int family, cudaStream_t s);
+struct ProfScope {
+  int f; cudaStream_t s;
+  ProfScope(int family, cudaStream_t stream) : f(family), s(stream) { prof_begin(f, s); }
+  ~ProfScope() { prof_end(f, s); }
+};
 
 #define TT_CHECK_ARG(cond, ...)                      \
   do {                                               \

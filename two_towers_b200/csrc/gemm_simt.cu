@@ -24,6 +24,44 @@ int engine_mode() { return g_engine; }
 void note_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
 unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
+// ------------------------------------------------------------------------------ per-family event timing
+struct ProfSlot {
+  static constexpr int CAP = 256;
+  cudaEvent_t e0[CAP], e1[CAP];
+  int created = 0, n = 0;
+  double ms = 0.0;
+  unsigned long long count = 0;
+};
+static bool g_prof_on = false;
+static ProfSlot g_prof[PROF_FAMILIES];
+static void prof_drain(ProfSlot& p) {
+  for (int i = 0; i < p.n; ++i) {
+    float ms = 0.f;
+    if (cudaEventSynchronize(p.e1[i]) == cudaSuccess && cudaEventElapsedTime(&ms, p.e0[i], p.e1[i]) == cudaSuccess) {
+      p.ms += ms;
+      ++p.count;
+    }
+  }
+  p.n = 0;
+}
+void prof_begin(int family, cudaStream_t s) {
+  if (!g_prof_on) return;
+  ProfSlot& p = g_prof[family];
+  if (p.n == ProfSlot::CAP) prof_drain(p);
+  if (p.n == p.created) {
+    cudaEventCreate(&p.e0[p.created]);
+    cudaEventCreate(&p.e1[p.created]);
+    ++p.created;
+  }
+  cudaEventRecord(p.e0[p.n], s);
+}
+void prof_end(int family, cudaStream_t s) {
+  if (!g_prof_on) return;
+  ProfSlot& p = g_prof[family];
+  cudaEventRecord(p.e1[p.n], s);
+  ++p.n;
+}
+
 template <bool A_RC, bool B_RC>
 __global__ void __launch_bounds__(NT) gemm_f32_kernel(GemmArgs g) {
   __shared__ __align__(16) float As[BK][LDS];
@@ -168,6 +206,24 @@ int tt_set_engine(int32_t mode) {
   return TT_OK;
 }
 const char* tt_last_error(void) { return tt::last_error(); }
+int tt_prof_enable(int32_t on) {
+  for (int f = 0; f < tt::PROF_FAMILIES; ++f) { tt::prof_drain(tt::g_prof[f]); tt::g_prof[f].ms = 0.0; tt::g_prof[f].count = 0; }
+  tt::g_prof_on = on != 0;
+  return TT_OK;
+}
+const char* tt_prof_family(int32_t family) {
+  static const char* names[tt::PROF_FAMILIES] = {"gru_seq_kernel (persistent forward recurrence)",
+                                                 "gru_bwd_seq_kernel (persistent fused BPTT)",
+                                                 "umma_gemm_kernel (tcgen05 GEMM engine)"};
+  return family >= 0 && family < tt::PROF_FAMILIES ? names[family] : nullptr;
+}
+int tt_prof_read(int32_t family, double* total_ms, uint64_t* launches) {
+  if (family < 0 || family >= tt::PROF_FAMILIES) { tt::set_error("tt_prof_read: family %d out of range", family); return TT_ERR_INVALID; }
+  tt::prof_drain(tt::g_prof[family]);
+  if (total_ms) *total_ms = tt::g_prof[family].ms;
+  if (launches) *launches = tt::g_prof[family].count;
+  return TT_OK;
+}
 
 int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, const float* bias,
                int32_t M, int32_t N, int32_t K, float alpha, float beta, void* stream) {

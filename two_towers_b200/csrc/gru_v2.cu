@@ -1409,6 +1409,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
       TT_CUDA(cudaMemsetAsync(f.ready, 0, sizeof(int) * nd * MT, s));
       void* args[] = {&sp};
       note_launch();
+      ProfScope prof(PROF_GRU_SEQ_FWD, s);
       if (seq_mode() == 2) {
         static bool a2 = false;
         if (!a2) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a2 = true; }
@@ -1525,6 +1526,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
       note_launch();
+      ProfScope prof(PROF_GRU_SEQ_BWD, s);
 #define TT_BWD_SEQ(NCHV, DABV)                                                                                        \
   do {                                                                                                                \
     static bool attr = false;                                                                                         \

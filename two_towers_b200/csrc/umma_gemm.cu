@@ -307,6 +307,7 @@ static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
   }
   const int grid = items < num_sms ? items : num_sms;
   note_launch();
+  ProfScope prof(PROF_GEMM_TC, s);
   kern<<<grid, kThreads, Cfg<BN, NPASS>::SMEM_BYTES, s>>>(p);
   TT_LAUNCH_CHECK();
   return TT_OK;
