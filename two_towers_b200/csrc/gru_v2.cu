@@ -824,7 +824,10 @@ constexpr int R_WSTAGE = 64 * 256 * 2;             // one k-block of W_hh: [64 k
 constexpr int R_WSTAGES = 3;
 constexpr int R_STG = 4 * 16384;                   // one staging buffer: tiles dr | dz | dn*r | dn, [128][64] fp16 each
 constexpr int R_SMEM = R_WSTAGES * R_WSTAGE + 2 * R_STG + 1024 + 512;
-constexpr int R_THREADS = 64 + 512 + 32;          // TMA producer, MMA issuer, 16 gate-gradient warps, dG writer
+constexpr int R_THREADS = 512 + 128;              // warps 0-15 gate gradients; control warpgroup: 16 TMA, 17 MMA, 18 dG writer, 19 idle
+constexpr int R_WARP_TMA = 16, R_WARP_MMA = 17, R_WARP_STORE = 18;
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 struct alignas(64) BwdSeqParams {
   CUtensorMap dg[2];                 // store maps over the dG planes [T*Bp][4H], box 64 x 128
@@ -866,6 +869,9 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) 
       : "memory");
 }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2_bulk(const void* gptr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 
 // requires H in {64, 128, 256} (one <=256-column accumulator holds every hidden unit of the tile); NCH = H / 64.
@@ -898,13 +904,16 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
     mbar_init(acc_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == R_WARP_MMA) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  // register budget: the 16 gate-gradient warps (warpgroups 0-3) take what the control warpgroup gives up
+  if (warp >= 16) {
+    setmaxnreg_dec<32>();   // 512 * 112 + 128 * 32 == 640 * 96 registers: exactly what the launch allocated
+  if (warp == R_WARP_TMA) {
     // ================================================================= W_hh producer (same 3*NCH k-blocks every step)
     if (lane == 0) {
       int stage = 0, phase = 0;
@@ -922,7 +931,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == R_WARP_MMA) {
     // ================================================================= MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_f16(128, H, 0, 1);
@@ -953,7 +962,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         }
       }
     }
-  } else if (warp == 18) {
+  } else if (warp == R_WARP_STORE) {
     // ================================================================= dG plane writer (off the cell threads' critical path)
     if (lane == 0) {
       int use = 0;
@@ -961,6 +970,25 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         const int mt = tile % MT, dir = tile / MT, m0 = mt * 128;
         for (int step = T - 1; step >= 0; --step) {
           const int t = dir == 0 ? step : T - 1 - step;
+          if (step > 0) {
+            // pull the NEXT step's saved-gate records (contiguous per (dir, t, row tile)) into L2 one whole step ahead:
+            // the cell threads' loads then see L2 latency instead of HBM latency
+            const int tn = dir == 0 ? step - 1 : T - step;
+            const int64_t grp = (((int64_t)dir * T + tn) * MT + mt) * h4;
+            const char* g = reinterpret_cast<const char*>(p.g16 + grp * 128 * 2);
+            const char* hnp = reinterpret_cast<const char*>(p.hn) + grp * 128 * 16;
+#pragma unroll 1
+            for (int i = 0; i < NCH; ++i) {
+              prefetch_l2_bulk(g + i * 65536, 65536);
+              if (i < (NCH + 1) / 2) prefetch_l2_bulk(hnp + i * 65536, NCH == 1 ? 32768 : 65536);
+            }
+            if (HAS_DAB) {
+              const char* dp = reinterpret_cast<const char*>(p.d_above) +
+                               (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2)) * 128 * 16;
+#pragma unroll 1
+              for (int i = 0; i < (NCH + 1) / 2; ++i) prefetch_l2_bulk(dp + i * 65536, NCH == 1 ? 32768 : 65536);
+            }
+          }
           for (int c = 0; c < NCH; ++c, ++use) {
             const int sb = use & 1;
             mbar_wait(&sfull[sb], (use >> 1) & 1);
@@ -974,10 +1002,12 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         }
       }
     }
+  }
   } else {
+    setmaxnreg_inc<112>();
     // ================================================================= gate gradients: thread = (batch row, 16 units per chunk)
-    const int e = threadIdx.x - 64;
-    const int quarter = warp & 3, sub = (warp - 2) >> 2;
+    const int e = threadIdx.x;
+    const int quarter = warp & 3, sub = warp >> 2;
     const int row = quarter * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
     int it = 0, use = 0;
@@ -1016,10 +1046,10 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         for (int g = 0; g < NCH * 4; ++g)
           zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + (rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) * 2) + 1)
                        : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);                             // z = 1: gradient passes through
-        float4 da[2][4];
+        float4 da[4];
         if (HAS_DAB) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) da[0][i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int i = 0; i < 4; ++i) da[i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (e == 0) BWD_MARK(it, 0);
         if (step != T - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
@@ -1031,12 +1061,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
           float dh[16];
           tmem_ld16v(cur + 64 * c + 16 * sub, dh);
           if (HAS_DAB) {
-            if (c + 1 < NCH) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i)
-                da[(c + 1) & 1][i] = live ? __ldg(dab0 + (int64_t)(16 * (c + 1) + i) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            float4* d4 = da[c & 1];
+            float4* d4 = da;
             if (p.drop_p > 0.f && live) {
               const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * c + 16 * sub);
               float s8[8];
@@ -1049,6 +1074,11 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) { dh[4 * i] += d4[i].x; dh[4 * i + 1] += d4[i].y; dh[4 * i + 2] += d4[i].z; dh[4 * i + 3] += d4[i].w; }
+            if (c + 1 < NCH) {                                   // next chunk's d_above (L2-resident: prefetched a step ahead)
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                da[i] = live ? __ldg(dab0 + (int64_t)(16 * (c + 1) + i) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
             tmem_st16(cur + 64 * c + 16 * sub, dh);
           }
 #pragma unroll
@@ -1138,7 +1168,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (warp == R_WARP_MMA) tmem_dealloc(tmem_base, 512);
 }
 
 // ------------------------------------------------------------------------------------------ backward helpers
