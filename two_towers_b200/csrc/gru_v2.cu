@@ -1235,16 +1235,44 @@ __global__ void dout_tiled_kernel(const float* __restrict__ d_out, const float* 
   }
 }
 // column sums of the dG planes of one direction -> cs[4H] (fp32, still scaled); thread = 4 columns
-__global__ void colsum_dg_kernel(const f16* __restrict__ dg, int64_t rows, int C, float* __restrict__ cs) {
-  for (int c = threadIdx.x * 4; c < C; c += blockDim.x * 4) {
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
-      const uint2 v = __ldg(reinterpret_cast<const uint2*>(dg + r * C + c));
-      const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
-      const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
-      a0 += x.x; a1 += x.y; a2 += y.x; a3 += y.y;
+__global__ void __launch_bounds__(256) colsum_dg_kernel(const f16* __restrict__ dg, int64_t rows, int C, float* __restrict__ cs) {
+  // thread = (8 consecutive columns, row phase): 16-byte loads, 4 rows in flight per thread
+  const int cg = C >> 3;
+  for (int g0 = 0; g0 < cg; g0 += 256) {
+    const int lanes = min(cg - g0, 256), rpi = 256 / lanes;
+    const int g = g0 + (int)threadIdx.x % lanes, rr = (int)threadIdx.x / lanes;
+    if (rr >= rpi) continue;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const uint4* src = reinterpret_cast<const uint4*>(dg) + g;
+    const int64_t stride = (int64_t)gridDim.x * rpi;
+    int64_t r = (int64_t)blockIdx.x * rpi + rr;
+    for (; r + 3 * stride < rows; r += 4 * stride) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(src + (r + u * stride) * cg);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+          acc[2 * i] += x.x; acc[2 * i + 1] += x.y;
+        }
+      }
     }
-    atomicAdd(cs + c, a0); atomicAdd(cs + c + 1, a1); atomicAdd(cs + c + 2, a2); atomicAdd(cs + c + 3, a3);
+    for (; r < rows; r += stride) {
+      const uint4 v = __ldg(src + r * cg);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        acc[2 * i] += x.x; acc[2 * i + 1] += x.y;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(cs + 8 * g + i, acc[i]);
   }
 }
 __global__ void bias_grads_kernel(const float* __restrict__ cs, const float* __restrict__ scale, int H, float* __restrict__ d_b_ih,

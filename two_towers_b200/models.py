@@ -45,6 +45,30 @@ class _TwoTowerBase(nn.Module):
             self._emb_table = fn(self._emb_table)
         return self
 
+    # The two towers are independent until the loss, and the persistent recurrence kernels of one tower leave SMs
+    # idle (the BPTT kernel runs one CTA per (128-row tile, direction)): the query tower goes on a side stream so the
+    # hardware can co-schedule it with the doc tower, forward and (autograd replays each node on its forward stream)
+    # backward.  Set `overlap_towers = False` for strictly serial execution on the caller's stream.
+    overlap_towers = True
+    _side_streams = {}
+
+    def _two_towers(self, fq, q_in, fd, d_in):
+        if not (self.overlap_towers and q_in.is_cuda and d_in.is_cuda):
+            return fq(q_in), fd(d_in)
+        cur = torch.cuda.current_stream(q_in.device)
+        key = (q_in.device.index, cur.cuda_stream)
+        side = _TwoTowerBase._side_streams.get(key)
+        if side is None:
+            side = _TwoTowerBase._side_streams[key] = torch.cuda.Stream(q_in.device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            q_in.record_stream(side)
+            q = fq(q_in)
+        d = fd(d_in)
+        cur.wait_stream(side)
+        q.record_stream(cur)
+        return q, d
+
     def _tower(self, x, encoder, proj, lengths=None):
         if not x.is_cuda:
             raise RuntimeError("two_towers_b200 models run on CUDA only (no CPU fallback); call .to('cuda')")
@@ -77,7 +101,7 @@ class SimpleTwoTower(_TwoTowerBase):
         return self._tower(doc_emb, self.doc_encoder, self.doc_proj, lengths)
 
     def forward(self, query_emb, doc_emb):
-        return self.encode_query(query_emb), self.encode_doc(doc_emb)
+        return self._two_towers(self.encode_query, query_emb, self.encode_doc, doc_emb)
 
 
 class TwoTowerModel(_TwoTowerBase):
@@ -108,8 +132,9 @@ class TwoTowerModel(_TwoTowerBase):
         return self.encode(doc_emb, self.doc_encoder, lengths)
 
     def forward(self, query_emb, doc_emb):
-        return self.compute_similarity(self.encode(query_emb, self.query_encoder),
-                                       self.encode(doc_emb, self.doc_encoder))
+        q, d = self._two_towers(lambda x: self.encode(x, self.query_encoder), query_emb,
+                                lambda x: self.encode(x, self.doc_encoder), doc_emb)
+        return self.compute_similarity(q, d)
 
 
 class EnhancedTwoTowerModel(_TwoTowerBase):
@@ -130,7 +155,7 @@ class EnhancedTwoTowerModel(_TwoTowerBase):
         return self._tower(doc_emb, self.doc_encoder, self.doc_proj, lengths)
 
     def forward(self, query_emb, doc_emb):
-        return self.encode_query(query_emb), self.encode_doc(doc_emb)
+        return self._two_towers(self.encode_query, query_emb, self.encode_doc, doc_emb)
 
 
 EnhancedTwoTower = EnhancedTwoTowerModel
