@@ -433,6 +433,9 @@ __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 struct alignas(64) SeqParams {
   Step2Params s;
   int* ready;                        // [ndir][MT] counters, zero before the launch
@@ -445,10 +448,11 @@ struct alignas(64) SeqParams {
   } while (0)
 
 template <int EWQ>                                              // epilogue warps per TMEM lane quarter (2 or 4)
-__global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid_constant__ SeqParams sp) {
+__global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __grid_constant__ SeqParams sp) {
   constexpr int UT = S_UN / EWQ;                                // hidden units per epilogue thread (32 or 16)
   constexpr int NCH = UT / 8;                                   // 8-unit chunks per thread
   constexpr int EPI_THREADS = 128 * EWQ;
+  constexpr int W_TMA = 4 * EWQ, W_MMA = 4 * EWQ + 1;           // control warpgroup follows the epilogue warpgroups
   const Step2Params& p = sp.s;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -468,13 +472,15 @@ __global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 1); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, Q_TMEM_COLS);
+  if (warp == W_MMA) tmem_alloc(tmem_slot, Q_TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp >= 4 * EWQ) {
+    if (EWQ == 4) setmaxnreg_dec<32>();                          // 512 * 112 + 128 * 32 == 640 * 96: what the launch allocated
+  if (warp == W_TMA) {
     // ================================================================= TMA producer
     if (lane == 0) {
       int stage = 0, phase = 0, pitem = 0;
@@ -511,7 +517,7 @@ __global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == W_MMA) {
     // ================================================================= MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_f16(S_BM, S_BN, 0, 0);
@@ -543,10 +549,12 @@ __global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid
         }
       }
     }
+  }
   } else {
+    if (EWQ == 4) setmaxnreg_inc<112>();
     // ================================================================= fused GRU cell: thread = (batch row, UT units)
-    const int e = threadIdx.x - 64;
-    const int quarter = warp & 3, sub = (warp - 2) >> 2;
+    const int e = threadIdx.x;
+    const int quarter = warp & 3, sub = warp >> 2;
     const int row = quarter * 32 + lane;
     const int h4 = H >> 2;
     int item = 0;
@@ -712,7 +720,7 @@ __global__ void __launch_bounds__(64 + 128 * EWQ, 1) gru_seq_kernel(const __grid
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, Q_TMEM_COLS);
+  if (warp == W_MMA) tmem_dealloc(tmem_base, Q_TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------ K-C' gate gradients
@@ -826,8 +834,7 @@ constexpr int R_STG = 4 * 16384;                   // one staging buffer: tiles 
 constexpr int R_SMEM = R_WSTAGES * R_WSTAGE + 2 * R_STG + 1024 + 512;
 constexpr int R_THREADS = 512 + 128;              // warps 0-15 gate gradients; control warpgroup: 16 TMA, 17 MMA, 18 dG writer, 19 idle
 constexpr int R_WARP_TMA = 16, R_WARP_MMA = 17, R_WARP_STORE = 18;
-template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
-template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 
 struct alignas(64) BwdSeqParams {
   CUtensorMap dg[2];                 // store maps over the dG planes [T*Bp][4H], box 64 x 128
@@ -1471,11 +1478,11 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
       if (seq_mode() == 2) {
         static bool a2 = false;
         if (!a2) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a2 = true; }
-        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<2>, dim3(ncta), dim3(64 + 256), args, Q_SMEM, s));
+        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<2>, dim3(ncta), dim3(256 + 128), args, Q_SMEM, s));
       } else {
         static bool a4 = false;
         if (!a4) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a4 = true; }
-        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<4>, dim3(ncta), dim3(64 + 512), args, Q_SMEM, s));
+        TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<4>, dim3(ncta), dim3(512 + 128), args, Q_SMEM, s));
       }
     } else {
       dim3 grid((unsigned)(H / S_UN), (unsigned)MT, (unsigned)nd);
