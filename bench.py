@@ -40,6 +40,7 @@ def parse():
     p.add_argument("--vocab", type=int, default=3_000_000)
     p.add_argument("--cpu-batch", type=int, default=256, help="pairs per step of the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--serial-towers", action="store_true", help="both towers on one stream (for per-kernel launch lists)")
     return p.parse_args()
 
 
@@ -229,6 +230,7 @@ def run_ours(args):
     table = torch.empty(V, E, device=dev).normal_(0, 0.1, generator=torch.Generator(device=dev).manual_seed(7))
     table[0] = 0
     model.attach_embeddings(table, pad_id=0)
+    model.overlap_towers = not args.serial_towers
     crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
     opt = torch.optim.Adam(model.parameters(), fused=True)
     reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None
@@ -280,7 +282,7 @@ def run_ours(args):
     barrier()
     roofs, fams = kernel_rooflines(lib, args.steps, B, peaks())
     lib.tt_prof_enable(0)
-    model.overlap_towers = True
+    model.overlap_towers = not args.serial_towers
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)

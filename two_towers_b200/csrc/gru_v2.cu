@@ -1241,7 +1241,8 @@ __global__ void dout_tiled_kernel(const float* __restrict__ d_out, const float* 
     reinterpret_cast<float4*>(out)[i] = v;
   }
 }
-// column sums of the dG planes of one direction -> cs[4H] (fp32, still scaled); thread = 4 columns
+constexpr int kColsumBlocks = 592;
+// column sums of the dG planes of one direction -> partial sums cs[block * rpi + phase][4H] (fp32, still scaled)
 __global__ void __launch_bounds__(256) colsum_dg_kernel(const f16* __restrict__ dg, int64_t rows, int C, float* __restrict__ cs) {
   // thread = (8 consecutive columns, row phase): 16-byte loads, 4 rows in flight per thread
   const int cg = C >> 3;
@@ -1278,17 +1279,31 @@ __global__ void __launch_bounds__(256) colsum_dg_kernel(const f16* __restrict__ 
         acc[2 * i] += x.x; acc[2 * i + 1] += x.y;
       }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) atomicAdd(cs + 8 * g + i, acc[i]);
+    // per-(block, row phase) partial sums, reduced by bias_grads_kernel (same-address atomics from every block
+    // serialise in L2 and cost as much as the streaming read itself)
+    float* out = cs + ((int64_t)blockIdx.x * rpi + rr) * C + 8 * g;
+    *reinterpret_cast<float4*>(out) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(out + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
   }
 }
-__global__ void bias_grads_kernel(const float* __restrict__ cs, const float* __restrict__ scale, int H, float* __restrict__ d_b_ih,
-                                  float* __restrict__ d_b_hh) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= 3 * H) return;
-  const float inv = scale[1];
-  d_b_hh[n] = cs[n] * inv;                              // (dr, dz, dn*r)
-  d_b_ih[n] = cs[n < 2 * H ? n : n + H] * inv;          // (dr, dz, dn)
+// one block per 32 columns of the dG plane: sums the `parts` partial rows, then scatters to the two bias gradients
+__global__ void __launch_bounds__(256) bias_grads_kernel(const float* __restrict__ cs, int parts, const float* __restrict__ scale, int H,
+                                                         float* __restrict__ d_b_ih, float* __restrict__ d_b_hh) {
+  __shared__ float red[8][33];
+  const int C = 4 * H, col = blockIdx.x * 32 + (threadIdx.x & 31), ph = threadIdx.x >> 5;
+  float v = 0.f;
+  for (int pi = ph; pi < parts; pi += 8) v += cs[(int64_t)pi * C + col];
+  red[ph][threadIdx.x & 31] = v;
+  __syncthreads();
+  if (ph == 0) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) v += red[i][threadIdx.x & 31];
+    v *= scale[1];
+    const int gate = col / H, u = col - gate * H;         // plane columns: dr | dz | dn*r | dn
+    if (gate < 3) d_b_hh[col] = v;                        // (dr, dz, dn*r)
+    if (gate < 2) d_b_ih[col] = v;                        // (dr, dz, dn)
+    else if (gate == 3) d_b_ih[2 * H + u] = v;
+  }
 }
 
 static inline unsigned gblocks(int64_t n, int per = 256, int cap = 148 * 16) {
@@ -1509,7 +1524,7 @@ static uint64_t carve_bwd_ws(const V2Dims& d, void* base, uint64_t size, V2BwdWs
   for (int i = 0; i < d.nd; ++i) f.dg[i] = w.take<f16>(d.ntok * 4 * d.H);
   f.dhs = w.take<float>((int64_t)d.nd * d.Bp * d.H);
   for (int i = 0; i < 2; ++i) f.dab[i] = w.take<float>(d.ntok * d.nd * d.H);
-  f.cs = w.take<float>((int64_t)d.nd * 4 * d.H);
+  f.cs = w.take<float>((int64_t)kColsumBlocks * (d.H >= 512 ? 1 : 512 / d.H) * 4 * d.H);   // per-block partial column sums (one direction at a time)
   f.scale = w.take<float>(4);
   f.mx = w.take<unsigned int>(4);
   for (int i = 0; i < d.nd; ++i) { f.whh_hi[i] = w.take<f16>((int64_t)3 * d.H * d.H); f.wih_hi[i] = w.take<f16>((int64_t)3 * d.H * kpmax); }
@@ -1625,10 +1640,10 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     float* d_below = nullptr;                            // tiled dX for the layer below
     for (int dd = 0; dd < nd; ++dd) {
       const Planes dgp{(const bf16*)f.dg[dd], nullptr, 4 * H};
-      float* cs = f.cs + (int64_t)dd * 4 * H;
-      TT_CUDA(cudaMemsetAsync(cs, 0, sizeof(float) * 4 * H, s));
-      note_launch(); colsum_dg_kernel<<<592, 256, 0, s>>>(f.dg[dd], d.ntok, 4 * H, cs);
-      note_launch(); bias_grads_kernel<<<(unsigned)ceil_div(3 * H, 256), 256, 0, s>>>(cs, f.scale, H, a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
+      float* cs = f.cs;
+      const int cgs = (4 * H) >> 3, rpi = cgs >= 256 ? 1 : 256 / cgs;
+      note_launch(); colsum_dg_kernel<<<kColsumBlocks, 256, 0, s>>>(f.dg[dd], d.ntok, 4 * H, cs);
+      note_launch(); bias_grads_kernel<<<(unsigned)(4 * H / 32), 256, 0, s>>>(cs, kColsumBlocks * rpi, f.scale, H, a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
       TT_LAUNCH_CHECK();
       // dW_hh[3H,H] = dGH^T h_prev   (reduction over all tokens; h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
       {
