@@ -171,7 +171,8 @@ struct alignas(64) Step2Params {
   CUtensorMap x_hi, x_lo;            // next layer's input planes [T*Bp][ndir*H], box 64 x 128 (store)
   const float* gi;                   // tiled [ndir][T][MT][3][H/4][128][4], biases folded
   const float* b_hh[2];              // only the n-gate third is read
-  uint4* g16;                        // saved gates [ndir][T][MT][H/4][128][16 x 16 bit] or null
+  uint4* g16;                        // saved gates or null: plane A [ndir][T][MT][H/4][128] x (r0..3, z0..3 as u16), then
+  int64_t g16_plane;                 // plane B (n0..3, q0..3 as s16) g16_plane uint4 further on (each plane contiguous per row)
   float* hn;                         // saved h W_hn^T + b_hn, tiled [ndir][T][MT][H/4][128][4] or null
   float* out;                        // fp32 [B,T,ndir*H] or null
   float* h_n;                        // fp32 [ndir][B][H] (written at the last step)
@@ -355,8 +356,8 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
           bq.y = q_s16(n[o + 2], kNScale) | (q_s16(n[o + 3], kNScale) << 16);
           bq.z = q_s16(q[o], kQScale) | (q_s16(q[o + 1], kQScale) << 16);
           bq.w = q_s16(q[o + 2], kQScale) | (q_s16(q[o + 3], kQScale) << 16);
-          uint4* gp = p.g16 + (gbase + (int64_t)(2 * c + g4) * 128) * 2;
-          gp[0] = a; gp[1] = bq;
+          const int64_t gidx = gbase + (int64_t)(2 * c + g4) * 128;
+          p.g16[gidx] = a; p.g16[p.g16_plane + gidx] = bq;
           reinterpret_cast<float4*>(p.hn)[gbase + (int64_t)(2 * c + g4) * 128] = make_float4(hn[o], hn[o + 1], hn[o + 2], hn[o + 3]);
         }
       }
@@ -656,8 +657,8 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
               bq.y = q_s16(n[o + 2], kNScale) | (q_s16(n[o + 3], kNScale) << 16);
               bq.z = q_s16(q[o], kQScale) | (q_s16(q[o + 1], kQScale) << 16);
               bq.w = q_s16(q[o + 2], kQScale) | (q_s16(q[o + 3], kQScale) << 16);
-              uint4* gp = p.g16 + (gbase + (int64_t)(2 * c + g4) * 128) * 2;
-              gp[0] = a; gp[1] = bq;
+              const int64_t gidx = gbase + (int64_t)(2 * c + g4) * 128;
+              p.g16[gidx] = a; p.g16[p.g16_plane + gidx] = bq;
               reinterpret_cast<float4*>(p.hn)[gbase + (int64_t)(2 * c + g4) * 128] = make_float4(hn[o], hn[o + 1], hn[o + 2], hn[o + 3]);
             }
           }
@@ -728,6 +729,7 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
 struct alignas(64) CellBwdParams {
   CUtensorMap dg[2];                 // store maps, box 64 x 128
   const uint4* g16;
+  int64_t g16_plane;
   const float* hn;
   float* dhs;                        // tiled running dL/dh [ndir][MT][H/4][128][4] (scaled)
   const float* d_above;              // tiled [T][MT][ndir*H/4][128][4] (scaled) or null
@@ -760,8 +762,8 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
     float4 hn4[4], dh4[4], da4[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      ga[i] = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2);
-      gb[i] = __ldg(p.g16 + (gbase + (int64_t)i * 128) * 2 + 1);
+      ga[i] = __ldg(p.g16 + gbase + (int64_t)i * 128);
+      gb[i] = __ldg(p.g16 + p.g16_plane + gbase + (int64_t)i * 128);
       hn4[i] = __ldg(reinterpret_cast<const float4*>(p.hn) + gbase + (int64_t)i * 128);
       dh4[i] = dhs[i * 128];
       da4[i] = dab ? __ldg(dab + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -840,6 +842,7 @@ struct alignas(64) BwdSeqParams {
   CUtensorMap dg[2];                 // store maps over the dG planes [T*Bp][4H], box 64 x 128
   CUtensorMap w[2];                  // load maps over W_hh hi planes [3H][H], box 64 x 64
   const uint4* g16;
+  int64_t g16_plane;
   const float* hn;
   const float* dhs0;                 // tiled initial dL/dh [ndir][MT][H/4][128][4] (scaled)
   const float* d_above;              // tiled [T][MT][ndir*H/4][128][4] (scaled) or null
@@ -982,12 +985,15 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             // the cell threads' loads then see L2 latency instead of HBM latency
             const int tn = dir == 0 ? step - 1 : T - step;
             const int64_t grp = (((int64_t)dir * T + tn) * MT + mt) * h4;
-            const char* g = reinterpret_cast<const char*>(p.g16 + grp * 128 * 2);
+            const char* ga = reinterpret_cast<const char*>(p.g16 + grp * 128);
+            const char* gb = reinterpret_cast<const char*>(p.g16 + p.g16_plane + grp * 128);
             const char* hnp = reinterpret_cast<const char*>(p.hn) + grp * 128 * 16;
 #pragma unroll 1
-            for (int i = 0; i < NCH; ++i) {
-              prefetch_l2_bulk(g + i * 65536, 65536);
-              if (i < (NCH + 1) / 2) prefetch_l2_bulk(hnp + i * 65536, NCH == 1 ? 32768 : 65536);
+            for (int i = 0; i < (NCH + 1) / 2; ++i) {             // each region: H/4 groups x 128 rows x 16 B = NCH x 32 KB
+              constexpr uint32_t PF = NCH == 1 ? 32768 : 65536;
+              prefetch_l2_bulk(ga + i * 65536, PF);
+              prefetch_l2_bulk(gb + i * 65536, PF);
+              prefetch_l2_bulk(hnp + i * 65536, PF);
             }
             if (HAS_DAB) {
               const char* dp = reinterpret_cast<const char*>(p.d_above) +
@@ -1051,7 +1057,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         uint2 zw[NCH * 4];
 #pragma unroll
         for (int g = 0; g < NCH * 4; ++g)
-          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + (rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) * 2) + 1)
+          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) + 1)
                        : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);                             // z = 1: gradient passes through
         float4 da[4];
         if (HAS_DAB) {
@@ -1104,8 +1110,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
 #define TT_LOAD_HALF(GA, GB, HN, HCV)                                                                          \
   _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                              \
     const int64_t rec = rec0 + (int64_t)(((HCV) >> 1) * 16 + ((HCV) & 1) * 2 + i) * 128;                       \
-    GA[i] = live ? __ldg(p.g16 + rec * 2) : make_uint4(0u, 0u, 0u, 0u);                                        \
-    GB[i] = live ? __ldg(p.g16 + rec * 2 + 1) : make_uint4(0u, 0u, 0u, 0u);                                    \
+    GA[i] = live ? __ldg(p.g16 + rec) : make_uint4(0u, 0u, 0u, 0u);                                            \
+    GB[i] = live ? __ldg(p.g16 + p.g16_plane + rec) : make_uint4(0u, 0u, 0u, 0u);                              \
     HN[i] = live ? __ldg(reinterpret_cast<const float4*>(p.hn) + rec) : make_float4(0.f, 0.f, 0.f, 0.f);       \
   }
 #define TT_GRAD_HALF(GA, GB, HN, CV, CCV, SBUF)                                                                \
@@ -1462,6 +1468,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     }
     p.gi = f.gi;
     p.g16 = save ? sv.g16[l] : nullptr; p.hn = save ? sv.hn[l] : nullptr;
+    p.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128;
     p.out = (a->out && !has_next) ? a->out : nullptr;
     p.h_n = a->h_n + (int64_t)l * nd * B * H;
     p.lengths = a->lengths;
@@ -1577,7 +1584,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     CellBwdParams cp;
     memset(&cp, 0, sizeof(cp));
     for (int dd = 0; dd < nd; ++dd) TT_TRY(make_plane_map(&cp.dg[dd], f.dg[dd], d.ntok, 4 * H, 4 * H, 128, 1));
-    cp.g16 = sv.g16[l]; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
+    cp.g16 = sv.g16[l]; cp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
     cp.B = B; cp.Bp = Bp; cp.T = T; cp.H = H; cp.ndir = nd;
     cp.drop_p = (has_next && d_above) ? fw->dropout_p : 0.f;
     cp.inv_keep = cp.drop_p > 0.f ? 1.f / (1.f - cp.drop_p) : 1.f;
@@ -1601,7 +1608,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
         bp.dg[dd] = cp.dg[dd];
         TT_TRY(make_plane_map(&bp.w[dd], f.whh_hi[dd], 3 * H, H, H, 64, 1));
       }
-      bp.g16 = sv.g16[l]; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
+      bp.g16 = sv.g16[l]; bp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
       bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
       bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
