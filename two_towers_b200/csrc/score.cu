@@ -2,7 +2,11 @@
 // The [Bl,Bg] logit matrix is never held whole: it is produced in column chunks sized to stay L2-resident
 // (<= 32 MiB of the 126 MB L2), consumed by a row-statistics (fwd) or softmax-gradient (bwd) kernel, and
 // overwritten by the next chunk.  Scores are exact fp32 (one FMA chain per element).
+#include <cuda_fp16.h>
 #include "common.cuh"
+#include "umma.cuh"
+#include "umma_gemm.cuh"
+#include "gru_umma.cuh"
 
 namespace tt {
 
@@ -64,6 +68,63 @@ __global__ void ce_grad_kernel(float* __restrict__ S, int ld, int Bl, int c0, in
     const float v = *p - (is_pos ? 0.f : margin);
     *p = (__expf(v - row_lse[row]) - (is_pos ? 1.f : 0.f)) * coef;
   }
+}
+
+// fp32 [rows][cols] -> fp16 hi/lo planes [rows][pitch] (pad columns zero)
+__global__ void split_rows_f16_kernel(const float* __restrict__ x, int64_t rows, int cols, int64_t pitch,
+                                      __half* __restrict__ hi, __half* __restrict__ lo) {
+  const int64_t total = rows * pitch;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % pitch);
+    const float v = c < cols ? x[(i / pitch) * cols + c] : 0.f;
+    __half a, b;
+    umma::split_f16(v, a, b);
+    hi[i] = a; lo[i] = b;
+  }
+}
+// G = (softmax - onehot) * coef as fp16 hi/lo planes [Bl][pitch]; columns [nc, pitch) are zero.  coef carries a power
+// of two that lifts the tiny probabilities out of the fp16 subnormal range (undone by alpha of the gradient GEMMs).
+__global__ void ce_grad_planes_kernel(const float* __restrict__ S, int ld, int Bl, int c0, int nc, int pos_offset, float margin,
+                                      const float* __restrict__ row_lse, float coef, __half* __restrict__ gh,
+                                      __half* __restrict__ gl, int pitch) {
+  const int64_t total = (int64_t)Bl * pitch;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i / pitch), c = (int)(i % pitch);
+    float g = 0.f;
+    if (c < nc) {
+      const bool is_pos = (c0 + c) == pos_offset + row;
+      const float v = S[(int64_t)row * ld + c] - (is_pos ? 0.f : margin);
+      g = (__expf(v - row_lse[row]) - (is_pos ? 1.f : 0.f)) * coef;
+    }
+    __half a, b;
+    umma::split_f16(g, a, b);
+    gh[i] = a; gl[i] = b;
+  }
+}
+static inline bool score_tc() { return engine_mode() >= 1 && umma_available(); }
+struct ScorePlanes { __half *xh, *xl, *yh, *yl, *gh, *gl; int64_t dp, ncp; };
+static void carve_score_planes(Workspace& w, int Bl, int Bg, int D, int NC, bool grad, ScorePlanes* o) {
+  o->dp = plane_pitch(D); o->ncp = plane_pitch(NC);
+  o->xh = w.take<__half>((int64_t)Bl * o->dp); o->xl = w.take<__half>((int64_t)Bl * o->dp);
+  o->yh = w.take<__half>((int64_t)Bg * o->dp); o->yl = w.take<__half>((int64_t)Bg * o->dp);
+  o->gh = o->gl = nullptr;
+  if (grad) { o->gh = w.take<__half>((int64_t)Bl * o->ncp); o->gl = w.take<__half>((int64_t)Bl * o->ncp); }
+}
+static int split_xy(const float* x, int Bl, const float* y, int Bg, int D, const ScorePlanes& sp, cudaStream_t s) {
+  note_launch(); split_rows_f16_kernel<<<592, 256, 0, s>>>(x, Bl, D, sp.dp, sp.xh, sp.xl);
+  note_launch(); split_rows_f16_kernel<<<592, 256, 0, s>>>(y, Bg, D, sp.dp, sp.yh, sp.yl);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+// S[Bl, nc] = inv_temp * x y[c0:c0+nc]^T on the tensor engine (x3)
+static int score_chunk_tc(const ScorePlanes& sp, int Bl, int Bg, int D, int c0, int nc, int NC, float inv_temp, float* S,
+                          cudaStream_t s) {
+  UmmaGemm g{};
+  g.A[0] = Planes{(const bf16*)sp.xh, (const bf16*)sp.xl, sp.dp};
+  g.B[0] = Planes{(const bf16*)sp.yh, (const bf16*)sp.yl, sp.dp};
+  g.C[0] = S; g.ldc = NC; g.M = Bl; g.N = nc; g.K = D; g.nbatch = 1;
+  g.b_rows = Bg; g.b_row0 = c0; g.alpha = inv_temp; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
+  return umma_gemm(g, s);
 }
 
 // ---------------------------------------------------------------------------------- K-G hinge
@@ -131,10 +192,11 @@ using namespace tt;
 extern "C" {
 
 uint64_t tt_score_ce_workspace(int32_t Bl, int32_t Bg, int32_t D) {
-  (void)D;
   Workspace w(nullptr, 0);
   w.take<float>((int64_t)Bl * chunk_cols(Bl, Bg));
   for (int i = 0; i < 3; ++i) w.take<float>(Bl);
+  ScorePlanes sp;
+  carve_score_planes(w, Bl, Bg, D, chunk_cols(Bl, Bg), true, &sp);   // tensor-engine operand planes (fwd uses a prefix)
   return w.used + 256;
 }
 
@@ -148,14 +210,22 @@ int tt_score_ce_fwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
   Workspace w(workspace, workspace_bytes);
   float* S = w.take<float>((int64_t)Bl * NC);
   float* rmax = w.take<float>(Bl); float* rsum = w.take<float>(Bl); float* plog = w.take<float>(Bl);
+  const bool tc = score_tc();
+  ScorePlanes sp{};
+  if (tc) carve_score_planes(w, Bl, Bg, D, NC, false, &sp);
   if (!w.ok()) { set_error("score_ce_fwd: workspace too small"); return TT_ERR_WORKSPACE; }
+  if (tc) TT_TRY(split_xy(x, Bl, y, Bg, D, sp, s));
   for (int c0 = 0; c0 < Bg; c0 += NC) {
     const int nc = (Bg - c0) < NC ? (Bg - c0) : NC;
-    GemmArgs g{};
-    g.A[0] = x; g.B[0] = y + (int64_t)c0 * D; g.C[0] = S;
-    g.a_rs = D; g.a_cs = 1; g.b_rs = D; g.b_cs = 1; g.ldc = NC;
-    g.M = Bl; g.N = nc; g.K = D; g.nbatch = 1; g.splitk = 1; g.alpha = inv_temp; g.beta = 0.f;
-    TT_TRY(gemm_f32(g, s));
+    if (tc) {
+      TT_TRY(score_chunk_tc(sp, Bl, Bg, D, c0, nc, NC, inv_temp, S, s));
+    } else {
+      GemmArgs g{};
+      g.A[0] = x; g.B[0] = y + (int64_t)c0 * D; g.C[0] = S;
+      g.a_rs = D; g.a_cs = 1; g.b_rs = D; g.b_cs = 1; g.ldc = NC;
+      g.M = Bl; g.N = nc; g.K = D; g.nbatch = 1; g.splitk = 1; g.alpha = inv_temp; g.beta = 0.f;
+      TT_TRY(gemm_f32(g, s));
+    }
     tt::note_launch(); ce_rowstats_kernel<<<(unsigned)ceil_div(Bl, 8), 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, rmax, rsum, plog, c0 == 0);
   }
   tt::note_launch(); ce_finish_kernel<<<(unsigned)ceil_div(Bl, 256), 256, 0, s>>>(rmax, rsum, plog, row_loss, row_lse, Bl);
@@ -171,9 +241,44 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
   const int NC = chunk_cols(Bl, Bg);
   Workspace w(workspace, workspace_bytes);
   float* S = w.take<float>((int64_t)Bl * NC);
+  for (int i = 0; i < 3; ++i) w.take<float>(Bl);              // (same carve order as the forward / the workspace query)
+  const bool tc = score_tc();
+  ScorePlanes sp{};
+  if (tc) carve_score_planes(w, Bl, Bg, D, NC, true, &sp);
   if (!w.ok()) { set_error("score_ce_bwd: workspace too small"); return TT_ERR_WORKSPACE; }
+  if (tc) TT_TRY(split_xy(x, Bl, y, Bg, D, sp, s));
+  // power of two lifting |G| <= |gscale| * inv_temp into [4, 8): keeps small probabilities out of fp16 subnormals
+  float lift = 1.f;
+  if (tc) {
+    const float gmax = fabsf(gscale * inv_temp);
+    int ex = 0;
+    if (gmax > 0.f && isfinite(gmax)) { frexpf(gmax, &ex); lift = ldexpf(1.f, 3 - ex); }
+  }
   for (int c0 = 0; c0 < Bg; c0 += NC) {
     const int nc = (Bg - c0) < NC ? (Bg - c0) : NC;
+    if (tc) {
+      TT_TRY(score_chunk_tc(sp, Bl, Bg, D, c0, nc, NC, inv_temp, S, s));
+      int64_t tot = (int64_t)Bl * sp.ncp, nb = ceil_div(tot, 256);
+      if (nb > 148 * 16) nb = 148 * 16;
+      tt::note_launch();
+      ce_grad_planes_kernel<<<(unsigned)nb, 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, row_lse, gscale * inv_temp * lift,
+                                                         sp.gh, sp.gl, (int)sp.ncp);
+      // dx[Bl,D] (+)= G[Bl,nc] Y[c0:c0+nc, D]      (A K-major over the chunk columns, B = Y rows as an MN-major operand)
+      UmmaGemm gx{};
+      gx.A[0] = Planes{(const bf16*)sp.gh, (const bf16*)sp.gl, sp.ncp};
+      gx.B[0] = Planes{(const bf16*)(sp.yh + (int64_t)c0 * sp.dp), (const bf16*)(sp.yl + (int64_t)c0 * sp.dp), sp.dp};
+      gx.C[0] = dx; gx.ldc = D; gx.M = Bl; gx.N = D; gx.K = nc; gx.nbatch = 1; gx.a_mn = false; gx.b_mn = true;
+      gx.alpha = 1.f / lift; gx.beta = c0 == 0 ? 0.f : 1.f; gx.splitk = 0; gx.f16 = 1; gx.npass = 3;
+      TT_TRY(umma_gemm(gx, s));
+      // dy[c0:c0+nc, D] = G^T X                     (both operands MN-major: reduction over the Bl rows)
+      UmmaGemm gy{};
+      gy.A[0] = Planes{(const bf16*)sp.gh, (const bf16*)sp.gl, sp.ncp};
+      gy.B[0] = Planes{(const bf16*)sp.xh, (const bf16*)sp.xl, sp.dp};
+      gy.C[0] = dy + (int64_t)c0 * D; gy.ldc = D; gy.M = nc; gy.N = D; gy.K = Bl; gy.nbatch = 1; gy.a_mn = gy.b_mn = true;
+      gy.alpha = 1.f / lift; gy.beta = 0.f; gy.splitk = 0; gy.f16 = 1; gy.npass = 3;
+      TT_TRY(umma_gemm(gy, s));
+      continue;
+    }
     GemmArgs g{};
     g.A[0] = x; g.B[0] = y + (int64_t)c0 * D; g.C[0] = S;
     g.a_rs = D; g.a_cs = 1; g.b_rs = D; g.b_cs = 1; g.ldc = NC;

@@ -373,7 +373,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   p.splitk = splitk;
   out->items = MT * NT * g.nbatch * splitk;
   const int major = (!g.a_mn && !g.b_mn) ? 0 : (g.a_mn && g.b_mn) ? 1 : (!g.a_mn && g.b_mn) ? 2 : 3;
-  if (major == 3 || (major == 2 && npass == 3)) {
+  if (major == 3) {
     set_error("umma_gemm: operand major / pass combination not instantiated");
     return TT_ERR_INVALID;
   }
@@ -398,11 +398,13 @@ int umma_gemm_launch(const UmmaPrepared& prep, const int* a_row0, cudaStream_t s
   switch (prep.kind) {
     case 0: return launch_cfg<128, false, false, 3>(p, items, s);
     case 1: return launch_cfg<128, true, true, 3>(p, items, s);
+    case 2: return launch_cfg<128, false, true, 3>(p, items, s);
     case 4: return launch_cfg<128, false, false, 1>(p, items, s);
     case 5: return launch_cfg<128, true, true, 1>(p, items, s);
     case 6: return launch_cfg<128, false, true, 1>(p, items, s);
     case 8: return launch_cfg<256, false, false, 3>(p, items, s);
     case 9: return launch_cfg<256, true, true, 3>(p, items, s);
+    case 10: return launch_cfg<256, false, true, 3>(p, items, s);
     case 12: return launch_cfg<256, false, false, 1>(p, items, s);
     case 13: return launch_cfg<256, true, true, 1>(p, items, s);
     case 14: return launch_cfg<256, false, true, 1>(p, items, s);
