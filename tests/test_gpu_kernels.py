@@ -322,6 +322,28 @@ def test_rows_topk_dot_is_bit_exact(Q, N, D, k):
         assert (idx.cpu().numpy()[:, N:] == -1).all() and np.isneginf(val.cpu().numpy()[:, N:]).all()
 
 
+@pytest.mark.parametrize("cosine", [False, True])
+def test_rows_topk_tensor_route_equals_exact_scan(cosine):
+    """tensor-engine candidate selection + exact re-score (default engine) must reproduce the exact fused scan
+    (engine 0) bit for bit, including rows that fail the acceptance test (40 copies of one document -> more ties
+    than candidate slots) and a masked positive."""
+    rng = np.random.default_rng(77)
+    Q, N, D, k = 300, 20000, 128, 8
+    x, y = rng.standard_normal((Q, D)).astype(np.float32), rng.standard_normal((N, D)).astype(np.float32)
+    y[100:140] = y[50]                                   # 41 identical rows
+    x[:20] = y[50] + 0.01 * rng.standard_normal((20, D)).astype(np.float32)   # queries whose top hits are those ties
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    try:
+        lib.tt_set_engine(0)
+        ev, ei = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine, mask_pos_offset=5, index_base=1000)
+    finally:
+        lib.tt_set_engine(2)
+    tv, ti = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine, mask_pos_offset=5, index_base=1000)
+    assert torch.equal(ti, ei) and torch.equal(tv, ev)
+    assert ti[0].tolist() == [1050] + list(range(1100, 1107))
+
+
 def test_hard_negatives_match_golden_and_reference_semantics():
     g = load_golden("losses_mining")
     from two_towers_b200 import enhanced_two_tower as E

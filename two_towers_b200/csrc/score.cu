@@ -101,6 +101,12 @@ __global__ void ce_grad_planes_kernel(const float* __restrict__ S, int ld, int B
     gh[i] = a; gl[i] = b;
   }
 }
+int split_rows_f16(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, cudaStream_t s) {
+  if (rows <= 0) return TT_OK;
+  note_launch(); split_rows_f16_kernel<<<592, 256, 0, s>>>(x, rows, cols, pitch, (__half*)hi, (__half*)lo);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
 static inline bool score_tc() { return engine_mode() >= 1 && umma_available(); }
 struct ScorePlanes { __half *xh, *xl, *yh, *yl, *gh, *gl; int64_t dp, ncp; };
 static void carve_score_planes(Workspace& w, int Bl, int Bg, int D, int NC, bool grad, ScorePlanes* o) {

@@ -1,5 +1,11 @@
 // K-F / K-H exact-fp32 score + streaming row top-k, K-I shard merge, MRR rank kernel.
 //
+// Two routes to the same result.  Exact route (engine 0, and the fall-back of the other): the fused scan below.
+// Tensor route: approximate scores from the tcgen05 engine (fp16 hi/lo planes, 3 passes, |error| <= 2^-13 |x||y|)
+// only SELECT k+8 candidates per row; the candidates are then re-scored with the exact chain and ordered by the same
+// total order, and a row is accepted only if its k-th exact score clears every non-candidate by more than the error
+// bound - otherwise that row is redone by the exact scan.  Indices are therefore bit-exact on either route.
+//
 // score(i,j) is ONE fp32 FMA chain over d = 0..D-1 (ascending), optionally scaled to a cosine with
 // pre-computed inverse norms: (dot * invx[i]) * invy[j].  The scan never stores scores: a 128x128 tile is
 // reduced in registers, each value is compared against its row's current k-th best (score desc, index asc
@@ -9,6 +15,8 @@
 #include <limits.h>
 #include "common.cuh"
 #include "simt_tile.cuh"
+#include "umma_gemm.cuh"
+#include "gru_umma.cuh"
 
 namespace tt {
 
@@ -41,7 +49,8 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
                                                       int64_t N, int D, int k, const float* __restrict__ invx,
                                                       const float* __restrict__ invy, int64_t mask_pos_offset,
                                                       int64_t index_base, int64_t cols_per_split,
-                                                      float* __restrict__ out_val, int64_t* __restrict__ out_idx) {
+                                                      float* __restrict__ out_val, int64_t* __restrict__ out_idx,
+                                                      const int* __restrict__ need) {
   __shared__ __align__(16) float As[BK][LDS];
   __shared__ __align__(16) float Bs[BK][LDS];
   __shared__ float thr_v[BM];
@@ -52,6 +61,7 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
 
   const int t = threadIdx.x, tx = t & 15, ty = t >> 4, lane = t & 31, warp = t >> 5;
   const int bm = blockIdx.x * BM;
+  if (need && !__syncthreads_or(t < BM && bm + t < Q && need[bm + t] != 0)) return;   // no row of this tile was rejected
   const int64_t cbeg = (int64_t)blockIdx.y * cols_per_split;
   const int64_t cend = cbeg + cols_per_split < N ? cbeg + cols_per_split : N;
 
@@ -148,7 +158,7 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
 #pragma unroll
   for (int r = 0; r < 16; ++r) {
     const int m = bm + warp * 16 + r;
-    if (m < Q && lane < k) {
+    if (m < Q && lane < k && !(need && need[m] == 0)) {
       const int64_t o = ((int64_t)blockIdx.y * Q + m) * k + lane;
       const bool empty = li[r] == INT_MAX;
       out_val[o] = empty ? -INFINITY : lv[r];
@@ -159,9 +169,9 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
 
 // one warp per query: merge S lists of k (vals [S,Q,k], idx [S,Q,k]) by (score desc, idx asc)
 __global__ void topk_merge_kernel(const float* __restrict__ vals, const int64_t* __restrict__ idx, int S, int Q, int k,
-                                  float* __restrict__ out_val, int64_t* __restrict__ out_idx) {
+                                  float* __restrict__ out_val, int64_t* __restrict__ out_idx, const int* __restrict__ need) {
   const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (q >= Q) return;
+  if (q >= Q || (need && need[q] == 0)) return;
   float lv = -INFINITY; long long li = LLONG_MAX;
   for (int s = 0; s < S; ++s)
     for (int e = 0; e < k; ++e) {
@@ -194,6 +204,106 @@ __global__ void mrr_ranks_kernel(const int64_t* __restrict__ topk_idx, const int
   rr[q] = rank ? 1.f / rank : 0.f;
 }
 
+
+// ------------------------------------------------------------------------------------------ tensor route
+constexpr int kCandSlack = 8;
+constexpr float kScoreErr = 1.220703125e-4f;                 // 2^-13: bound on |approx - exact| / (|x| |y|), 4x margin
+
+__global__ void list_init_kernel(float* __restrict__ lv, int* __restrict__ li, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { lv[i] = -INFINITY; li[i] = INT_MAX; }
+}
+__global__ void min_pos_kernel(const float* __restrict__ v, int64_t n, unsigned int* __restrict__ out) {
+  float m = INFINITY;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) m = fminf(m, v[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMin(out, __float_as_uint(m));       // positive floats order like their bit patterns
+}
+// one warp per row of the approximate score tile S[nq][ld] (columns c0 .. c0+nc of the corpus): fold it into the row's
+// running candidate list (lane r = rank r, K2 entries used)
+__global__ void select_rows_kernel(const float* __restrict__ S, int64_t ld, int q0, int nq, int64_t c0, int nc, int cosine,
+                                   const float* __restrict__ invx, const float* __restrict__ invy, int64_t mask_pos_offset,
+                                   int K2, float* __restrict__ list_v, int* __restrict__ list_i) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (r >= nq) return;
+  const int row = q0 + r;
+  float lv = list_v[(int64_t)row * 32 + lane];
+  int li = list_i[(int64_t)row * 32 + lane];
+  float tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
+  int ti = __shfl_sync(0xffffffffu, li, K2 - 1);
+  const float rinv = cosine ? invx[row] : 1.f;
+  const float* s = S + (int64_t)r * ld;
+  for (int c = 0; c < nc; c += 32) {
+    const int cl = c + lane;
+    const int64_t cg = c0 + cl;
+    float sc = -INFINITY;
+    if (cl < nc) {
+      sc = s[cl];
+      if (cosine) sc = (sc * rinv) * invy[cg];
+      if (mask_pos_offset >= 0 && cg == mask_pos_offset + row) sc = -1.f;
+      if (sc != sc) sc = INFINITY;                           // NaN (fp16 overflow of an operand): force the exact route
+    }
+    unsigned m = __ballot_sync(0xffffffffu, sc > -INFINITY && better(sc, (int)cg, tv, ti));
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      const float cv = __shfl_sync(0xffffffffu, sc, b);
+      const int ci = (int)(c0 + c + b);
+      if (better(cv, ci, tv, ti)) {
+        list_insert(lv, li, cv, ci, lane);
+        tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
+        ti = __shfl_sync(0xffffffffu, li, K2 - 1);
+      }
+    }
+  }
+  list_v[(int64_t)row * 32 + lane] = lv;
+  list_i[(int64_t)row * 32 + lane] = li;
+}
+// one warp per row: exact chain for each candidate, exact order, acceptance test
+__global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const float* __restrict__ Y, int D, int k, int K2,
+                                    int cosine, const float* __restrict__ invx, const float* __restrict__ invy,
+                                    const unsigned int* __restrict__ min_invy, int64_t mask_pos_offset, int64_t index_base,
+                                    const float* __restrict__ list_v, const int* __restrict__ list_i,
+                                    float* __restrict__ out_val, int64_t* __restrict__ out_idx, int* __restrict__ need) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= Q) return;
+  const float av = list_v[(int64_t)row * 32 + lane];
+  const int ci = list_i[(int64_t)row * 32 + lane];
+  const bool valid = lane < K2 && ci != INT_MAX;
+  float ev = -INFINITY;
+  if (valid) {
+    const float* x = X + (int64_t)row * D;
+    const float* y = Y + (int64_t)ci * D;
+    float acc = 0.f;
+    for (int d = 0; d < D; ++d) acc = fmaf(x[d], y[d], acc);
+    ev = cosine ? (acc * invx[row]) * invy[ci] : acc;
+    if (mask_pos_offset >= 0 && ci == mask_pos_offset + row) ev = -1.f;
+  }
+  const int ei = valid ? ci : INT_MAX - 31 + lane;           // distinct keys: empty slots rank after every candidate, in lane order
+  int rank = 0;
+#pragma unroll 1
+  for (int l = 0; l < 32; ++l) {
+    const float ov = __shfl_sync(0xffffffffu, ev, l);
+    const int oi = __shfl_sync(0xffffffffu, ei, l);
+    if (l != lane && better(ov, oi, ev, ei)) ++rank;
+  }
+  // acceptance: every non-candidate has approx <= a_min, hence exact <= a_min + err; the k-th exact score must clear that
+  const float a_min = __shfl_sync(0xffffffffu, av, K2 - 1);
+  const bool full = __shfl_sync(0xffffffffu, ci, K2 - 1) != INT_MAX;       // list not full: every column is a candidate
+  const unsigned at_k = __ballot_sync(0xffffffffu, rank == k - 1 && valid);
+  float e_k = -INFINITY;
+  if (at_k) e_k = __shfl_sync(0xffffffffu, ev, __ffs(at_k) - 1);
+  // cosine: |x| invx and |y| invy are <= 1; dot: |x| max|y|  (invx = 1/max(|x|,1e-8))
+  const float scale = cosine ? 1.f : (1.f / invx[row]) * (1.f / __uint_as_float(*min_invy));
+  const bool ok = !full || (e_k - a_min > kScoreErr * scale);               // false for NaN/inf as well
+  if (lane == 0) need[row] = ok ? 0 : 1;
+  if (ok && rank < k) {
+    out_val[(int64_t)row * k + rank] = valid ? ev : -INFINITY;
+    out_idx[(int64_t)row * k + rank] = valid ? index_base + ci : -1;
+  }
+}
+
 static int topk_splits(int Q, int64_t N) {
   const int64_t row_tiles = ceil_div(Q, BM);
   int64_t s = ceil_div(2 * 148, row_tiles);
@@ -208,12 +318,40 @@ using namespace tt;
 
 extern "C" {
 
-uint64_t tt_rows_topk_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode) {
-  (void)D;
-  Workspace w(nullptr, 0);
-  if (mode == 1) { w.take<float>(Q); w.take<float>(N); }
+// tensor route tiling: S tile = QT x NC fp32 <= 128 MiB
+static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma_available() && N >= 256 && N < INT_MAX - 64 && k + kCandSlack <= 32; }
+static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
+static inline int64_t topk_nc(int Q, int64_t N) {
+  int64_t nc = (128ll << 20) / (4ll * topk_qt(Q));
+  nc = nc / 256 * 256;
+  if (nc > 65536) nc = 65536;
+  return nc < N ? nc : (N + 7) / 8 * 8;
+}
+struct TopkWs {
+  float *invx, *invy; unsigned int* ymin; float* pv; int64_t* pi;
+  __half *xh, *xl, *yh, *yl; float* S; float* lv; int* li; int* need; int64_t dp;
+};
+static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, TopkWs* o) {
+  const bool tc = topk_tc(N, k);
+  o->invx = o->invy = nullptr;
+  if (mode == 1 || tc) { o->invx = w.take<float>(Q); o->invy = w.take<float>(N); }
   const int S = topk_splits(Q, N);
-  if (S > 1) { w.take<float>((int64_t)S * Q * 32); w.take<int64_t>((int64_t)S * Q * 32); }
+  o->pv = nullptr; o->pi = nullptr;
+  if (S > 1) { o->pv = w.take<float>((int64_t)S * Q * 32); o->pi = w.take<int64_t>((int64_t)S * Q * 32); }
+  if (tc) {
+    o->dp = plane_pitch(D);
+    o->ymin = w.take<unsigned int>(64);
+    o->xh = w.take<__half>((int64_t)Q * o->dp); o->xl = w.take<__half>((int64_t)Q * o->dp);
+    o->yh = w.take<__half>(N * o->dp); o->yl = w.take<__half>(N * o->dp);
+    o->S = w.take<float>((int64_t)topk_qt(Q) * topk_nc(Q, N));
+    o->lv = w.take<float>((int64_t)Q * 32); o->li = w.take<int>((int64_t)Q * 32); o->need = w.take<int>(Q);
+  }
+}
+
+uint64_t tt_rows_topk_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode) {
+  Workspace w(nullptr, 0);
+  TopkWs t;
+  carve_topk(w, Q, N, D, mode, 1, &t);          // k only gates the route (k + slack <= 32): size for the larger one
   return w.used + 256;
 }
 
@@ -225,22 +363,57 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
   TT_CHECK_ARG(mode == 0 || mode == 1, "rows_topk: mode must be 0 (dot) or 1 (cosine)");
   cudaStream_t s = (cudaStream_t)stream;
   Workspace w(workspace, workspace_bytes);
-  float *invx = nullptr, *invy = nullptr;
-  if (mode == 1) { invx = w.take<float>(Q); invy = w.take<float>(N); }
-  const int S = topk_splits(Q, N);
-  float* pv = nullptr; int64_t* pi = nullptr;
-  if (S > 1) { pv = w.take<float>((int64_t)S * Q * 32); pi = w.take<int64_t>((int64_t)S * Q * 32); }
+  TopkWs t;
+  carve_topk(w, Q, N, D, mode, k, &t);
   if (!w.ok()) { set_error("rows_topk: workspace too small"); return TT_ERR_WORKSPACE; }
-  if (mode == 1) {
+  const bool tc = topk_tc(N, k);
+  float* invx = t.invx; float* invy = t.invy;
+  if (invx) {
     tt::note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, D, 1e-8f, invx);
     if (N > 0) { note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy); }
   }
+  const int* need = nullptr;
+  if (tc) {
+    // ---- tensor route: approximate tile scores -> candidates -> exact re-score -> acceptance
+    const int K2 = k + kCandSlack, QT = topk_qt(Q);
+    const int64_t NC = topk_nc(Q, N);
+    TT_CUDA(cudaMemsetAsync(t.ymin, 0x7f, sizeof(unsigned int), s));
+    note_launch(); min_pos_kernel<<<296, 256, 0, s>>>(invy, N, t.ymin);
+    note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)Q * 32, 256), 256, 0, s>>>(t.lv, t.li, (int64_t)Q * 32);
+    TT_TRY(split_rows_f16(x, Q, D, t.dp, t.xh, t.xl, s));
+    TT_TRY(split_rows_f16(y, N, D, t.dp, t.yh, t.yl, s));
+    for (int q0 = 0; q0 < Q; q0 += QT) {
+      const int nq = Q - q0 < QT ? Q - q0 : QT;
+      for (int64_t c0 = 0; c0 < N; c0 += NC) {
+        const int nc = (int)(N - c0 < NC ? N - c0 : NC);
+        UmmaGemm g{};
+        g.A[0] = Planes{(const bf16*)t.xh, (const bf16*)t.xl, t.dp};
+        g.B[0] = Planes{(const bf16*)t.yh, (const bf16*)t.yl, t.dp};
+        g.C[0] = t.S; g.ldc = NC; g.M = nq; g.N = nc; g.K = D; g.nbatch = 1;
+        g.a_rows = Q; g.a_row0 = q0; g.b_rows = N; g.b_row0 = (int32_t)c0;
+        g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
+        TT_TRY(umma_gemm(g, s));
+        note_launch();
+        select_rows_kernel<<<(unsigned)ceil_div(nq, 8), 256, 0, s>>>(t.S, NC, q0, nq, c0, nc, mode, invx, invy, mask_pos_offset, K2,
+                                                                    t.lv, t.li);
+      }
+    }
+    note_launch();
+    rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, t.ymin, mask_pos_offset,
+                                                                index_base, t.lv, t.li, out_val, out_idx, t.need);
+    TT_LAUNCH_CHECK();
+    need = t.need;
+    if (mode == 0) { invx = nullptr; invy = nullptr; }      // the exact scan applies norms only for the cosine
+  }
+  // ---- exact scan: everything (engine 0) or only the rows the acceptance test rejected
+  const int S = topk_splits(Q, N);
+  float* pv = t.pv; int64_t* pi = t.pi;
   int64_t cps = ceil_div(N > 0 ? N : 1, S);
   cps = ceil_div(cps, BN) * BN;
   dim3 grid((unsigned)ceil_div(Q, BM), (unsigned)S);
   tt::note_launch(); rows_topk_kernel<<<grid, NT, 0, s>>>(x, Q, y, N, D, k, invx, invy, mask_pos_offset, index_base, cps,
-                                      S > 1 ? pv : out_val, S > 1 ? pi : out_idx);
-  if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx); }
+                                      S > 1 ? pv : out_val, S > 1 ? pi : out_idx, need);
+  if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx, need); }
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -248,7 +421,7 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
 int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k, float* out_val,
                   int64_t* out_idx, void* stream) {
   TT_CHECK_ARG(vals && idx && out_val && out_idx && S > 0 && Q > 0 && k >= 1 && k <= 32, "topk_merge: bad args");
-  tt::note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx);
+  tt::note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx, nullptr);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
