@@ -33,8 +33,8 @@ FLOPS_PER_PAIR = 3.0 * 12 * GRU_H * (E + 4 * GRU_H) * (TQ + TD)
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
-    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--batch", type=int, default=4096, help="pairs per GPU (4096 = the BASELINE config)")
     p.add_argument("--vocab", type=int, default=3_000_000)
@@ -69,11 +69,14 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.t0 = self.t1 = None
 
     def start(self):
+        """Launch the sampler (nvidia-smi needs ~0.2 s before its first line, so this happens before the warm-up);
+        only lines that arrive inside [mark_begin, mark_end] are kept."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -81,16 +84,26 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([time.perf_counter()] + [c.strip() for c in line.split(",")])
+
+    def mark_begin(self):
+        self.t0 = time.perf_counter()
+
+    def mark_end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.t1 is None:
+            self.mark_end()
+        time.sleep(0.05)
         self.proc.terminate()
-        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        rows = [r[1:] for r in self.rows if self.t0 is None or self.t0 <= r[0] <= self.t1 + 0.03]
+        sm = [float(r[1]) for r in rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
+        reasons = sorted({n for r in rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
 
@@ -255,14 +268,15 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    sampler.start()
     for i in range(args.warmup):
         step(*resident[i % nb])
     # ---- value: inputs resident in HBM, CUDA events on the launch stream, max over ranks
-    sampler = ClockSampler(local)
     st = torch.cuda.current_stream()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    sampler.start()
+    sampler.mark_begin()
     k0 = lib.tt_kernel_launches()
     e0.record(st)
     for i in range(args.steps):
@@ -270,6 +284,7 @@ def run_ours(args):
     e1.record(st)
     barrier()
     launches = int(lib.tt_kernel_launches() - k0)
+    sampler.mark_end()
     clocks = sampler.stop()
     # ---- dominant-kernel timing: the same K steps again with the towers on ONE stream (kernel durations under
     # two-stream overlap would include time-slicing with the other tower), CUDA events around every launch

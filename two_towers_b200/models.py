@@ -60,6 +60,11 @@ class _TwoTowerBase(nn.Module):
         side = _TwoTowerBase._side_streams.get(key)
         if side is None:
             side = _TwoTowerBase._side_streams[key] = torch.cuda.Stream(q_in.device)
+            # gradients of the query tower are produced on the side stream by design; autograd synchronises the
+            # accumulation itself and only warns about it
+            warn_off = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+            if warn_off is not None:
+                warn_off(False)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
             q_in.record_stream(side)
