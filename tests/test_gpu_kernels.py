@@ -414,7 +414,7 @@ def test_gemm_x3_engine(M, N, K, trans, splitk):
 
 
 @pytest.mark.parametrize("flags", [0, 1, 3, 4 | 8, 1 | 4 | 8, 1 | 2 | 4 | 8, 1 | 2 | 8])
-@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 200, 130), (1000, 520, 96)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (300, 200, 130), (1000, 520, 96), (384, 300, 2100), (768, 256, 8192)])
 def test_gemm_operand_formats(M, N, K, flags):
     """bf16 / fp16 planes, 3 passes / 1 pass, K-major / MN-major operands of the tcgen05 GEMM vs float64."""
     from two_towers_b200 import _lib as L
