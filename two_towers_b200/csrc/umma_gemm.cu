@@ -12,7 +12,7 @@ namespace tt {
 using namespace umma;
 
 constexpr int UBM = 128, UBK = 64;
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue (two per TMEM lane quarter, half the columns each)
 
 struct alignas(64) UmmaParams {
   CUtensorMap a_hi[2], a_lo[2], b_hi[2], b_lo[2];
@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   } else {
     // ================================================================= epilogue (warps 2..5)
     const int quarter = warp & 3;             // TMEM lanes this warp may touch: [32*quarter, 32*quarter+32)
+    const int chalf = (warp - 2) >> 2;        // which half of the tile's columns this warp drains
     const int row = quarter * 32 + lane;
     const float alpha = p.alpha * (p.alpha_ptr ? __ldg(p.alpha_ptr) : 1.f);
     int tile = 0;
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       }
       const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C[bz]) & 15) == 0);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
         const int gn0 = n_blk * BN + c0;
