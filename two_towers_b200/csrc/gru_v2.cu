@@ -1293,12 +1293,12 @@ __global__ void __launch_bounds__(256) colsum_dg_kernel(const f16* __restrict__ 
   }
 }
 // one block per 32 columns of the dG plane: sums the `parts` partial rows, then scatters to the two bias gradients
-__global__ void __launch_bounds__(256) bias_grads_kernel(const float* __restrict__ cs, int parts, const float* __restrict__ scale, int H,
+__global__ void __launch_bounds__(256) bias_grads_kernel(const float* __restrict__ cs, int pitch, int parts, const float* __restrict__ scale, int H,
                                                          float* __restrict__ d_b_ih, float* __restrict__ d_b_hh) {
   __shared__ float red[8][33];
-  const int C = 4 * H, col = blockIdx.x * 32 + (threadIdx.x & 31), ph = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31), ph = threadIdx.x >> 5;   // cs already points at this direction's columns
   float v = 0.f;
-  for (int pi = ph; pi < parts; pi += 8) v += cs[(int64_t)pi * C + col];
+  for (int pi = ph; pi < parts; pi += 8) v += cs[(int64_t)pi * pitch + col];
   red[ph][threadIdx.x & 31] = v;
   __syncthreads();
   if (ph == 0) {
@@ -1528,13 +1528,19 @@ static uint64_t carve_bwd_ws(const V2Dims& d, void* base, uint64_t size, V2BwdWs
   V2BwdWs f{};
   int kpmax = 0;
   for (int l = 0; l < d.L; ++l) kpmax = d.kp_l(l) > kpmax ? d.kp_l(l) : kpmax;
-  for (int i = 0; i < d.nd; ++i) f.dg[i] = w.take<f16>(d.ntok * 4 * d.H);
+  f.dg[0] = w.take<f16>(d.ntok * d.nd * 4 * d.H);             // ONE plane [T*Bp][ndir*4H]: direction dd = columns [4H*dd, 4H*dd + 4H)
+  f.dg[1] = f.dg[0] + 4 * d.H;
   f.dhs = w.take<float>((int64_t)d.nd * d.Bp * d.H);
   for (int i = 0; i < 2; ++i) f.dab[i] = w.take<float>(d.ntok * d.nd * d.H);
-  f.cs = w.take<float>((int64_t)kColsumBlocks * (d.H >= 512 ? 1 : 512 / d.H) * 4 * d.H);   // per-block partial column sums (one direction at a time)
+  {
+    const int cg = d.nd * d.H / 2, rpi = cg >= 256 ? 1 : 256 / cg;      // as colsum_dg_kernel splits its 256 threads
+    f.cs = w.take<float>((int64_t)kColsumBlocks * rpi * d.nd * 4 * d.H);   // per-(block, row phase) partial column sums
+  }
   f.scale = w.take<float>(4);
   f.mx = w.take<unsigned int>(4);
-  for (int i = 0; i < d.nd; ++i) { f.whh_hi[i] = w.take<f16>((int64_t)3 * d.H * d.H); f.wih_hi[i] = w.take<f16>((int64_t)3 * d.H * kpmax); }
+  for (int i = 0; i < d.nd; ++i) f.whh_hi[i] = w.take<f16>((int64_t)3 * d.H * d.H);
+  f.wih_hi[0] = w.take<f16>((int64_t)d.nd * 3 * d.H * kpmax);   // both directions stacked along the gate rows: [ndir*3H][kp]
+  f.wih_hi[1] = nullptr;
   if (out) *out = f;
   return w.used + 256;
 }
@@ -1575,7 +1581,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     const bool has_next = l + 1 < L;
     for (int dd = 0; dd < nd; ++dd) {
       note_launch(); w_planes_kernel<<<gblocks((int64_t)3 * H * H), 256, 0, s>>>(wptr(fw, l, dd, 1), 3 * H, H, H, f.whh_hi[dd], nullptr);
-      note_launch(); w_planes_kernel<<<gblocks((int64_t)3 * H * kp), 256, 0, s>>>(wptr(fw, l, dd, 0), 3 * H, in, kp, f.wih_hi[dd], nullptr);
+      note_launch(); w_planes_kernel<<<gblocks((int64_t)3 * H * kp), 256, 0, s>>>(wptr(fw, l, dd, 0), 3 * H, in, kp, f.wih_hi[0] + (int64_t)dd * 3 * H * kp, nullptr);
     }
     note_launch();
     init_dhs_kernel<<<gblocks((int64_t)nd * Bp * (H / 4)), 256, 0, s>>>(a->d_h_n ? a->d_h_n + (int64_t)l * nd * B * H : nullptr, f.scale, B, Bp, H, nd, f.dhs);
@@ -1583,7 +1589,8 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
 
     CellBwdParams cp;
     memset(&cp, 0, sizeof(cp));
-    for (int dd = 0; dd < nd; ++dd) TT_TRY(make_plane_map(&cp.dg[dd], f.dg[dd], d.ntok, 4 * H, 4 * H, 128, 1));
+    const int dgp_pitch = nd * 4 * H;
+    for (int dd = 0; dd < nd; ++dd) TT_TRY(make_plane_map(&cp.dg[dd], f.dg[dd], d.ntok, 4 * H, dgp_pitch, 128, 1));
     cp.g16 = sv.g16[l]; cp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
     cp.B = B; cp.Bp = Bp; cp.T = T; cp.H = H; cp.ndir = nd;
     cp.drop_p = (has_next && d_above) ? fw->dropout_p : 0.f;
@@ -1592,7 +1599,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     // per step: dhs (tiled) += dGH_t W_hh     (A rows t*Bp.., K = 3H; B = W_hh as stored = [K][N] MN-major)
     UmmaGemm r{};
     for (int dd = 0; dd < nd; ++dd) {
-      r.A[dd] = Planes{(const bf16*)f.dg[dd], nullptr, 4 * H};
+      r.A[dd] = Planes{(const bf16*)f.dg[dd], nullptr, dgp_pitch};
       r.B[dd] = Planes{(const bf16*)f.whh_hi[dd], nullptr, H};
       r.C[dd] = f.dhs + (int64_t)dd * Bp * H;
     }
@@ -1645,13 +1652,19 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }
 
     float* d_below = nullptr;                            // tiled dX for the layer below
-    for (int dd = 0; dd < nd; ++dd) {
-      const Planes dgp{(const bf16*)f.dg[dd], nullptr, 4 * H};
-      float* cs = f.cs;
-      const int cgs = (4 * H) >> 3, rpi = cgs >= 256 ? 1 : 256 / cgs;
-      note_launch(); colsum_dg_kernel<<<kColsumBlocks, 256, 0, s>>>(f.dg[dd], d.ntok, 4 * H, cs);
-      note_launch(); bias_grads_kernel<<<(unsigned)(4 * H / 32), 256, 0, s>>>(cs, kColsumBlocks * rpi, f.scale, H, a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
+    {
+      // bias gradients: column sums of the whole dG plane (both directions in one pass)
+      const int C = dgp_pitch, cgs = C >> 3, rpi = cgs >= 256 ? 1 : 256 / cgs;
+      note_launch(); colsum_dg_kernel<<<kColsumBlocks, 256, 0, s>>>(f.dg[0], d.ntok, C, f.cs);
+      for (int dd = 0; dd < nd; ++dd) {
+        note_launch();
+        bias_grads_kernel<<<(unsigned)(4 * H / 32), 256, 0, s>>>(f.cs + dd * 4 * H, C, kColsumBlocks * rpi, f.scale, H,
+                                                              a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
+      }
       TT_LAUNCH_CHECK();
+    }
+    for (int dd = 0; dd < nd; ++dd) {
+      const Planes dgp{(const bf16*)f.dg[dd], nullptr, dgp_pitch};
       // dW_hh[3H,H] = dGH^T h_prev   (reduction over all tokens; h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
       {
         UmmaGemm g{};
@@ -1661,7 +1674,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
         g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
         TT_TRY(umma_gemm(g, s));
       }
-      // dW_ih[3H,In] = dGI^T X   (dGI = columns [0,2H) and [3H,4H) of the dG planes)
+      // dW_ih[3H,In] = dGI^T X   (dGI = columns [0,2H) and [3H,4H) of the direction's dG columns)
       {
         UmmaGemm g{};
         g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H;
@@ -1670,21 +1683,24 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
         g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
         TT_TRY(umma_gemm(g, s));
       }
-      // dX (+)= dGI W_ih : tiled for the layer below, or the API's batch-first fp32 d_x
-      if (l > 0 || a->d_x) {
-        UmmaGemm g{};
-        g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H; g.a_rows = d.ntok;
-        g.B[0] = Planes{(const bf16*)f.wih_hi[dd], nullptr, kp};
-        g.M = (int)d.ntok; g.N = in; g.K = 3 * H; g.nbatch = 1; g.a_mn = false; g.b_mn = true;
-        g.alpha = 1.f; g.beta = dd == 0 ? 0.f : 1.f; g.splitk = 1; g.f16 = 1; g.npass = 1;
-        if (l > 0) {
-          d_below = f.dab[(l - 1) & 1];
-          g.C[0] = d_below; g.epi = 1; g.tl_Bp = Bp; g.tl_G = 1; g.tl_Hc = in;
-        } else {
-          g.C[0] = a->d_x; g.ldc = in; g.alpha_ptr = f.scale + 1; g.rm_Bp = Bp; g.rm_B = B; g.rm_T = T;
-        }
-        TT_TRY(umma_gemm(g, s));
+    }
+    // dX = sum over directions of dGI W_ih, as ONE GEMM with the directions concatenated along the reduction:
+    // A = plane columns {dir0: dr dz dn, dir1: dr dz dn} (two skipped dn*r blocks), B = W_ih rows stacked [ndir*3H][kp].
+    // Tiled for the layer below, or the API's batch-first fp32 d_x.
+    if (l > 0 || a->d_x) {
+      UmmaGemm g{};
+      g.A[0] = Planes{(const bf16*)f.dg[0], nullptr, dgp_pitch}; g.a_seg = 2 * H; g.a_skip = H; g.a_seg2 = nd == 2 ? 5 * H : 0;
+      g.a_rows = d.ntok;
+      g.B[0] = Planes{(const bf16*)f.wih_hi[0], nullptr, kp};
+      g.M = (int)d.ntok; g.N = in; g.K = nd * 3 * H; g.nbatch = 1; g.a_mn = false; g.b_mn = true;
+      g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 1;
+      if (l > 0) {
+        d_below = f.dab[(l - 1) & 1];
+        g.C[0] = d_below; g.epi = 1; g.tl_Bp = Bp; g.tl_G = 1; g.tl_Hc = in;
+      } else {
+        g.C[0] = a->d_x; g.ldc = in; g.alpha_ptr = f.scale + 1; g.rm_Bp = Bp; g.rm_B = B; g.rm_T = T;
       }
+      TT_TRY(umma_gemm(g, s));
     }
     d_above = d_below;
   }

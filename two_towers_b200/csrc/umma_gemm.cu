@@ -23,7 +23,7 @@ struct alignas(64) UmmaParams {
   int32_t M, N, K, nbatch, splitk;
   float alpha, beta;
   uint32_t idesc;
-  int32_t a_row0[2], b_row0, a_seg, a_skip;
+  int32_t a_row0[2], b_row0, a_seg, a_skip, a_seg2;
   int32_t epi, rm_Bp, rm_B, rm_T, tl_Bp, tl_G, tl_Hc;
 };
 
@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           if (!A_MN) {
             int ka = kb * UBK;
             if (p.a_seg > 0 && ka >= p.a_seg) ka += p.a_skip;
+            if (p.a_seg2 > 0 && kb * UBK >= p.a_seg2) ka += p.a_skip;
             tma_load_2d(&p.a_hi[bz], &full[stage], sa_hi, ka, m_blk * UBM + p.a_row0[bz]);
             if (NPASS == 3) tma_load_2d(&p.a_lo[bz], &full[stage], sa_lo, ka, m_blk * UBM + p.a_row0[bz]);
           } else {
@@ -327,7 +328,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0) BN = 128;
   UmmaParams& p = *reinterpret_cast<UmmaParams*>(out->blob);
   const int f16 = g.f16;
-  const int64_t skipA = g.a_seg > 0 ? g.a_skip : 0;
+  const int64_t skipA = g.a_seg > 0 ? (int64_t)g.a_skip * (g.a_seg2 > 0 ? 2 : 1) : 0;
   for (int b = 0; b < g.nbatch; ++b) {
     // K-major: plane [MN rows][K cols], box rows = tile MN extent.  MN-major: plane [K rows][MN cols], box 64x64.
     if (!g.a_mn) {
@@ -351,7 +352,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     p.C[b] = g.C[b]; p.bias[b] = g.bias[b]; p.a_row0[b] = g.a_row0;
   }
   p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K; p.nbatch = g.nbatch; p.alpha = g.alpha; p.beta = g.beta;
-  p.alpha_ptr = g.alpha_ptr; p.b_row0 = g.b_row0; p.a_seg = g.a_seg; p.a_skip = g.a_skip;
+  p.alpha_ptr = g.alpha_ptr; p.b_row0 = g.b_row0; p.a_seg = g.a_seg; p.a_skip = g.a_skip; p.a_seg2 = g.a_seg2;
   p.epi = g.epi; p.rm_Bp = g.rm_Bp; p.rm_B = g.rm_B; p.rm_T = g.rm_T; p.tl_Bp = g.tl_Bp; p.tl_G = g.tl_G; p.tl_Hc = g.tl_Hc;
   p.idesc = f16 ? make_idesc_f16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0) : make_idesc_bf16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0);
   if (g.epi == 1)

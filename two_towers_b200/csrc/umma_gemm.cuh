@@ -41,6 +41,7 @@ struct UmmaGemm {
   int32_t npass;       // 0/3: hi*hi + lo*hi + hi*lo ; 1: hi*hi only (lo planes unused)
   int64_t a_rows, b_rows;   // rows of the plane arrays the tensor maps cover (0: derived from M/N/K)
   int32_t a_row0, b_row0;   // K-major operands: first plane row of the problem (e.g. t*Bp for one timestep)
+  int32_t a_seg2;           // optional second threshold of the remap below: i >= a_seg2 skips a_skip once more (K-major A)
   int32_t a_seg, a_skip;    // A column remap: logical index i >= a_seg reads plane column i + a_skip
                             //   (K-major A: i = k ; MN-major A: i = m).  Both multiples of 64 (128 for MN-major).
   const float* alpha_ptr;   // optional device scalar multiplied into alpha (loss-scale undo)
