@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--cpu-batch", type=int, default=256, help="pairs per step of the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--serial-towers", action="store_true", help="both towers on one stream (for per-kernel launch lists)")
+    p.add_argument("--eval-queries", type=int, default=8192, help="queries of the retrieval leg (0 = skip it)")
+    p.add_argument("--eval-docs", type=int, default=1_100_000, help="corpus rows per GPU of the retrieval leg (C5 shard)")
     return p.parse_args()
 
 
@@ -219,6 +221,46 @@ def kernel_rooflines(lib, steps, B, pk):
     return out, fams
 
 
+def eval_leg(args, dev, rank, world, group):
+    """SURVEY 8d metric (ii) on a bounded sample of BASELINE configs[4]: score + top-10 + shard merge + MRR@10 over
+    pre-computed embeddings.  Queries replicated, corpus sharded by contiguous global id (1.1 M rows per GPU = the C5
+    shard size); one relevant doc per query planted as normalize(q + 0.5 randn)."""
+    import two_towers_b200 as tt
+    Q, Nl, D = args.eval_queries, args.eval_docs, HID
+    g = torch.Generator(device=dev).manual_seed(4321)
+    q = torch.nn.functional.normalize(torch.randn(Q, D, device=dev, generator=g), dim=1)
+    gl = torch.Generator(device=dev).manual_seed(99 + rank)
+    docs = torch.nn.functional.normalize(torch.randn(Nl, D, device=dev, generator=gl), dim=1)
+    rel = torch.randint(0, Nl * world, (Q,), device=dev, generator=g)
+    mine = (rel // Nl) == rank
+    noisy = torch.nn.functional.normalize(q + 0.5 * torch.randn(Q, D, device=dev, generator=g) / D ** 0.5, dim=1)
+    docs[(rel % Nl)[mine]] = noisy[mine]
+
+    def run():
+        val, idx = tt.sharded_search_topk(q, docs, rank * Nl, k=10, group=group)
+        return tt.mrr_recall(idx, rel)
+
+    run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    reps = 3
+    e0.record()
+    for _ in range(reps):
+        m = run()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = ms.item()
+    return {"metric": "eval queries/sec (score + top-10 + shard merge + MRR@10)", "value": Q / (ms * 1e-3), "unit": "queries/s",
+            "queries": Q, "docs_per_gpu": Nl, "docs_total": Nl * world, "dim": D, "ms": ms, "mrr10": m["MRR"],
+            "recall10": m["R@10"], "algorithmic_tflops": 2.0 * Q * Nl * world * D / (ms * 1e-3) / 1e12,
+            "note": "bounded sample of BASELINE configs[4] (1e5 queries x 8.8 M docs): same shard size, fewer queries; "
+                    "includes the fp32 -> fp16 hi/lo conversion of the corpus shard on every call"}
+
+
 def run_ours(args):
     import torch.distributed as dist
     import two_towers_b200 as tt
@@ -331,8 +373,12 @@ def run_ours(args):
         }
         line["roofline"] = roofs[0] if roofs else None
         line["kernels"] = roofs[1:] + [f for f in fams[2:]]
-        del resident[:], host[:]
-        torch.cuda.empty_cache()
+    del resident[:], host[:]
+    del model, opt, table
+    torch.cuda.empty_cache()
+    ev = eval_leg(args, dev, rank, world, group) if args.eval_queries > 0 else None
+    if rank == 0:
+        line["eval"] = ev
         if world == 1 and not args.no_cpu_baseline:
             val, ms, threads = cpu_reference(3, 1, args.cpu_batch)
             line["cpu_baseline"] = {"value": val, "unit": "pairs/s", "cores": threads, "kind": "port",

@@ -318,11 +318,12 @@ using namespace tt;
 
 extern "C" {
 
-// tensor route tiling: S tile = QT x NC fp32 <= 128 MiB
+// tensor route tiling: S tile = QT x NC fp32 <= 48 MiB, so that the tile written by the GEMM is still in the 126 MB L2
+// when the selection kernel reads it
 static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma_available() && N >= 256 && N < INT_MAX - 64 && k + kCandSlack <= 32; }
 static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
 static inline int64_t topk_nc(int Q, int64_t N) {
-  int64_t nc = (128ll << 20) / (4ll * topk_qt(Q));
+  int64_t nc = (48ll << 20) / (4ll * topk_qt(Q));
   nc = nc / 256 * 256;
   if (nc > 65536) nc = 65536;
   return nc < N ? nc : (N + 7) / 8 * 8;
