@@ -286,6 +286,7 @@ def run_ours(args):
     table[0] = 0
     model.attach_embeddings(table, pad_id=0)
     model.overlap_towers = not args.serial_towers
+    lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
     crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
     opt = torch.optim.Adam(model.parameters(), fused=True)
     reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None
@@ -331,6 +332,7 @@ def run_ours(args):
     # ---- dominant-kernel timing: the same K steps again with the towers on ONE stream (kernel durations under
     # two-stream overlap would include time-slicing with the other tower), CUDA events around every launch
     model.overlap_towers = False
+    lib.tt_debug_wgrad_overlap(0)
     step(*resident[0])
     barrier()
     lib.tt_prof_enable(1)
@@ -339,6 +341,7 @@ def run_ours(args):
     barrier()
     roofs, fams = kernel_rooflines(lib, args.steps, B, peaks())
     lib.tt_prof_enable(0)
+    lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
     model.overlap_towers = not args.serial_towers
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:

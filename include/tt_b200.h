@@ -261,6 +261,10 @@ int tt_debug_seq_mode(int32_t mode);
 /* BPTT of the v2 pipeline: 1 (default) = fused persistent kernel (dL/dh resident in tensor memory, hidden size <= 256),
  * 0 = gate-gradient kernel + dh GEMM per timestep. */
 int tt_debug_bwd_seq_mode(int32_t mode);
+/* 1 (default): in a multi-layer backward the weight / bias gradient GEMMs of layer l run on a library-owned helper stream,
+ * concurrently with the BPTT kernel of layer l-1, and are joined back into the caller's stream before the call returns
+ * (to the caller all work stays ordered on its stream).  0: everything on the caller's stream (per-kernel timing). */
+int tt_debug_wgrad_overlap(int32_t on);
 
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);

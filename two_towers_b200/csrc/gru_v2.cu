@@ -155,6 +155,7 @@ __global__ void fold_bias_kernel(const float* __restrict__ b_ih, const float* __
 unsigned long long* g_step_dbg = nullptr;
 static int g_seq_mode = 4;                    // 0: one launch per timestep; 2 / 4: persistent kernel, epilogue warps per quarter
 static int seq_mode() { return g_seq_mode; }
+static int g_wgrad_overlap = 1;               // 1: weight-gradient GEMMs of layer l overlap the BPTT of layer l-1 (helper stream)
 static int g_bwd_seq_mode = 1;                // 1: fused persistent BPTT kernel (H <= 256); 0: two launches per timestep
 static int bwd_seq_mode() { return g_bwd_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
 constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
@@ -1521,6 +1522,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
 
 // ------------------------------------------------------------------------------------------ backward
 struct V2BwdWs {
+  f16* dgbuf[2]; float* csbuf[2];   // [layer & 1]: the weight-gradient GEMMs of layer l overlap the BPTT of layer l-1
   f16* dg[2]; float* dhs; float* dab[2]; float* cs; float* scale; unsigned int* mx; f16* whh_hi[2]; f16* wih_hi[2];
 };
 static uint64_t carve_bwd_ws(const V2Dims& d, void* base, uint64_t size, V2BwdWs* out) {
@@ -1528,13 +1530,15 @@ static uint64_t carve_bwd_ws(const V2Dims& d, void* base, uint64_t size, V2BwdWs
   V2BwdWs f{};
   int kpmax = 0;
   for (int l = 0; l < d.L; ++l) kpmax = d.kp_l(l) > kpmax ? d.kp_l(l) : kpmax;
-  f.dg[0] = w.take<f16>(d.ntok * d.nd * 4 * d.H);             // ONE plane [T*Bp][ndir*4H]: direction dd = columns [4H*dd, 4H*dd + 4H)
-  f.dg[1] = f.dg[0] + 4 * d.H;
+  // dG: ONE plane [T*Bp][ndir*4H] per buffer, direction dd = columns [4H*dd, 4H*dd + 4H)
+  f.dgbuf[0] = w.take<f16>(d.ntok * d.nd * 4 * d.H);
+  f.dgbuf[1] = d.L > 1 ? w.take<f16>(d.ntok * d.nd * 4 * d.H) : f.dgbuf[0];
   f.dhs = w.take<float>((int64_t)d.nd * d.Bp * d.H);
   for (int i = 0; i < 2; ++i) f.dab[i] = w.take<float>(d.ntok * d.nd * d.H);
   {
     const int cg = d.nd * d.H / 2, rpi = cg >= 256 ? 1 : 256 / cg;      // as colsum_dg_kernel splits its 256 threads
-    f.cs = w.take<float>((int64_t)kColsumBlocks * rpi * d.nd * 4 * d.H);   // per-(block, row phase) partial column sums
+    f.csbuf[0] = w.take<float>((int64_t)kColsumBlocks * rpi * d.nd * 4 * d.H);   // per-(block, row phase) partial column sums
+    f.csbuf[1] = d.L > 1 ? w.take<float>((int64_t)kColsumBlocks * rpi * d.nd * 4 * d.H) : f.csbuf[0];
   }
   f.scale = w.take<float>(4);
   f.mx = w.take<unsigned int>(4);
@@ -1545,6 +1549,23 @@ static uint64_t carve_bwd_ws(const V2Dims& d, void* base, uint64_t size, V2BwdWs
   return w.used + 256;
 }
 uint64_t gru_stack_bwd_workspace_v2(const tt_gru_stack_grad* a) { return carve_bwd_ws(dims_of(&a->fwd), nullptr, 0, nullptr); }
+
+// Helper stream per caller stream: the weight-gradient GEMMs + bias sums of layer l run here, concurrently with the
+// BPTT kernel of layer l-1 on the caller's stream (that kernel occupies one CTA per (row tile, direction), the GEMMs
+// get the remaining SMs).  Forked / joined with events, so to the caller all work stays ordered on its stream.
+struct SideStream { cudaStream_t caller, side; cudaEvent_t fork, done[2]; bool used; };
+static SideStream* side_for(cudaStream_t caller) {
+  static SideStream table[8];
+  static int n = 0;
+  for (int i = 0; i < n; ++i) if (table[i].caller == caller) return &table[i];
+  if (n == 8) return nullptr;
+  SideStream& t = table[n];
+  if (cudaStreamCreateWithFlags(&t.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+  if (cudaEventCreateWithFlags(&t.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  for (int i = 0; i < 2; ++i) if (cudaEventCreateWithFlags(&t.done[i], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  t.caller = caller; t.used = false;
+  return &table[n++];
+}
 
 int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
   const tt_gru_stack* fw = &a->fwd;
@@ -1576,8 +1597,17 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     TT_LAUNCH_CHECK();
     d_above = f.dab[(L - 1) & 1];
   }
+  static int num_sms_b = 0;
+  if (!num_sms_b) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms_b, cudaDevAttrMultiProcessorCount, dev)); }
+  const int bptt_ctas = MT * nd < num_sms_b ? MT * nd : num_sms_b;
+  const int free_ctas = num_sms_b - bptt_ctas;           // SMs the BPTT kernel of the next layer leaves idle
+  SideStream* side = (g_wgrad_overlap && L > 1 && free_ctas >= 32 && bwd_seq_mode() != 0 && (H == 64 || H == 128 || H == 256)) ? side_for(s) : nullptr;
+  bool pending[2] = {false, false};                      // side work still reading dgbuf[i] / csbuf[i]
   for (int l = L - 1; l >= 0; --l) {
     const int in = d.in_l(l), kp = d.kp_l(l);
+    const int pb = l & 1;
+    f.dg[0] = f.dgbuf[pb]; f.dg[1] = f.dgbuf[pb] + 4 * H; f.cs = f.csbuf[pb];
+    if (side && pending[pb]) { TT_CUDA(cudaStreamWaitEvent(s, side->done[pb], 0)); pending[pb] = false; }
     const bool has_next = l + 1 < L;
     for (int dd = 0; dd < nd; ++dd) {
       note_launch(); w_planes_kernel<<<gblocks((int64_t)3 * H * H), 256, 0, s>>>(wptr(fw, l, dd, 1), 3 * H, H, H, f.whh_hi[dd], nullptr);
@@ -1652,41 +1682,9 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }
 
     float* d_below = nullptr;                            // tiled dX for the layer below
-    {
-      // bias gradients: column sums of the whole dG plane (both directions in one pass)
-      const int C = dgp_pitch, cgs = C >> 3, rpi = cgs >= 256 ? 1 : 256 / cgs;
-      note_launch(); colsum_dg_kernel<<<kColsumBlocks, 256, 0, s>>>(f.dg[0], d.ntok, C, f.cs);
-      for (int dd = 0; dd < nd; ++dd) {
-        note_launch();
-        bias_grads_kernel<<<(unsigned)(4 * H / 32), 256, 0, s>>>(f.cs + dd * 4 * H, C, kColsumBlocks * rpi, f.scale, H,
-                                                              a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
-      }
-      TT_LAUNCH_CHECK();
-    }
-    for (int dd = 0; dd < nd; ++dd) {
-      const Planes dgp{(const bf16*)f.dg[dd], nullptr, dgp_pitch};
-      // dW_hh[3H,H] = dGH^T h_prev   (reduction over all tokens; h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
-      {
-        UmmaGemm g{};
-        g.A[0] = dgp;
-        g.B[0] = Planes{(const bf16*)(sv.hhi[l][dd] + (dd == 0 ? 0 : (int64_t)Bp * H)), nullptr, H};
-        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 1]; g.ldc = H; g.M = 3 * H; g.N = H; g.K = (int)d.ntok; g.nbatch = 1;
-        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
-        TT_TRY(umma_gemm(g, s));
-      }
-      // dW_ih[3H,In] = dGI^T X   (dGI = columns [0,2H) and [3H,4H) of the direction's dG columns)
-      {
-        UmmaGemm g{};
-        g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H;
-        g.B[0] = Planes{(const bf16*)sv.xhi[l], nullptr, kp};
-        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 0]; g.ldc = in; g.M = 3 * H; g.N = in; g.K = (int)d.ntok; g.nbatch = 1;
-        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
-        TT_TRY(umma_gemm(g, s));
-      }
-    }
     // dX = sum over directions of dGI W_ih, as ONE GEMM with the directions concatenated along the reduction:
     // A = plane columns {dir0: dr dz dn, dir1: dr dz dn} (two skipped dn*r blocks), B = W_ih rows stacked [ndir*3H][kp].
-    // Tiled for the layer below, or the API's batch-first fp32 d_x.
+    // Tiled for the layer below, or the API's batch-first fp32 d_x.  First, because the next layer's BPTT waits for it.
     if (l > 0 || a->d_x) {
       UmmaGemm g{};
       g.A[0] = Planes{(const bf16*)f.dg[0], nullptr, dgp_pitch}; g.a_seg = 2 * H; g.a_skip = H; g.a_seg2 = nd == 2 ? 5 * H : 0;
@@ -1702,13 +1700,65 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       }
       TT_TRY(umma_gemm(g, s));
     }
+    // weight and bias gradients of this layer: off the critical path.  With a layer below still to do they go to the
+    // helper stream (capped to the SMs its BPTT kernel leaves idle), otherwise they stay on the caller's stream.
+    const bool overlap = side != nullptr && l > 0;
+    cudaStream_t ws = s;
+    if (overlap) {
+      TT_CUDA(cudaEventRecord(side->fork, s));
+      TT_CUDA(cudaStreamWaitEvent(side->side, side->fork, 0));
+      ws = side->side;
+    }
+    const int cap = overlap ? free_ctas : 0;
+    {
+      // bias gradients: column sums of the whole dG plane (both directions in one pass)
+      const int C = dgp_pitch, cgs = C >> 3, rpi = cgs >= 256 ? 1 : 256 / cgs;
+      const int cblocks = overlap ? (free_ctas * 4 < kColsumBlocks ? free_ctas * 4 : kColsumBlocks) : kColsumBlocks;
+      note_launch(); colsum_dg_kernel<<<cblocks, 256, 0, ws>>>(f.dg[0], d.ntok, C, f.cs);
+      for (int dd = 0; dd < nd; ++dd) {
+        note_launch();
+        bias_grads_kernel<<<(unsigned)(4 * H / 32), 256, 0, ws>>>(f.cs + dd * 4 * H, C, cblocks * rpi, f.scale, H,
+                                                               a->d_weights[(l * nd + dd) * 4 + 2], a->d_weights[(l * nd + dd) * 4 + 3]);
+      }
+      TT_LAUNCH_CHECK();
+    }
+    for (int dd = 0; dd < nd; ++dd) {
+      const Planes dgp{(const bf16*)f.dg[dd], nullptr, dgp_pitch};
+      // dW_hh[3H,H] = dGH^T h_prev   (reduction over all tokens; h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
+      {
+        UmmaGemm g{};
+        g.A[0] = dgp;
+        g.B[0] = Planes{(const bf16*)(sv.hhi[l][dd] + (dd == 0 ? 0 : (int64_t)Bp * H)), nullptr, H};
+        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 1]; g.ldc = H; g.M = 3 * H; g.N = H; g.K = (int)d.ntok; g.nbatch = 1;
+        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
+        g.max_ctas = cap;
+        TT_TRY(umma_gemm(g, ws));
+      }
+      // dW_ih[3H,In] = dGI^T X   (dGI = columns [0,2H) and [3H,4H) of the direction's dG columns)
+      {
+        UmmaGemm g{};
+        g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H;
+        g.B[0] = Planes{(const bf16*)sv.xhi[l], nullptr, kp};
+        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 0]; g.ldc = in; g.M = 3 * H; g.N = in; g.K = (int)d.ntok; g.nbatch = 1;
+        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
+        g.max_ctas = cap;
+        TT_TRY(umma_gemm(g, ws));
+      }
+    }
+    if (overlap) { TT_CUDA(cudaEventRecord(side->done[pb], side->side)); pending[pb] = true; }
     d_above = d_below;
   }
+  for (int i = 0; i < 2; ++i)
+    if (side && pending[i]) TT_CUDA(cudaStreamWaitEvent(s, side->done[i], 0));   // join: the caller's stream sees every gradient
   return TT_OK;
 }
 
 }  // namespace tt
 
+extern "C" int tt_debug_wgrad_overlap(int32_t on) {
+  tt::g_wgrad_overlap = on ? 1 : 0;
+  return TT_OK;
+}
 extern "C" int tt_debug_seq_mode(int32_t mode) {
   if (mode != 0 && mode != 2 && mode != 4) { tt::set_error("tt_debug_seq_mode: 0, 2 or 4"); return TT_ERR_INVALID; }
   tt::g_seq_mode = mode;

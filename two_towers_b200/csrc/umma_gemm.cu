@@ -294,7 +294,7 @@ __global__ void prescale_kernel(float* C, int64_t ldc, int M, int N, float beta)
 }
 
 template <int BN, bool A_MN, bool B_MN, int NPASS>
-static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
+static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t s) {
   auto kern = umma_gemm_kernel<BN, A_MN, B_MN, NPASS>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -307,7 +307,8 @@ static int launch_cfg(const UmmaParams& p, int items, cudaStream_t s) {
     TT_CUDA(cudaGetDevice(&dev));
     TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  const int grid = items < num_sms ? items : num_sms;
+  const int cap = (max_ctas > 0 && max_ctas < num_sms) ? max_ctas : num_sms;
+  const int grid = items < cap ? items : cap;
   note_launch();
   ProfScope prof(PROF_GEMM_TC, s);
   kern<<<grid, kThreads, Cfg<BN, NPASS>::SMEM_BYTES, s>>>(p);
@@ -380,6 +381,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     return TT_ERR_INVALID;
   }
   out->kind = (BN == 128 ? 0 : 8) + (npass == 1 ? 4 : 0) + major;
+  out->max_ctas = g.max_ctas;
   return TT_OK;
 }
 
@@ -398,18 +400,18 @@ int umma_gemm_launch(const UmmaPrepared& prep, const int* a_row0, cudaStream_t s
   }
   const int items = prep.items;
   switch (prep.kind) {
-    case 0: return launch_cfg<128, false, false, 3>(p, items, s);
-    case 1: return launch_cfg<128, true, true, 3>(p, items, s);
-    case 2: return launch_cfg<128, false, true, 3>(p, items, s);
-    case 4: return launch_cfg<128, false, false, 1>(p, items, s);
-    case 5: return launch_cfg<128, true, true, 1>(p, items, s);
-    case 6: return launch_cfg<128, false, true, 1>(p, items, s);
-    case 8: return launch_cfg<256, false, false, 3>(p, items, s);
-    case 9: return launch_cfg<256, true, true, 3>(p, items, s);
-    case 10: return launch_cfg<256, false, true, 3>(p, items, s);
-    case 12: return launch_cfg<256, false, false, 1>(p, items, s);
-    case 13: return launch_cfg<256, true, true, 1>(p, items, s);
-    case 14: return launch_cfg<256, false, true, 1>(p, items, s);
+    case 0: return launch_cfg<128, false, false, 3>(p, items, prep.max_ctas, s);
+    case 1: return launch_cfg<128, true, true, 3>(p, items, prep.max_ctas, s);
+    case 2: return launch_cfg<128, false, true, 3>(p, items, prep.max_ctas, s);
+    case 4: return launch_cfg<128, false, false, 1>(p, items, prep.max_ctas, s);
+    case 5: return launch_cfg<128, true, true, 1>(p, items, prep.max_ctas, s);
+    case 6: return launch_cfg<128, false, true, 1>(p, items, prep.max_ctas, s);
+    case 8: return launch_cfg<256, false, false, 3>(p, items, prep.max_ctas, s);
+    case 9: return launch_cfg<256, true, true, 3>(p, items, prep.max_ctas, s);
+    case 10: return launch_cfg<256, false, true, 3>(p, items, prep.max_ctas, s);
+    case 12: return launch_cfg<256, false, false, 1>(p, items, prep.max_ctas, s);
+    case 13: return launch_cfg<256, true, true, 1>(p, items, prep.max_ctas, s);
+    case 14: return launch_cfg<256, false, true, 1>(p, items, prep.max_ctas, s);
   }
   set_error("umma_gemm: bad prepared kind %d", prep.kind);
   return TT_ERR_INVALID;

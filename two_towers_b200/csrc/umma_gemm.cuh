@@ -41,6 +41,7 @@ struct UmmaGemm {
   int32_t npass;       // 0/3: hi*hi + lo*hi + hi*lo ; 1: hi*hi only (lo planes unused)
   int64_t a_rows, b_rows;   // rows of the plane arrays the tensor maps cover (0: derived from M/N/K)
   int32_t a_row0, b_row0;   // K-major operands: first plane row of the problem (e.g. t*Bp for one timestep)
+  int32_t max_ctas;         // 0 = one CTA per SM; otherwise cap of the persistent grid (GEMMs co-scheduled with another kernel)
   int32_t a_seg2;           // optional second threshold of the remap below: i >= a_seg2 skips a_skip once more (K-major A)
   int32_t a_seg, a_skip;    // A column remap: logical index i >= a_seg reads plane column i + a_skip
                             //   (K-major A: i = k ; MN-major A: i = m).  Both multiples of 64 (128 for MN-major).
@@ -53,7 +54,7 @@ struct UmmaGemm {
 int umma_gemm(const UmmaGemm& g, cudaStream_t s);
 // encode the tensor maps / pick the configuration once, launch many times (per-timestep GEMMs only change the first
 // plane row of A, given per batched problem)
-struct UmmaPrepared { alignas(64) unsigned char blob[1408]; int kind, items; };
+struct UmmaPrepared { alignas(64) unsigned char blob[1408]; int kind, items, max_ctas; };
 int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out);
 int umma_gemm_launch(const UmmaPrepared& p, const int* a_row0, cudaStream_t s);
 
