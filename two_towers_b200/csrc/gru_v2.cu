@@ -75,13 +75,22 @@ __device__ __forceinline__ void split8(const float (&x)[8], uint4& hi, uint4& lo
   lo = make_uint4(pack_h2(l[0], l[1]), pack_h2(l[2], l[3]), pack_h2(l[4], l[5]), pack_h2(l[6], l[7]));
 }
 
-// 16-bit fixed point for saved gates: r, z in [0,1] -> u16 ; n in [-1,1], q = h - n in [-2,2] -> s16
-__device__ __forceinline__ uint32_t q_u16(float x) { return __float2uint_rn(__saturatef(x) * 65535.f); }
+// 16-bit fixed point for saved gates: r, z in [0,1] -> u16 ; n in [-1,1], q = h - n in [-2,2] -> 16-bit offset binary
+// (stored = round(x * scale) + 32768).  Conversions go through the mantissa of 2^23 (magic-number add / or) on the
+// FMA and ALU pipes: F2I / I2F issue at 16 per clock and SM on the XU pipe, which was the busiest pipe of both
+// persistent kernels (it also carries the ex2 / rcp of the gate activations).
+__device__ __forceinline__ uint32_t q_u16(float x) { return __float_as_uint(fmaf(__saturatef(x), 65535.f, 8388608.f)) & 0xFFFFu; }
 __device__ __forceinline__ uint32_t q_s16(float x, float scale) {
-  return (uint32_t)(__float2int_rn(fminf(fmaxf(x * scale, -32767.f), 32767.f))) & 0xFFFFu;
+  const float lim = 32767.f / scale;
+  return __float_as_uint(fmaf(fminf(fmaxf(x, -lim), lim), scale, 8388608.f + 32768.f)) & 0xFFFFu;
 }
-__device__ __forceinline__ float dq_u16(uint32_t v) { return (float)(v & 0xFFFFu) * (1.f / 65535.f); }
-__device__ __forceinline__ float dq_s16(uint32_t v, float inv_scale) { return (float)(int16_t)(v & 0xFFFFu) * inv_scale; }
+__device__ __forceinline__ float dq_u16(uint32_t v) {                      // low 16 bits of v
+  constexpr float c = 1.f / 65535.f;
+  return fmaf(__uint_as_float((v & 0xFFFFu) | 0x4B000000u), c, -8388608.f * c);   // == float(v16) * c, one rounding
+}
+__device__ __forceinline__ float dq_s16(uint32_t v, float inv_scale) {
+  return (__uint_as_float((v & 0xFFFFu) | 0x4B000000u) - (8388608.f + 32768.f)) * inv_scale;
+}
 constexpr float kNScale = 32767.f, kQScale = 16383.5f;
 
 // ------------------------------------------------------------------------------------------ operand producers
