@@ -131,6 +131,38 @@ def test_gru_stack_backward_vs_torch_autograd(engine, B, T, In, H, use_len):
         assert rel_err(w.grad, p.grad) < engine.grad, (n, rel_err(w.grad, p.grad))
 
 
+@pytest.mark.parametrize("overlap", [1, 0])
+def test_gru_three_layer_backward_helper_stream(overlap):
+    """3 layers: the weight-gradient GEMMs of layers 2 and 1 run on the library's helper stream under the BPTT of the
+    layer below (double-buffered dG plane, buffer reuse at layer 0 waits for layer 2's GEMMs); same gradients with the
+    overlap switched off, both equal to nn.GRU in float64."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    torch.manual_seed(5)
+    B, T, In, H, NL = 140, 6, 40, 64, 3
+    ref = torch.nn.GRU(In, H, num_layers=NL, batch_first=True, bidirectional=True).double()
+    x = torch.randn(B, T, In, dtype=torch.float64, requires_grad=True)
+    o, hn = ref(x)
+    go, gh = torch.randn_like(o), torch.randn_like(hn)
+    (o * go).sum().add((hn * gh).sum()).backward()
+    ws = [p.detach().float().to(DEV).requires_grad_(True) for p in ref.parameters()]
+    xg = x.detach().float().to(DEV).requires_grad_(True)
+    try:
+        lib.tt_debug_wgrad_overlap(overlap)
+        for _ in range(2):                                   # twice: helper stream / events are reused
+            for w in ws:
+                w.grad = None
+            xg.grad = None
+            o2, hn2 = Fn.gru_stack(xg, ws, In, H, NL, True)
+            ((o2 * go.float().to(DEV)).sum() + (hn2 * gh.float().to(DEV)).sum()).backward()
+            torch.cuda.synchronize()
+            assert rel_err(xg.grad, x.grad) < 1e-3
+            for (n, p), w in zip(ref.named_parameters(), ws):
+                assert rel_err(w.grad, p.grad) < 1e-3, (n, rel_err(w.grad, p.grad))
+    finally:
+        lib.tt_debug_wgrad_overlap(1)
+
+
 def test_gru_token_ids_equal_pregathered_floats(engine):
     torch.manual_seed(1)
     table = torch.randn(40, 12)
