@@ -1,0 +1,22 @@
+"""Retrieval scan alone (the `eval` leg of bench.py): Q queries x N docs, top-10; prints ms and queries/s.
+Under `ncu --metrics gpu__time_duration.sum` it gives the launch list of one scan."""
+import sys, torch
+sys.path.insert(0, ".")
+import two_towers_b200 as tt
+Q = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+N = int(sys.argv[2]) if len(sys.argv) > 2 else 1_100_000
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+dev = torch.device("cuda")
+g = torch.Generator(device=dev).manual_seed(1)
+q = torch.nn.functional.normalize(torch.randn(Q, 128, device=dev, generator=g), dim=1)
+docs = torch.nn.functional.normalize(torch.randn(N, 128, device=dev, generator=g), dim=1)
+tt.search_topk(q, docs, 10)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(reps):
+    v, i = tt.search_topk(q, docs, 10)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / reps
+print(f"Q={Q} N={N}: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s, {2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic")

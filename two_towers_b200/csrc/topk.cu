@@ -234,26 +234,50 @@ __global__ void select_rows_kernel(const float* __restrict__ S, int64_t ld, int 
   int ti = __shfl_sync(0xffffffffu, li, K2 - 1);
   const float rinv = cosine ? invx[row] : 1.f;
   const float* s = S + (int64_t)r * ld;
-  for (int c = 0; c < nc; c += 32) {
-    const int cl = c + lane;
-    const int64_t cg = c0 + cl;
-    float sc = -INFINITY;
-    if (cl < nc) {
-      sc = s[cl];
-      if (cosine) sc = (sc * rinv) * invy[cg];
-      if (mask_pos_offset >= 0 && cg == mask_pos_offset + row) sc = -1.f;
-      if (sc != sc) sc = INFINITY;                           // NaN (fp16 overflow of an operand): force the exact route
+  // 128 columns per iteration (one 16-byte load per lane); the common case - nothing beats the row's K2-th best - costs
+  // one vote.  ld and c0 are multiples of 4, so the vector loads are aligned; columns >= nc of the tile row are masked.
+  for (int c = 0; c < nc; c += 128) {
+    const int cl0 = c + 4 * lane;
+    const int64_t cg0 = c0 + cl0;
+    float sc[4];
+    {
+      const float4 v = cl0 < nc ? *reinterpret_cast<const float4*>(s + cl0) : make_float4(0.f, 0.f, 0.f, 0.f);
+      sc[0] = v.x; sc[1] = v.y; sc[2] = v.z; sc[3] = v.w;
     }
-    unsigned m = __ballot_sync(0xffffffffu, sc > -INFINITY && better(sc, (int)cg, tv, ti));
-    while (m) {
-      const int b = __ffs(m) - 1;
-      m &= m - 1;
-      const float cv = __shfl_sync(0xffffffffu, sc, b);
-      const int ci = (int)(c0 + c + b);
-      if (better(cv, ci, tv, ti)) {
-        list_insert(lv, li, cv, ci, lane);
-        tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
-        ti = __shfl_sync(0xffffffffu, li, K2 - 1);
+    if (cosine) {
+      float iy[4];
+      if (cl0 + 3 < nc) {
+        const float4 w = *reinterpret_cast<const float4*>(invy + cg0);
+        iy[0] = w.x; iy[1] = w.y; iy[2] = w.z; iy[3] = w.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) iy[j] = cl0 + j < nc ? invy[cg0 + j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sc[j] = (sc[j] * rinv) * iy[j];
+    }
+    bool any = false;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (mask_pos_offset >= 0 && cg0 + j == mask_pos_offset + row) sc[j] = -1.f;
+      if (sc[j] != sc[j]) sc[j] = INFINITY;                  // NaN (fp16 overflow of an operand): force the exact route
+      if (cl0 + j >= nc) sc[j] = -INFINITY;
+      any |= sc[j] > -INFINITY && better(sc[j], (int)(cg0 + j), tv, ti);
+    }
+    if (!__ballot_sync(0xffffffffu, any)) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      unsigned m = __ballot_sync(0xffffffffu, sc[j] > -INFINITY && better(sc[j], (int)(cg0 + j), tv, ti));
+      while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1;
+        const float cv = __shfl_sync(0xffffffffu, sc[j], b);
+        const int ci = (int)(c0 + c + 4 * b + j);
+        if (better(cv, ci, tv, ti)) {
+          list_insert(lv, li, cv, ci, lane);
+          tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
+          ti = __shfl_sync(0xffffffffu, li, K2 - 1);
+        }
       }
     }
   }

@@ -35,7 +35,8 @@ struct Cfg {
   static constexpr int STAGE_BYTES = NPLANES * (A_BYTES + B_BYTES);
   static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 6 ? 6 : (200 * 1024) / STAGE_BYTES;
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int TR_BYTES = 8 * 32 * 32 * 4;           // one 32x32 fp32 transpose tile per epilogue warp
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + TR_BYTES;
 };
 
 template <int BN, bool A_MN, bool B_MN, int NPASS>
@@ -49,6 +50,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]
   uint64_t* tempty = tfull + 2;                // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* tr_smem = reinterpret_cast<float*>(smem + C_::STAGES * C_::STAGE_BYTES + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int MT = (p.M + UBM - 1) / UBM, NT = (p.N + BN - 1) / BN, KB = (p.K + UBK - 1) / UBK;
@@ -186,6 +188,29 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
         const int gn0 = n_blk * BN + c0;
+        // plain row-major store of a full 32-column block: transpose the warp's 32x32 block through shared memory so
+        // that 8 lanes write one 128-byte row segment (a TMEM lane is a row: direct stores would put 32 rows, 16 bytes
+        // each, into every instruction).  All conditions are warp-uniform.
+        if (p.epi == 0 && p.splitk == 1 && p.beta == 0.f && p.rm_Bp == 0 && vec_ok && gn0 + 32 <= p.N && kb0 < kb1) {
+          float* T = tr_smem + (warp - 2) * 1024;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 o = make_float4(alpha * v[4 * j], alpha * v[4 * j + 1], alpha * v[4 * j + 2], alpha * v[4 * j + 3]);
+            if (bias) { o.x += bias[gn0 + 4 * j]; o.y += bias[gn0 + 4 * j + 1]; o.z += bias[gn0 + 4 * j + 2]; o.w += bias[gn0 + 4 * j + 3]; }
+            *reinterpret_cast<float4*>(T + lane * 32 + ((j ^ (lane & 7)) << 2)) = o;
+          }
+          __syncwarp();
+          const int c4 = lane & 7, rsub = lane >> 3;
+          float* cbase = p.C[bz] + (int64_t)(m_blk * UBM + quarter * 32) * p.ldc + gn0 + 4 * c4;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + rsub;
+            const float4 o = *reinterpret_cast<const float4*>(T + rr * 32 + ((c4 ^ (rr & 7)) << 2));
+            if (m_blk * UBM + quarter * 32 + rr < p.M) *reinterpret_cast<float4*>(cbase + (int64_t)rr * p.ldc) = o;
+          }
+          __syncwarp();
+          continue;
+        }
         if (row_ok && gn0 < p.N && kb0 < kb1) {
           if (p.epi == 1) {
             const int hc4 = p.tl_Hc >> 2;
