@@ -13,6 +13,7 @@
 // (lane r = rank r).  Because the filter and the insertion use the same total order, the result does not
 // depend on the order in which threads report candidates: ties always resolve to the lowest index.
 #include <limits.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "simt_tile.cuh"
 #include "umma_gemm.cuh"
@@ -236,12 +237,14 @@ __global__ void select_rows_kernel(const float* __restrict__ S, int64_t ld, int 
   const float* s = S + (int64_t)r * ld;
   // 128 columns per iteration (one 16-byte load per lane); the common case - nothing beats the row's K2-th best - costs
   // one vote.  ld and c0 are multiples of 4, so the vector loads are aligned; columns >= nc of the tile row are masked.
+  float4 vnext = 4 * lane < nc ? *reinterpret_cast<const float4*>(s + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
   for (int c = 0; c < nc; c += 128) {
     const int cl0 = c + 4 * lane;
     const int64_t cg0 = c0 + cl0;
     float sc[4];
     {
-      const float4 v = cl0 < nc ? *reinterpret_cast<const float4*>(s + cl0) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 v = vnext;                                  // loaded one iteration ahead
+      if (cl0 + 128 < nc) vnext = *reinterpret_cast<const float4*>(s + cl0 + 128);
       sc[0] = v.x; sc[1] = v.y; sc[2] = v.z; sc[3] = v.w;
     }
     if (cosine) {
@@ -342,12 +345,16 @@ using namespace tt;
 
 extern "C" {
 
-// tensor route tiling: S tile = QT x NC fp32 <= 48 MiB, so that the tile written by the GEMM is still in the 126 MB L2
+// tensor route tiling: S tile = QT x NC fp32 <= 64 MiB (TT_TOPK_TILE_MB), so that the tile written by the GEMM is still in the 126 MB L2
 // when the selection kernel reads it
 static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma_available() && N >= 256 && N < INT_MAX - 64 && k + kCandSlack <= 32; }
 static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
+static inline int64_t topk_tile_bytes() {
+  static int64_t v = []() { const char* e = getenv("TT_TOPK_TILE_MB"); int mb = e ? atoi(e) : 0; return (int64_t)(mb > 0 ? mb : 64) << 20; }();
+  return v;
+}
 static inline int64_t topk_nc(int Q, int64_t N) {
-  int64_t nc = (48ll << 20) / (4ll * topk_qt(Q));
+  int64_t nc = topk_tile_bytes() / (4ll * topk_qt(Q));
   nc = nc / 256 * 256;
   if (nc > 65536) nc = 65536;
   return nc < N ? nc : (N + 7) / 8 * 8;
