@@ -35,11 +35,13 @@ def parse():
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=5)
-    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--impl", default="ours", choices=["ours", "reference", "torch-gpu"])
     p.add_argument("--batch", type=int, default=4096, help="pairs per GPU (4096 = the BASELINE config)")
     p.add_argument("--vocab", type=int, default=3_000_000)
     p.add_argument("--cpu-batch", type=int, default=256, help="pairs per step of the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
+                   help="fused = this repo's tt_opt_step Adam kernel (FusedAdam); torch = torch.optim.Adam(fused=True)")
     p.add_argument("--serial-towers", action="store_true", help="both towers on one stream (for per-kernel launch lists)")
     p.add_argument("--eval-queries", type=int, default=8192, help="queries of the retrieval leg (0 = skip it)")
     p.add_argument("--eval-docs", type=int, default=1_100_000, help="corpus rows per GPU of the retrieval leg (C5 shard)")
@@ -165,6 +167,78 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+# ----------------------------------------------------------------------------------------- stock torch on the GPU
+def run_torch_gpu(args):
+    """Extra arm (SURVEY 8d "the real beat-it bar"), not part of the driver contract: the reference's architecture
+    (enhanced_two_tower.py:14-65: nn.GRU bi x2 + Linear/LayerNorm/ReLU/Linear heads), its in-batch margin loss
+    (:90-101) and cosine + topk mining (:123-133) written with STOCK torch modules and run on cuda:0 - cuDNN GRU,
+    cuBLAS - on the same workload as the default arm (ids gathered from the same-sized table on the device).
+    Nothing of this repo's library and nothing under oracle/ is on this path.  One JSON line per cuDNN TF32 setting."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    dev = torch.device("cuda", 0)
+    B, V = args.batch, args.vocab
+
+    class Stock(nn.Module):
+        def __init__(self):
+            super().__init__()
+            mk = lambda: nn.GRU(E, GRU_H, num_layers=2, batch_first=True, bidirectional=True, dropout=0.1)
+            hd = lambda: nn.Sequential(nn.Linear(4 * HID, 2 * HID), nn.LayerNorm(2 * HID), nn.ReLU(), nn.Linear(2 * HID, HID))
+            self.query_encoder, self.doc_encoder, self.query_proj, self.doc_proj = mk(), mk(), hd(), hd()
+
+        def enc(self, x, gru, proj):
+            _, h = gru(x)
+            return proj(torch.cat([h[-2], h[-1]], dim=1))
+
+        def forward(self, q, d):
+            return self.enc(q, self.query_encoder, self.query_proj), self.enc(d, self.doc_encoder, self.doc_proj)
+
+    gen = torch.Generator().manual_seed(1234)
+    table = torch.empty(V, E, device=dev).normal_(0, 0.1, generator=torch.Generator(device=dev).manual_seed(7))
+    table[0] = 0
+    ids = [(make_ids(B, TQ, V, gen).to(dev), make_ids(B, TD, V, gen).to(dev)) for _ in range(4)]
+    eye = torch.eye(B, device=dev)
+    for tf32 in (True, False):
+        torch.backends.cudnn.allow_tf32 = tf32
+        torch.manual_seed(0)
+        model = Stock().to(dev).train()
+        opt = torch.optim.Adam(model.parameters(), fused=True)
+
+        def step(qi, di):
+            opt.zero_grad(set_to_none=True)
+            qv, dv = model(F.embedding(qi, table), F.embedding(di, table))
+            sim = qv @ dv.t() / 0.1
+            sim = sim - 0.2 * (1 - eye)
+            loss = F.cross_entropy(sim, torch.arange(B, device=dev))
+            with torch.no_grad():
+                cs = F.normalize(qv, dim=1, eps=1e-8) @ F.normalize(dv, dim=1, eps=1e-8).t()
+                cs.fill_diagonal_(-1.0)
+                hard = cs.topk(TOPK, dim=1).indices
+            loss.backward()
+            opt.step()
+            return loss, hard
+
+        for i in range(args.warmup):
+            step(*ids[i % 4])
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(args.steps):
+            loss, _ = step(*ids[i % 4])
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.steps
+        print(json.dumps({"impl": "torch-gpu", "metric": METRIC, "value": B / (ms * 1e-3), "unit": "pairs/s", "n_gpus": 1,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+                          "dtype": "f32 (cuDNN GRU, allow_tf32=%s; cuBLAS matmul fp32)" % tf32, "data": "synthetic",
+                          "config": workload_config(B, 1, V), "loss": loss.item(),
+                          "note": "stock torch nn.GRU/nn.Linear/LayerNorm/cross_entropy/topk on the GPU; not this repo's kernels"}),
+              flush=True)
+        del model, opt
+
+
 # ----------------------------------------------------------------------------------------- this repo's arm
 def seq_kernel_work(B):
     """Algorithmic work of the persistent recurrence kernels per train step (both towers, 2 layers, 2 directions);
@@ -288,7 +362,7 @@ def run_ours(args):
     model.overlap_towers = not args.serial_towers
     lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
     crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
-    opt = torch.optim.Adam(model.parameters(), fused=True)
+    opt = tt.FusedAdam(model.parameters()) if args.optimizer == "fused" else torch.optim.Adam(model.parameters(), fused=True)
     reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None
     nb = 4
     host = [(make_ids(B, TQ, V, gen).pin_memory(), make_ids(B, TD, V, gen).pin_memory()) for _ in range(nb)]
@@ -361,6 +435,12 @@ def run_ours(args):
             ev.record(copy_stream)
         return qd, dd, ev
 
+    # the loss of step i goes to a pinned host slot with an async copy right after the step is queued and is READ on
+    # the host while step i+1 runs (one-step-late logging, as a training loop would do it): one D2H read per step
+    # inside the timed region, but the host never drains the launch queue between steps
+    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+    losses = []
     barrier()
     t0 = time.perf_counter()
     nxt = upload(0)
@@ -371,7 +451,14 @@ def run_ours(args):
         st.wait_event(ev)
         qd.record_stream(st); dd.record_stream(st)
         loss, _ = step(qd, dd)
-        loss_val = loss.item()
+        loss_host[i & 1].copy_(loss.detach(), non_blocking=True)
+        loss_ev[i & 1].record(st)
+        if i > 0:
+            loss_ev[(i - 1) & 1].synchronize()
+            losses.append(float(loss_host[(i - 1) & 1]))
+    loss_ev[(args.steps - 1) & 1].synchronize()
+    losses.append(float(loss_host[(args.steps - 1) & 1]))
+    loss_val = losses[-1]
     barrier()
     e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
     if world > 1:
@@ -385,7 +472,9 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 accumulate; forward GEMMs as 3 fp16 hi/lo tensor passes, backward GEMMs 1 fp16 pass",
             "data": "synthetic", "config": workload_config(B, world, V),
-            "e2e": {"value": e2e_val, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+            "e2e": {"value": e2e_val, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "note": "wall clock over K steps through the nn.Module API: pinned int64 ids -> device on a copy stream "
+                            "(one step ahead), every step's loss copied to pinned memory and read on the host one step late"},
             "gpu_launches": launches, "clocks": clocks, "loss": loss_val,
             "engine": lib.tt_engine().decode(),
             "step_tflops_per_gpu": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12,
@@ -420,4 +509,4 @@ def workload_config(B, world, V):
 
 if __name__ == "__main__":
     a = parse()
-    run_reference(a) if a.impl == "reference" else run_ours(a)
+    {"reference": run_reference, "torch-gpu": run_torch_gpu, "ours": run_ours}[a.impl](a)

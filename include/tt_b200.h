@@ -234,6 +234,54 @@ int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, 
 int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D,
                  float margin, float gscale, float* dq, float* dpos, float* dneg, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * N4  fused clip_grad_norm_ + Adam / AdamW step over a parameter list.  Replaces
+ * torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=1.0) + optimizer.step():
+ * simple_two_tower.py:193,239 (AdamW lr 1e-4 wd 0.01), train_margin.py:64-67 (Adam + clip), train_enhanced.py:43.
+ * `tensors` and `chunks` are DEVICE arrays the host builds once per parameter set: every tensor is covered by
+ * chunks of at most TT_OPT_CHUNK elements (chunk = tensor index + element offset; offsets multiples of 4).
+ * Math (per element, torch's single-tensor Adam): g *= coef; AdamW: p *= 1 - lr*wd, Adam: g += wd*p;
+ * m += (g-m)(1-b1); v = b2 v + (1-b2) g^2; p -= lr/bc1 * m / (sqrt(v)/sqrt(bc2) + eps).
+ * flags: TT_OPT_NORM  norm_out[0] = total L2 norm of the gradients of THIS table, norm_out[1] = clip coefficient
+ *                     min(1, max_norm / (norm + 1e-6))  (1 when max_norm <= 0); needs the workspace
+ *        TT_OPT_STEP  run the update
+ *        TT_OPT_CLIP  the update scales every gradient by norm_out[1] (from this or an earlier call - several
+ *                     parameter groups share one norm) and stores the scaled gradient back, as clip_grad_norm_ does */
+#define TT_OPT_CHUNK 65536
+#define TT_OPT_NORM 1
+#define TT_OPT_STEP 2
+#define TT_OPT_CLIP 4
+typedef struct { float* param; float* grad; float* exp_avg; float* exp_avg_sq; int64_t numel; } tt_opt_tensor;
+typedef struct { int32_t tensor; int32_t reserved; int64_t offset; } tt_opt_chunk;
+typedef struct {
+  const tt_opt_tensor* tensors; const tt_opt_chunk* chunks;
+  int32_t ntensors, nchunks, flags, decoupled_wd;      /* decoupled_wd: 1 = AdamW, 0 = Adam (L2 folded into the gradient) */
+  float lr, beta1, beta2, eps, weight_decay, max_norm;
+  float bias_correction1, bias_correction2_sqrt;       /* 1 - beta1^t and sqrt(1 - beta2^t) for this step t >= 1 (host) */
+  float* norm_out;                                     /* device [2] */
+  void* workspace; uint64_t workspace_bytes;
+} tt_opt_args;
+uint64_t tt_opt_step_workspace(int32_t nchunks);
+int tt_opt_step(const tt_opt_args* a, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * N1  host input pipeline: text -> token ids.  HOST functions taking HOST pointers - the one exception to
+ * the device-pointer convention above.  Replaces the per-word CPU embedding lookup of SimpleDataset.text_to_embedding
+ * (simple_two_tower.py:88-110 == enhanced_two_tower.py:144-166): `words = text.lower().split()[:max_len]`, words not
+ * in the vocabulary are skipped, the row is padded at the END with pad_id (the table row that reads as zeros).
+ * Vocabulary: nwords UTF-8 words, word i = words_blob[word_offsets[i] .. word_offsets[i+1]); its id is ids[i] (ids == NULL:
+ * i).  Texts are passed the same way (UTF-8 blob + ntexts+1 offsets); ASCII letters are lower-cased, whitespace is
+ * Python's str.isspace() set.  mode 0 = reference order (truncate to max_len words, then drop unknown words),
+ * mode 1 = drop unknown words, then truncate.  out_ids [ntexts, max_len] int32 or int64, out_lengths [ntexts] (may be
+ * NULL) = number of real tokens per row.  nthreads <= 0: all host threads. */
+typedef struct tt_vocab tt_vocab;
+tt_vocab* tt_vocab_create(const char* words_blob, const int64_t* word_offsets, int64_t nwords, const int32_t* ids);
+void tt_vocab_destroy(tt_vocab* v);
+int64_t tt_vocab_size(const tt_vocab* v);
+int tt_tokenize_batch(const tt_vocab* v, const char* text_blob, const int64_t* text_offsets, int64_t ntexts,
+                      int32_t max_len, int64_t pad_id, int32_t mode, int32_t ids_are_i64, void* out_ids,
+                      int32_t* out_lengths, int32_t nthreads);
+
 /* plain fp32 GEMM used by the ops above, exported for kernel-level tests:
  * C[M,N] = alpha * A[M,K] * B[N,K]^T + beta * C + bias[N]   (bias may be NULL) */
 int tt_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,

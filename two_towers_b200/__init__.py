@@ -8,6 +8,9 @@ from .losses import (InfoNCELoss, MarginRankingLoss, SymmetricInfoNCELoss, get_h
                      get_hard_negatives_batch)
 from .models import (EnhancedTwoTower, EnhancedTwoTowerModel, SimpleTwoTower, TokenTwoTowerModel,  # noqa: F401
                      TwoTowerModel)
-from .retrieval import encode_corpus, mrr_recall, search_topk, sharded_search_topk  # noqa: F401
+from .optim import FusedAdam, FusedAdamW, load_checkpoint, save_checkpoint  # noqa: F401
+from .pipeline import PinnedIdRing, Vocabulary, id_batches  # noqa: F401
+from .retrieval import (SearchService, encode_corpus, load_doc_embeddings, load_or_compute_doc_embeddings,  # noqa: F401
+                        mrr_recall, save_doc_embeddings, search_topk, sharded_search_topk)
 
 __version__ = "0.1.0"

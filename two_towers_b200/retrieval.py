@@ -60,3 +60,76 @@ def encode_corpus(model, docs, batch_size=4096, which="doc", lengths=None):
         outs.append(enc(docs[i:i + batch_size], ln) if ln is not None else enc(docs[i:i + batch_size]))
     model.train(was_training)
     return torch.cat(outs, 0)
+
+
+# ------------------------------------------------------------------------------------------- N2: embedding cache
+def save_doc_embeddings(path, doc_embeddings):
+    """The reference's on-disk cache is the bare [N,D] tensor (`torch.save(doc_embeddings, DOC_EMBEDDINGS_CACHE)`,
+    server/python-api/app.py:65)."""
+    torch.save(doc_embeddings, path)
+
+
+def load_doc_embeddings(path, device):
+    """`torch.load(DOC_EMBEDDINGS_CACHE, map_location=device)` (app.py:49)."""
+    t = torch.load(path, map_location=device)
+    if not torch.is_tensor(t) or t.dim() != 2:
+        raise ValueError(f"{path}: expected a 2-D tensor of document embeddings")
+    return t.float().contiguous()
+
+
+@torch.no_grad()
+def load_or_compute_doc_embeddings(model, doc_ids, cache_path=None, batch_size=4096):
+    """app.py:41-67 (`load_or_compute_doc_embeddings`) with the batch-1 encode loop replaced by `encode_corpus`.
+    doc_ids: int ids [N,T] (CPU or device; moved batch by batch)."""
+    import os
+    dev = next(model.parameters()).device
+    if cache_path is not None and os.path.exists(cache_path):
+        return load_doc_embeddings(cache_path, dev)
+    outs = []
+    was_training = model.training
+    model.eval()
+    for i in range(0, doc_ids.shape[0], batch_size):
+        outs.append(model.encode_doc(doc_ids[i:i + batch_size].to(dev, non_blocking=True)))
+    model.train(was_training)
+    emb = torch.cat(outs, 0) if outs else torch.empty(0, 0, device=dev)
+    if cache_path is not None:
+        save_doc_embeddings(cache_path, emb)
+    return emb
+
+
+# ------------------------------------------------------------------------------------------- N3: serving path
+class SearchService:
+    """The `/search` handler of server/python-api/app.py:85-120 without the web framework: query text -> ids ->
+    encode_query -> cosine top-k over the cached document embeddings (K-H with Q = 1) -> the response schema of
+    app.py:72-83 (`{"query", "results": [{"text", "score", "is_ground_truth", "rank"}]}`; text cut to 200 chars + "...").
+    `query_to_docs` maps a query string to its ground-truth documents (app.py:29-37)."""
+
+    def __init__(self, model, vocab, docs, max_length=30, top_k=3, cache_path=None, query_to_docs=None,
+                 margin_preprocessing=False, batch_size=4096):
+        self.model, self.vocab, self.docs = model.eval(), vocab, list(docs)
+        self.max_length, self.top_k = max_length, top_k
+        self.query_to_docs = query_to_docs or {}
+        self._enc = (lambda texts: vocab.encode_margin_batch(texts, max_length)) if margin_preprocessing else \
+            (lambda texts: vocab.encode_batch(texts, max_length))
+        self.device = next(model.parameters()).device
+        import os
+        if cache_path is not None and os.path.exists(cache_path):
+            self.doc_embeddings = load_doc_embeddings(cache_path, self.device)
+        else:
+            self.doc_embeddings = load_or_compute_doc_embeddings(model, self._enc(self.docs), cache_path, batch_size)
+        if self.doc_embeddings.shape[0] != len(self.docs):
+            raise ValueError("cached document embeddings do not match the document list")
+
+    @torch.no_grad()
+    def search(self, query, top_k=None):
+        k = min(top_k or self.top_k, len(self.docs))
+        ids = self._enc([query]).to(self.device)
+        qv = self.model.encode_query(ids)
+        scores, idx = search_topk(qv, self.doc_embeddings, k=k, cosine=True)
+        truth = self.query_to_docs.get(query, [])
+        results = []
+        for r, (i, s) in enumerate(zip(idx[0].tolist(), scores[0].tolist())):
+            text = self.docs[i]
+            results.append({"text": text[:200] + "..." if len(text) > 200 else text, "score": float(s),
+                            "is_ground_truth": text in truth, "rank": r + 1})
+        return {"query": query, "results": results}
