@@ -396,8 +396,10 @@ def run_ours(args):
     sampler.mark_begin()
     k0 = lib.tt_kernel_launches()
     e0.record(st)
+    th0 = time.perf_counter()
     for i in range(args.steps):
         loss, _ = step(*resident[i % nb])
+    host_launch_ms = (time.perf_counter() - th0) * 1e3 / args.steps     # host time to QUEUE a step (no sync inside)
     e1.record(st)
     barrier()
     launches = int(lib.tt_kernel_launches() - k0)
@@ -441,25 +443,41 @@ def run_ours(args):
     loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
     loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
     losses = []
+    dbg = os.environ.get("TT_E2E_DEBUG") == "1"
+    marks = []
     barrier()
     t0 = time.perf_counter()
     nxt = upload(0)
+    t_up0 = time.perf_counter()
     for i in range(args.steps):
+        ta = time.perf_counter()
         qd, dd, ev = nxt
         if i + 1 < args.steps:
             nxt = upload(i + 1)
         st.wait_event(ev)
         qd.record_stream(st); dd.record_stream(st)
+        tb = time.perf_counter()
         loss, _ = step(qd, dd)
+        tc = time.perf_counter()
         loss_host[i & 1].copy_(loss.detach(), non_blocking=True)
         loss_ev[i & 1].record(st)
         if i > 0:
             loss_ev[(i - 1) & 1].synchronize()
             losses.append(float(loss_host[(i - 1) & 1]))
+        if dbg:
+            marks.append((round((tb - ta) * 1e3, 2), round((tc - tb) * 1e3, 2), round((time.perf_counter() - tc) * 1e3, 2)))
+    t_loop = time.perf_counter()
     loss_ev[(args.steps - 1) & 1].synchronize()
     losses.append(float(loss_host[(args.steps - 1) & 1]))
+    if dbg and rank == 0:
+        print("e2e ms: first upload %.2f, loop %.2f, last loss %.2f" % ((t_up0 - t0) * 1e3, (t_loop - t_up0) * 1e3,
+                                                                        (time.perf_counter() - t_loop) * 1e3), file=sys.stderr)
+        print("e2e per-step host ms (upload, launch of the step, loss copy + wait for the previous loss):", marks, file=sys.stderr)
     loss_val = losses[-1]
+    t_b = time.perf_counter()
     barrier()
+    if dbg and rank == 0:
+        print("e2e ms: closing barrier %.2f" % ((time.perf_counter() - t_b) * 1e3), file=sys.stderr)
     e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
@@ -475,7 +493,7 @@ def run_ours(args):
             "e2e": {"value": e2e_val, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "note": "wall clock over K steps through the nn.Module API: pinned int64 ids -> device on a copy stream "
                             "(one step ahead), every step's loss copied to pinned memory and read on the host one step late"},
-            "gpu_launches": launches, "clocks": clocks, "loss": loss_val,
+            "gpu_launches": launches, "host_queue_ms_per_step": host_launch_ms, "clocks": clocks, "loss": loss_val,
             "engine": lib.tt_engine().decode(),
             "step_tflops_per_gpu": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12,
             "step_frac_of_bf16_sustained": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],

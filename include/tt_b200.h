@@ -203,6 +203,12 @@ int tt_score_ce_fwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
 int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
                     float inv_temp, float margin, const float* row_lse, float gscale,
                     float* dx, float* dy, void* workspace, uint64_t workspace_bytes, void* stream);
+/* same, with the upstream gradient left on the device: the effective scale is gscale * (*gscale_dev) (gscale_dev may be
+ * NULL).  loss.backward() hands the library a device scalar; reading it on the host would drain the launch queue at the
+ * start of every backward pass. */
+int tt_score_ce_bwd_dev(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
+                        float inv_temp, float margin, const float* row_lse, float gscale, const float* gscale_dev,
+                        float* dx, float* dy, void* workspace, uint64_t workspace_bytes, void* stream);
 
 /* K-F / K-H  row-wise exact-fp32 top-k of  score(i,j) = <x_i,y_j>  (mode 0)  or cosine (mode 1, norms
  * clamped at 1e-8 like F.cosine_similarity).  Every dot product is one fp32 FMA chain over d = 0..D-1 in
@@ -233,6 +239,9 @@ int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, 
                  float margin, float* row_loss, void* stream);
 int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D,
                  float margin, float gscale, float* dq, float* dpos, float* dneg, void* stream);
+int tt_hinge_bwd_dev(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D,
+                     float margin, float gscale, const float* gscale_dev, float* dq, float* dpos, float* dneg,
+                     void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * N4  fused clip_grad_norm_ + Adam / AdamW step over a parameter list.  Replaces
@@ -256,8 +265,9 @@ typedef struct { int32_t tensor; int32_t reserved; int64_t offset; } tt_opt_chun
 typedef struct {
   const tt_opt_tensor* tensors; const tt_opt_chunk* chunks;
   int32_t ntensors, nchunks, flags, decoupled_wd;      /* decoupled_wd: 1 = AdamW, 0 = Adam (L2 folded into the gradient) */
-  float lr, beta1, beta2, eps, weight_decay, max_norm;
-  float bias_correction1, bias_correction2_sqrt;       /* 1 - beta1^t and sqrt(1 - beta2^t) for this step t >= 1 (host) */
+  /* hyper-parameters as doubles: torch derives 1-beta, lr/bc1, 1-lr*wd in double and rounds ONCE to fp32 - so does this */
+  double lr, beta1, beta2, eps, weight_decay, max_norm;
+  double bias_correction1, bias_correction2_sqrt;      /* 1 - beta1^t and sqrt(1 - beta2^t) for this step t >= 1 (host) */
   float* norm_out;                                     /* device [2] */
   void* workspace; uint64_t workspace_bytes;
 } tt_opt_args;

@@ -54,6 +54,8 @@ int main(void){
   printf("%zu %zu\n", offsetof(tt_gru_layer_grad,d_out), offsetof(tt_head_grad,d_out));
   printf("%zu %zu %zu %zu %zu %zu\n", sizeof(tt_gru_stack), sizeof(tt_gru_stack_grad), offsetof(tt_gru_stack,x),
          offsetof(tt_gru_stack,seed), offsetof(tt_gru_stack,saved_bytes), offsetof(tt_gru_stack_grad,d_weights));
+  printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(tt_opt_tensor), sizeof(tt_opt_chunk), sizeof(tt_opt_args), offsetof(tt_opt_chunk,offset),
+         offsetof(tt_opt_args,lr), offsetof(tt_opt_args,bias_correction2_sqrt), offsetof(tt_opt_args,workspace_bytes));
   return 0; }
 '''
     with tempfile.TemporaryDirectory() as d:
@@ -69,6 +71,9 @@ int main(void){
            H.seed.offset, H.v_lo.offset, H.norm.offset, GG.d_out.offset, HG.d_out.offset]
     S, SG = _lib.GruStack, _lib.GruStackGrad
     exp += [ctypes.sizeof(S), ctypes.sizeof(SG), S.x.offset, S.seed.offset, S.saved_bytes.offset, SG.d_weights.offset]
+    from two_towers_b200 import optim as O
+    exp += [ctypes.sizeof(O.OptTensor), ctypes.sizeof(O.OptChunk), ctypes.sizeof(O.OptStep), O.OptChunk.offset.offset,
+            O.OptStep.lr.offset, O.OptStep.bias_correction2_sqrt.offset, O.OptStep.workspace_bytes.offset]
     assert out == exp
 
 

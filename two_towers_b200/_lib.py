@@ -103,6 +103,8 @@ SIGNATURES = {
     "tt_score_ce_workspace": (u64, [i32, i32, i32]),
     "tt_score_ce_fwd": (C.c_int, [P, i32, P, i32, i32, i32, F, F, P, P, P, u64, P]),
     "tt_score_ce_bwd": (C.c_int, [P, i32, P, i32, i32, i32, F, F, P, F, P, P, P, u64, P]),
+    "tt_score_ce_bwd_dev": (C.c_int, [P, i32, P, i32, i32, i32, F, F, P, F, P, P, P, P, u64, P]),
+    "tt_hinge_bwd_dev": (C.c_int, [P, P, P, i32, i32, i32, F, F, P, P, P, P, P]),
     "tt_rows_topk_workspace": (u64, [i32, i64, i32, i32]),
     "tt_rows_topk": (C.c_int, [P, i32, P, i64, i32, i32, i32, i64, i64, P, P, P, u64, P]),
     "tt_topk_merge": (C.c_int, [P, P, i32, i32, i32, P, P, P]),

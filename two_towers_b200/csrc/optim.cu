@@ -65,18 +65,18 @@ __global__ void __launch_bounds__(256) opt_finish_norm_kernel(const float* __res
   }
 }
 
-struct AdamConsts {
-  float lr, beta1, beta2, eps, wd, step_size, bc2_sqrt;
+struct AdamConsts {       // every derived constant is formed in double on the host and rounded once, as torch does
+  float decay, wd, omb1, beta2, omb2, eps, step_size, bc2_sqrt;
   int decoupled, store_grad;
 };
 
 __device__ __forceinline__ void adam_one(float& p, float& g, float& m, float& v, float coef, const AdamConsts& c) {
   g *= coef;
   float gg = g;
-  if (c.decoupled) p *= 1.f - c.lr * c.wd;          // AdamW: param.mul_(1 - lr * wd)
+  if (c.decoupled) p *= c.decay;                     // AdamW: param.mul_(1 - lr * wd)
   else if (c.wd != 0.f) gg = fmaf(c.wd, p, gg);      // Adam: grad.add(param, alpha=wd)
-  m = m + (gg - m) * (1.f - c.beta1);                // exp_avg.lerp_(grad, 1 - beta1)
-  v = fmaf(1.f - c.beta2, gg * gg, v * c.beta2);     // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  m = m + (gg - m) * c.omb1;                         // exp_avg.lerp_(grad, 1 - beta1)
+  v = fmaf(c.omb2, gg * gg, v * c.beta2);            // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
   const float denom = sqrtf(v) / c.bc2_sqrt + c.eps;
   p -= c.step_size * (m / denom);
 }
@@ -132,9 +132,9 @@ int tt_opt_step(const tt_opt_args* a, void* stream) {
   TT_CHECK_ARG(a->ntensors >= 0 && a->nchunks >= 0, "opt_step: negative counts");
   if (a->nchunks == 0) return TT_OK;
   TT_CHECK_ARG(a->tensors && a->chunks, "opt_step: null tensor / chunk table");
-  TT_CHECK_ARG(a->lr >= 0.f && a->eps >= 0.f && a->beta1 >= 0.f && a->beta1 < 1.f && a->beta2 >= 0.f && a->beta2 < 1.f,
+  TT_CHECK_ARG(a->lr >= 0.0 && a->eps >= 0.0 && a->beta1 >= 0.0 && a->beta1 < 1.0 && a->beta2 >= 0.0 && a->beta2 < 1.0,
                "opt_step: lr/eps/betas out of range");
-  TT_CHECK_ARG(a->bias_correction1 > 0.f && a->bias_correction2_sqrt > 0.f, "opt_step: bias corrections must be > 0 (step >= 1)");
+  TT_CHECK_ARG(a->bias_correction1 > 0.0 && a->bias_correction2_sqrt > 0.0, "opt_step: bias corrections must be > 0 (step >= 1)");
   const bool do_norm = (a->flags & TT_OPT_NORM) != 0, do_step = (a->flags & TT_OPT_STEP) != 0;
   const bool clip = (a->flags & TT_OPT_CLIP) != 0;
   TT_CHECK_ARG(!(do_norm || clip) || a->norm_out, "opt_step: TT_OPT_NORM / TT_OPT_CLIP need norm_out");
@@ -146,15 +146,16 @@ int tt_opt_step(const tt_opt_args* a, void* stream) {
     opt_sqnorm_kernel<<<(unsigned)a->nchunks, 256, 0, s>>>(a->tensors, a->chunks, partial);
     TT_LAUNCH_CHECK();
     tt::note_launch();
-    opt_finish_norm_kernel<<<1, 256, 0, s>>>(partial, a->nchunks, a->max_norm, a->norm_out);
+    opt_finish_norm_kernel<<<1, 256, 0, s>>>(partial, a->nchunks, (float)a->max_norm, a->norm_out);
     TT_LAUNCH_CHECK();
   }
   if (!do_step) return TT_OK;
   AdamConsts c;
-  c.lr = a->lr; c.beta1 = a->beta1; c.beta2 = a->beta2; c.eps = a->eps; c.wd = a->weight_decay;
-  c.step_size = a->lr / a->bias_correction1;
-  c.bc2_sqrt = a->bias_correction2_sqrt;
-  c.decoupled = a->decoupled_wd != 0 && a->weight_decay != 0.f;
+  c.decay = (float)(1.0 - a->lr * a->weight_decay); c.wd = (float)a->weight_decay;
+  c.omb1 = (float)(1.0 - a->beta1); c.beta2 = (float)a->beta2; c.omb2 = (float)(1.0 - a->beta2); c.eps = (float)a->eps;
+  c.step_size = (float)(a->lr / a->bias_correction1);
+  c.bc2_sqrt = (float)a->bias_correction2_sqrt;
+  c.decoupled = a->decoupled_wd != 0 && a->weight_decay != 0.0;
   c.store_grad = clip ? 1 : 0;
   tt::note_launch();
   opt_adam_kernel<<<(unsigned)a->nchunks, 256, 0, s>>>(a->tensors, a->chunks, clip ? a->norm_out : nullptr, c);

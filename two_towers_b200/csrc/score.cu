@@ -59,7 +59,8 @@ __global__ void ce_finish_kernel(const float* run_max, const float* run_sum, con
 }
 // in place: S <- (softmax - onehot) * coef
 __global__ void ce_grad_kernel(float* __restrict__ S, int ld, int Bl, int c0, int nc, int pos_offset, float margin,
-                               const float* __restrict__ row_lse, float coef) {
+                               const float* __restrict__ row_lse, float coef, const float* __restrict__ coef_dev) {
+  if (coef_dev) coef *= __ldg(coef_dev);
   const int64_t total = (int64_t)Bl * nc;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int row = (int)(i / nc), c = (int)(i % nc);
@@ -142,8 +143,10 @@ __device__ __forceinline__ void dot3(const float* a, const float* b, int D, int 
 }
 template <bool BWD>
 __global__ void hinge_kernel(const float* __restrict__ q, const float* __restrict__ pos, const float* __restrict__ neg,
-                             int B, int k, int D, float margin, float gscale, float* __restrict__ row_loss,
-                             float* __restrict__ dq, float* __restrict__ dpos, float* __restrict__ dneg) {
+                             int B, int k, int D, float margin, float gscale, const float* __restrict__ gscale_dev,
+                             float* __restrict__ row_loss, float* __restrict__ dq, float* __restrict__ dpos,
+                             float* __restrict__ dneg) {
+  if (BWD && gscale_dev) gscale *= __ldg(gscale_dev);
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= B) return;
   const float eps = 1e-8f;
@@ -242,6 +245,13 @@ int tt_score_ce_fwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
 int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
                     float inv_temp, float margin, const float* row_lse, float gscale, float* dx, float* dy,
                     void* workspace, uint64_t workspace_bytes, void* stream) {
+  return tt_score_ce_bwd_dev(x, Bl, y, Bg, D, pos_offset, inv_temp, margin, row_lse, gscale, nullptr, dx, dy, workspace,
+                             workspace_bytes, stream);
+}
+
+int tt_score_ce_bwd_dev(const float* x, int32_t Bl, const float* y, int32_t Bg, int32_t D, int32_t pos_offset,
+                        float inv_temp, float margin, const float* row_lse, float gscale, const float* gscale_dev,
+                        float* dx, float* dy, void* workspace, uint64_t workspace_bytes, void* stream) {
   TT_CHECK_ARG(x && y && row_lse && dx && dy && Bl > 0 && Bg > 0 && D > 0, "score_ce_bwd: bad args");
   cudaStream_t s = (cudaStream_t)stream;
   const int NC = chunk_cols(Bl, Bg);
@@ -274,14 +284,14 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
       gx.A[0] = Planes{(const bf16*)sp.gh, (const bf16*)sp.gl, sp.ncp};
       gx.B[0] = Planes{(const bf16*)(sp.yh + (int64_t)c0 * sp.dp), (const bf16*)(sp.yl + (int64_t)c0 * sp.dp), sp.dp};
       gx.C[0] = dx; gx.ldc = D; gx.M = Bl; gx.N = D; gx.K = nc; gx.nbatch = 1; gx.a_mn = false; gx.b_mn = true;
-      gx.alpha = 1.f / lift; gx.beta = c0 == 0 ? 0.f : 1.f; gx.splitk = 0; gx.f16 = 1; gx.npass = 3;
+      gx.alpha = 1.f / lift; gx.alpha_ptr = gscale_dev; gx.beta = c0 == 0 ? 0.f : 1.f; gx.splitk = 0; gx.f16 = 1; gx.npass = 3;
       TT_TRY(umma_gemm(gx, s));
       // dy[c0:c0+nc, D] = G^T X                     (both operands MN-major: reduction over the Bl rows)
       UmmaGemm gy{};
       gy.A[0] = Planes{(const bf16*)sp.gh, (const bf16*)sp.gl, sp.ncp};
       gy.B[0] = Planes{(const bf16*)sp.xh, (const bf16*)sp.xl, sp.dp};
       gy.C[0] = dy + (int64_t)c0 * D; gy.ldc = D; gy.M = nc; gy.N = D; gy.K = Bl; gy.nbatch = 1; gy.a_mn = gy.b_mn = true;
-      gy.alpha = 1.f / lift; gy.beta = 0.f; gy.splitk = 0; gy.f16 = 1; gy.npass = 3;
+      gy.alpha = 1.f / lift; gy.alpha_ptr = gscale_dev; gy.beta = 0.f; gy.splitk = 0; gy.f16 = 1; gy.npass = 3;
       TT_TRY(umma_gemm(gy, s));
       continue;
     }
@@ -292,7 +302,7 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
     TT_TRY(gemm_f32(g, s));
     int64_t tot = (int64_t)Bl * nc, nb = ceil_div(tot, 256);
     if (nb > 148 * 16) nb = 148 * 16;
-    tt::note_launch(); ce_grad_kernel<<<(unsigned)nb, 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, row_lse, gscale * inv_temp);
+    tt::note_launch(); ce_grad_kernel<<<(unsigned)nb, 256, 0, s>>>(S, NC, Bl, c0, nc, pos_offset, margin, row_lse, gscale * inv_temp, gscale_dev);
     // dx[Bl,D] (+)= G[Bl,nc] Y[c0:c0+nc, D]
     GemmArgs gx{};
     gx.A[0] = S; gx.B[0] = y + (int64_t)c0 * D; gx.C[0] = dx;
@@ -313,16 +323,20 @@ int tt_score_ce_bwd(const float* x, int32_t Bl, const float* y, int32_t Bg, int3
 int tt_hinge_fwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D, float margin,
                  float* row_loss, void* stream) {
   TT_CHECK_ARG(q && pos && neg && row_loss && B > 0 && k > 0 && D > 0, "hinge_fwd: bad args");
-  tt::note_launch(); hinge_kernel<false><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, 0.f,
+  tt::note_launch(); hinge_kernel<false><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, 0.f, nullptr,
                                                                                 row_loss, nullptr, nullptr, nullptr);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
 int tt_hinge_bwd(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D, float margin,
                  float gscale, float* dq, float* dpos, float* dneg, void* stream) {
+  return tt_hinge_bwd_dev(q, pos, neg, B, k, D, margin, gscale, nullptr, dq, dpos, dneg, stream);
+}
+int tt_hinge_bwd_dev(const float* q, const float* pos, const float* neg, int32_t B, int32_t k, int32_t D, float margin,
+                     float gscale, const float* gscale_dev, float* dq, float* dpos, float* dneg, void* stream) {
   TT_CHECK_ARG(q && pos && neg && dq && dpos && dneg && B > 0 && k > 0 && D > 0, "hinge_bwd: bad args");
   tt::note_launch(); hinge_kernel<true><<<(unsigned)ceil_div(B, 8), 256, 0, (cudaStream_t)stream>>>(q, pos, neg, B, k, D, margin, gscale,
-                                                                               nullptr, dq, dpos, dneg);
+                                                                               gscale_dev, nullptr, dq, dpos, dneg);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }

@@ -286,8 +286,11 @@ class ScoreCEFunction(torch.autograd.Function):
         Bg = y.shape[0]
         dx, dy = torch.empty_like(x), torch.empty_like(y)
         ws = L.workspace(lib.tt_score_ce_workspace(Bl, Bg, D), x.device)
-        L.check(lib.tt_score_ce_bwd(L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_lse),
-                                    float(g), L.ptr(dx), L.ptr(dy), ws.data_ptr(), ws.numel(), L.stream()), "tt_score_ce_bwd")
+        # the upstream gradient stays on the device (float(g) would drain the launch queue at the start of every backward)
+        g = L.f32c(g)
+        L.check(lib.tt_score_ce_bwd_dev(L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_lse),
+                                        1.0, L.ptr(g), L.ptr(dx), L.ptr(dy), ws.data_ptr(), ws.numel(), L.stream()),
+                "tt_score_ce_bwd_dev")
         return dx, dy, None, None, None
 
 
@@ -316,8 +319,9 @@ class HingeFunction(torch.autograd.Function):
         q, pos, neg = ctx.saved_tensors
         B, D = q.shape
         dq, dpos, dneg = torch.empty_like(q), torch.empty_like(pos), torch.empty_like(neg)
-        L.check(lib.tt_hinge_bwd(L.ptr(q), L.ptr(pos), L.ptr(neg), B, ctx.k, D, ctx.margin, float(g), L.ptr(dq),
-                                 L.ptr(dpos), L.ptr(dneg), L.stream()), "tt_hinge_bwd")
+        g = L.f32c(g)
+        L.check(lib.tt_hinge_bwd_dev(L.ptr(q), L.ptr(pos), L.ptr(neg), B, ctx.k, D, ctx.margin, 1.0, L.ptr(g), L.ptr(dq),
+                                     L.ptr(dpos), L.ptr(dneg), L.stream()), "tt_hinge_bwd_dev")
         return dq, dpos, dneg, None
 
 

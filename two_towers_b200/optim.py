@@ -33,9 +33,9 @@ class OptChunk(C.Structure):
 class OptStep(C.Structure):
     _fields_ = [("tensors", C.c_void_p), ("chunks", C.c_void_p),
                 ("ntensors", C.c_int32), ("nchunks", C.c_int32), ("flags", C.c_int32), ("decoupled_wd", C.c_int32),
-                ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
-                ("weight_decay", C.c_float), ("max_norm", C.c_float),
-                ("bias_correction1", C.c_float), ("bias_correction2_sqrt", C.c_float),
+                ("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
+                ("weight_decay", C.c_double), ("max_norm", C.c_double),
+                ("bias_correction1", C.c_double), ("bias_correction2_sqrt", C.c_double),
                 ("norm_out", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_uint64)]
 
 
@@ -58,11 +58,15 @@ def build_tables(entries):
 
 
 class _Table:
+    """Device copies of the two tables.  Uploaded from PINNED memory with non-blocking copies: a pageable cudaMemcpy
+    would block the host until everything queued before it (the whole backward pass) has run."""
+
     def __init__(self, entries, device):
         tb, cb, self.nchunks = build_tables(entries)
         self.ntensors = len(entries)
-        self.tensors = tb.to(device)
-        self.chunks = cb.to(device)
+        self._host = (tb.pin_memory(), cb.pin_memory())          # kept alive with the table
+        self.tensors = self._host[0].to(device, non_blocking=True)
+        self.chunks = self._host[1].to(device, non_blocking=True)
         self.ws = L.workspace(L.lib().tt_opt_step_workspace(self.nchunks), device)
 
 
@@ -110,11 +114,15 @@ class FusedAdam(torch.optim.Optimizer):
     def _table(self, key, entries, device):
         sig = tuple((p.data_ptr(), p.grad.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel())
                     for p, st in entries)
-        hit = self._tables.get(key)
-        if hit is None or hit[0] != sig:
-            hit = (sig, _Table(list(sig), device))
-            self._tables[key] = hit
-        return hit[1]
+        # gradients are fresh allocations after zero_grad(set_to_none=True); the caching allocator hands out a small
+        # set of recurring addresses, so a few tables per group are kept instead of rebuilding one every step
+        cache = self._tables.setdefault(key, {})
+        tab = cache.get(sig)
+        if tab is None:
+            if len(cache) >= 8:
+                cache.pop(next(iter(cache)))
+            tab = cache[sig] = _Table(list(sig), device)
+        return tab
 
     @torch.no_grad()
     def step(self, closure=None):
