@@ -361,6 +361,10 @@ def run_ours(args):
     model.attach_embeddings(table, pad_id=0)
     model.overlap_towers = not args.serial_towers
     lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
+    if os.environ.get("TT_BWD_SEQ_MODE"):
+        lib.tt_debug_bwd_seq_mode(int(os.environ["TT_BWD_SEQ_MODE"]))
+    if os.environ.get("TT_BWD_SEGMENTS"):
+        lib.tt_debug_bwd_segments(int(os.environ["TT_BWD_SEGMENTS"]))
     crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
     opt = tt.FusedAdam(model.parameters()) if args.optimizer == "fused" else torch.optim.Adam(model.parameters(), fused=True)
     reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None

@@ -316,13 +316,21 @@ int tt_debug_step_buffer(void* buf);
 /* forward recurrence of the v2 pipeline: 4 (default) / 2 = ONE persistent cooperative kernel for all timesteps of a
  * layer with 4 / 2 epilogue warps per TMEM lane quarter; 0 = one launch per timestep.  Test / measurement aid. */
 int tt_debug_seq_mode(int32_t mode);
-/* BPTT of the v2 pipeline: 1 (default) = fused persistent kernel (dL/dh resident in tensor memory, hidden size <= 256),
+/* BPTT of the v2 pipeline: 2 (default) = fused persistent kernel (dL/dh resident in tensor memory, hidden size <= 256),
+ * run on 2-CTA clusters when the hidden size is 256 and the pairs fit in half the SMs (each CTA owns half the hidden
+ * units; staged gate-gradient tiles are exchanged through distributed shared memory: lower latency per timestep, more
+ * SM-time); 3 = CTA pairs whenever the hidden size is 256; 1 = always one CTA per (row tile, direction);
  * 0 = gate-gradient kernel + dh GEMM per timestep. */
 int tt_debug_bwd_seq_mode(int32_t mode);
 /* 1 (default): in a multi-layer backward the weight / bias gradient GEMMs of layer l run on a library-owned helper stream,
  * concurrently with the BPTT kernel of layer l-1, and are joined back into the caller's stream before the call returns
  * (to the caller all work stays ordered on its stream).  0: everything on the caller's stream (per-kernel timing). */
 int tt_debug_wgrad_overlap(int32_t on);
+/* time segments of the fused BPTT (default 4; 1 = one launch per layer): the sequence runs as n launches of the persistent
+ * kernel and the weight-gradient GEMMs over a finished segment's tokens run on the helper stream under the next segment,
+ * which takes them off the critical path for every layer.  Needs tt_debug_wgrad_overlap(1); sequences shorter than 16*n
+ * steps use fewer segments. */
+int tt_debug_bwd_segments(int32_t n);
 
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);

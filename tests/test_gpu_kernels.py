@@ -163,6 +163,89 @@ def test_gru_three_layer_backward_helper_stream(overlap):
         lib.tt_debug_wgrad_overlap(1)
 
 
+@pytest.mark.parametrize("B,T,In,H,NL,nseg,use_len", [(140, 48, 40, 64, 2, 4, False), (130, 64, 24, 128, 1, 4, True),
+                                                        (70, 33, 300, 256, 2, 2, True), (260, 80, 16, 64, 3, 5, False),
+                                                        (140, 48, 40, 64, 2, 1, False)])
+def test_gru_backward_time_segments(B, T, In, H, NL, nseg, use_len):
+    """Fused BPTT run as `nseg` launches of the persistent kernel (dL/dh handed over through global memory) with the
+    weight-gradient GEMMs of each finished segment accumulated on the helper stream: same gradients as nn.GRU in
+    float64, for every layer count (1 layer = the helper stream is used although there is no layer below)."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    torch.manual_seed(B + T)
+    ref = torch.nn.GRU(In, H, num_layers=NL, batch_first=True, bidirectional=True).double()
+    x = torch.randn(B, T, In, dtype=torch.float64, requires_grad=True)
+    lens = torch.randint(1, T + 1, (B,)) if use_len else None
+    if use_len:
+        pk = torch.nn.utils.rnn.pack_padded_sequence(x, lens, batch_first=True, enforce_sorted=False)
+        o, hn = ref(pk)
+        o, _ = torch.nn.utils.rnn.pad_packed_sequence(o, batch_first=True, total_length=T)
+    else:
+        o, hn = ref(x)
+    go, gh = torch.randn_like(o), torch.randn_like(hn)
+    (o * go).sum().add((hn * gh).sum()).backward()
+    ws = [p.detach().float().to(DEV).requires_grad_(True) for p in ref.parameters()]
+    xg = x.detach().float().to(DEV).requires_grad_(True)
+    try:
+        lib.tt_debug_bwd_segments(nseg)
+        for _ in range(2):
+            for w in ws:
+                w.grad = None
+            xg.grad = None
+            o2, hn2 = Fn.gru_stack(xg, ws, In, H, NL, True, lengths=lens)
+            ((o2 * go.float().to(DEV)).sum() + (hn2 * gh.float().to(DEV)).sum()).backward()
+            torch.cuda.synchronize()
+            assert rel_err(xg.grad, x.grad) < 1e-3
+            for (n, p), w in zip(ref.named_parameters(), ws):
+                assert rel_err(w.grad, p.grad) < 1e-3, (n, rel_err(w.grad, p.grad))
+    finally:
+        lib.tt_debug_bwd_segments(4)
+
+
+@pytest.mark.parametrize("B,T,In,NL,use_len,drop", [(70, 9, 40, 2, True, 0.0), (300, 17, 300, 2, False, 0.0),
+                                                     (131, 33, 24, 1, True, 0.0), (200, 12, 64, 3, False, 0.25)])
+def test_gru_backward_cta_pairs(B, T, In, NL, use_len, drop):
+    """H = 256: the BPTT on 2-CTA clusters (hidden units split over the pair, gate-gradient tiles exchanged through
+    distributed shared memory; mode 3) gives the gradients of nn.GRU in float64 and - same saved state, same dropout
+    stream - the gradients of the one-CTA kernel (mode 1) up to the summation order of the fp32 accumulators."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    H = 256
+    torch.manual_seed(B + T)
+    ref = torch.nn.GRU(In, H, num_layers=NL, batch_first=True, bidirectional=True).double()
+    x = torch.randn(B, T, In, dtype=torch.float64, requires_grad=True)
+    lens = torch.randint(1, T + 1, (B,)) if use_len else None
+    go = torch.randn(B, T, 2 * H, dtype=torch.float64)
+    gh = torch.randn(NL * 2, B, H, dtype=torch.float64)
+    if drop == 0.0:
+        if use_len:
+            pk = torch.nn.utils.rnn.pack_padded_sequence(x, lens, batch_first=True, enforce_sorted=False)
+            o, hn = ref(pk)
+            o, _ = torch.nn.utils.rnn.pad_packed_sequence(o, batch_first=True, total_length=T)
+        else:
+            o, hn = ref(x)
+        (o * go).sum().add((hn * gh).sum()).backward()
+    grads = {}
+    try:
+        for mode in (3, 1):
+            lib.tt_debug_bwd_seq_mode(mode)
+            ws = [p.detach().float().to(DEV).requires_grad_(True) for p in ref.parameters()]
+            xg = x.detach().float().to(DEV).requires_grad_(True)
+            torch.manual_seed(77)                                     # same Philox seed for both modes
+            o2, hn2 = Fn.gru_stack(xg, ws, In, H, NL, True, lengths=lens, dropout_p=drop, training=drop > 0)
+            ((o2 * go.float().to(DEV)).sum() + (hn2 * gh.float().to(DEV)).sum()).backward()
+            torch.cuda.synchronize()
+            grads[mode] = [xg.grad.clone()] + [w.grad.clone() for w in ws]
+            if drop == 0.0:
+                assert rel_err(xg.grad, x.grad) < 1e-3
+                for (n, p), w in zip(ref.named_parameters(), ws):
+                    assert rel_err(w.grad, p.grad) < 1e-3, (mode, n, rel_err(w.grad, p.grad))
+    finally:
+        lib.tt_debug_bwd_seq_mode(2)
+    for a, b in zip(grads[3], grads[1]):
+        assert rel_err(a, b) < 2e-4, rel_err(a, b)
+
+
 def test_gru_token_ids_equal_pregathered_floats(engine):
     torch.manual_seed(1)
     table = torch.randn(40, 12)

@@ -165,7 +165,10 @@ unsigned long long* g_step_dbg = nullptr;
 static int g_seq_mode = 4;                    // 0: one launch per timestep; 2 / 4: persistent kernel, epilogue warps per quarter
 static int seq_mode() { return g_seq_mode; }
 static int g_wgrad_overlap = 1;               // 1: weight-gradient GEMMs of layer l overlap the BPTT of layer l-1 (helper stream)
-static int g_bwd_seq_mode = 1;                // 1: fused persistent BPTT kernel (H <= 256); 0: two launches per timestep
+static int g_bwd_seq_mode = 2;                // 2: fused persistent BPTT, on CTA pairs when H == 256 and the pairs fit in half the SMs;
+                                              // 3: CTA pairs whenever H == 256; 1: always one CTA per (row tile, direction) (H <= 256);
+                                              // 0: two launches per timestep
+static int g_bwd_segments = 1;                // time segments per fused BPTT (weight gradients of a finished segment overlap the next one)
 static int bwd_seq_mode() { return g_bwd_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
 constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
 constexpr int S_A_BYTES = S_BM * S_BK * 2, S_B_BYTES = S_BN * S_BK * 2;
@@ -861,6 +864,11 @@ struct alignas(64) BwdSeqParams {
   float drop_p, inv_keep;
   uint64_t seed;
   unsigned long long* dbg;
+  // time segment of this launch: BPTT steps step_begin-1, step_begin-2, ..., step_end (step s is timestep s of the
+  // forward direction, T-1-s of the reverse one).  A whole sequence is (T, 0).  dhs_out (may alias dhs0, may be null):
+  // dL/dh after the segment's last step, in the dhs0 layout - the next segment's launch starts from it.
+  int32_t step_begin, step_end;
+  float* dhs_out;
 };
 #define BWD_MARK(itv, slot)                                                              \
   do {                                                                                   \
@@ -939,7 +947,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
       int stage = 0, phase = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
         const int dir = tile / MT;
-        for (int step = 0; step < T; ++step)
+        for (int step = p.step_end; step < p.step_begin; ++step)
           for (int c = 0; c < NCH; ++c)
             for (int g = 0; g < 3; ++g) {
               mbar_wait(&wempty[stage], phase ^ 1);
@@ -957,7 +965,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
       constexpr uint32_t idesc = make_idesc_f16(128, H, 0, 1);
       int stage = 0, phase = 0, it = 0, use = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-        for (int step = 0; step < T; ++step, ++it) {
+        for (int step = p.step_end; step < p.step_begin; ++step, ++it) {
           const uint32_t d_tmem = tmem_base + ((it & 1) ^ 1) * 256;        // buf[nxt]
           mbar_wait(init_done, it & 1);
           tc_fence_after();
@@ -988,9 +996,9 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
       int use = 0;
       for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
         const int mt = tile % MT, dir = tile / MT, m0 = mt * 128;
-        for (int step = T - 1; step >= 0; --step) {
+        for (int step = p.step_begin - 1; step >= p.step_end; --step) {
           const int t = dir == 0 ? step : T - 1 - step;
-          if (step > 0) {
+          if (step > p.step_end) {
             // pull the NEXT step's saved-gate records (contiguous per (dir, t, row tile)) into L2 one whole step ahead:
             // the cell threads' loads then see L2 latency instead of HBM latency
             const int tn = dir == 0 ? step - 1 : T - step;
@@ -1053,7 +1061,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         }
         tmem_wait_st();
       }
-      for (int step = T - 1; step >= 0; --step, ++it) {
+      for (int step = p.step_begin - 1; step >= p.step_end; --step, ++it) {
         if (e == 0) BWD_MARK(it, 14);
         const int t = dir == 0 ? step : T - 1 - step;
         const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
@@ -1075,7 +1083,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
           for (int i = 0; i < 4; ++i) da[i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (e == 0) BWD_MARK(it, 0);
-        if (step != T - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+        if (step != p.step_begin - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
         if (e == 0) BWD_MARK(it, 1);
         // ---------------- pass 1: dht = dh (+ d_above); buf[cur] <- dht; buf[nxt] <- dht * z
         // (tcgen05.ld / .st are warp-collective: every lane executes them; only the VALUES depend on `live`)
@@ -1187,11 +1195,377 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
 #undef TT_GRAD_HALF
         use += NCH;
       }
+      // ---- hand dL/dh to the next time segment: after the last step it lives in buf[it & 1] (that step's buf[nxt])
+      if (p.dhs_out && p.step_begin > p.step_end) {
+        mbar_wait(acc_full, (it - 1) & 1);
+        tc_fence_after();
+        float4* dst = reinterpret_cast<float4*>(p.dhs_out) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float v[16];
+          tmem_ld16v(lane_base + (it & 1) * 256 + 64 * c + 16 * sub, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[(int64_t)(16 * c + 4 * sub + i) * 128] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == R_WARP_MMA) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------ fused BPTT, CTA pairs
+// H = 256 only.  The (row tile, direction) work item of gru_bwd_seq_kernel is split over a 2-CTA cluster by hidden
+// units: CTA r owns units [128 r, 128 r + 128) - their dL/dh accumulators (2 x 128 TMEM columns), their gate
+// gradients (2 chunks of 64 units per step instead of 4) and their 128 output columns of dh_prev = dG W_hh.  That
+// product reduces over ALL 768 gate units, so every staged chunk of gate gradients (dr | dz | dn*r tiles, 48 KB) is
+// also copied into the peer's landing slot with one shared::cta -> shared::cluster bulk copy that completes on the
+// peer's mbarrier; the peer's MMA thread consumes it like a TMA load and reports the slot free again through a
+// multicast tcgen05.commit.  Halves the per-SM gate-gradient work (the bound of the single-CTA kernel: instruction
+// issue / latency of 32 Ki gate units per timestep on one SM) and doubles the SMs in use.
+constexpr int P_WSTAGE = 64 * 128 * 2;             // one k-block of W_hh for this CTA's outputs: [64 k][128 n] fp16 = 16 KB
+constexpr int P_WSTAGES = 3;
+constexpr int P_LAND = 3 * 16384;                  // landing slot: the peer's dr | dz | dn*r tiles of one chunk
+constexpr int P_SMEM = P_WSTAGES * P_WSTAGE + 2 * R_STG + P_LAND + 1024 + 512;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// shared::cta -> peer shared memory, completion (bytes) on the PEER's mbarrier
+__device__ __forceinline__ void bulk_copy_to_peer(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_cluster),
+               "r"(src_cta), "r"(bytes), "r"(bar_cluster)
+               : "memory");
+}
+// arrive on the mbarrier at the same offset in every CTA of `mask` once this thread's earlier tcgen05.mma have completed
+__device__ __forceinline__ void mma_commit_multicast(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+
+template <bool HAS_DAB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bwd_pair_kernel(const __grid_constant__ BwdSeqParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* wring = smem;
+  uint8_t* stg = smem + P_WSTAGES * P_WSTAGE;
+  uint8_t* land = stg + 2 * R_STG;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(land + P_LAND);
+  uint64_t* wfull = bars;                 // [3]
+  uint64_t* wempty = bars + 3;            // [3]
+  uint64_t* sfull = bars + 6;             // [2] staging written (cell threads -> MMA, store warp)
+  uint64_t* sempty = bars + 8;            // [2] staging consumed by the local MMAs
+  uint64_t* init_done = bars + 10;        // buf[nxt] holds dht * z
+  uint64_t* acc_full = bars + 11;         // all MMAs of the step complete
+  uint64_t* sstored = bars + 12;          // [2] TMA store AND the peer are done with the staging buffer
+  uint64_t* pfull = bars + 14;            // landing slot holds the peer's chunk (tx bytes from the peer's bulk copy)
+  uint64_t* pfree = bars + 15;            // the peer's MMAs have consumed the chunk this CTA sent (multicast commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int H = 256, h4 = H >> 2, NCL = 2;          // NCL: chunks of 64 units this CTA owns
+  const int T = p.T, MT = p.Bp >> 7;
+  const uint32_t rank = cluster_ctarank(), peer = rank ^ 1u;
+  const int cg0 = 2 * (int)rank;                         // first global chunk (of 4) of this CTA
+  const int first_tile = blockIdx.x >> 1, tile_stride = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P_WSTAGES; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 1); mbar_init(&sempty[i], 1); mbar_init(&sstored[i], 1); }
+    mbar_init(init_done, 1);
+    mbar_init(acc_full, 1);
+    mbar_init(pfull, 1);
+    mbar_init(pfree, 1);
+    fence_barrier_init();
+  }
+  if (warp == R_WARP_MMA) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                     // both CTAs' barriers are initialised before any remote copy / commit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= 16) {
+    setmaxnreg_dec<32>();
+  if (warp == R_WARP_TMA) {
+    // ================================================================= W_hh producer: k-blocks in MMA order
+    // (own chunk 0, peer chunk 0, own chunk 1, peer chunk 1) x (3 gates); only this CTA's 128 output columns
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int tile = first_tile; tile < p.tiles; tile += tile_stride) {
+        const int dir = tile / MT;
+        for (int step = p.step_end; step < p.step_begin; ++step)
+          for (int src = 0; src < 4; ++src) {
+            const int cg = (src & 1) ? 2 * (int)peer + (src >> 1) : cg0 + (src >> 1);
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wempty[stage], phase ^ 1);
+              uint8_t* sb = wring + stage * P_WSTAGE;
+              mbar_arrive_expect_tx(&wfull[stage], P_WSTAGE);
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh) tma_load_2d(&p.w[dir], &wfull[stage], sb + hh * 8192, (cg0 + hh) * 64, g * H + cg * 64);
+              if (++stage == P_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+          }
+      }
+    }
+  } else if (warp == R_WARP_MMA) {
+    // ================================================================= MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(128, 128, 0, 1);
+      int stage = 0, phase = 0, it = 0, use = 0, pu = 0;
+      mbar_arrive_expect_tx(pfull, P_LAND);                                // arm the landing slot for the first chunk
+      for (int tile = first_tile; tile < p.tiles; tile += tile_stride) {
+        for (int step = p.step_end; step < p.step_begin; ++step, ++it) {
+          const uint32_t d_tmem = tmem_base + ((it & 1) ^ 1) * 128;        // buf[nxt]
+          mbar_wait(init_done, it & 1);
+          tc_fence_after();
+          for (int src = 0; src < 4; ++src) {
+            uint32_t sa0;
+            int sb = 0;
+            if (src & 1) {
+              mbar_wait(pfull, pu & 1);
+              mbar_arrive_expect_tx(pfull, P_LAND);                        // arm the next phase (its bytes cannot arrive before our commit)
+              sa0 = smem_u32(land);
+            } else {
+              sb = use & 1;
+              mbar_wait(&sfull[sb], (use >> 1) & 1);
+              sa0 = smem_u32(stg + sb * R_STG);
+            }
+            tc_fence_after();
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wfull[stage], phase);
+              tc_fence_after();
+              const uint32_t sa = sa0 + g * 16384, sw = smem_u32(wring + stage * P_WSTAGE);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                mma_bf16_ss(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sw + k * 2048, 8192, 1024), idesc, 1u);
+              mma_commit(&wempty[stage]);
+              if (++stage == P_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+            if (src & 1) { mma_commit_multicast(pfree, (uint16_t)(1u << peer)); ++pu; }
+            else { mma_commit(&sempty[sb]); ++use; }
+          }
+          mma_commit(acc_full);
+        }
+      }
+    }
+  } else if (warp == R_WARP_STORE) {
+    // ================================================================= dG plane writer + sender of the staged chunks
+    if (lane == 0) {
+      int use = 0;
+      const uint32_t peer_land = mapa_u32(smem_u32(land), peer), peer_pfull = mapa_u32(smem_u32(pfull), peer);
+      for (int tile = first_tile; tile < p.tiles; tile += tile_stride) {
+        const int mt = tile % MT, dir = tile / MT, m0 = mt * 128;
+        for (int step = p.step_begin - 1; step >= p.step_end; --step) {
+          const int t = dir == 0 ? step : T - 1 - step;
+          if (step > p.step_end) {
+            // next step's saved-gate records of THIS CTA's units (32 contiguous groups = 64 KB per array) into L2
+            const int tn = dir == 0 ? step - 1 : T - step;
+            const int64_t grp = (((int64_t)dir * T + tn) * MT + mt) * h4 + 32 * (int)rank;
+            prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + grp * 128), 65536);
+            prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + p.g16_plane + grp * 128), 65536);
+            prefetch_l2_bulk(reinterpret_cast<const char*>(p.hn) + grp * 128 * 16, 65536);
+            if (HAS_DAB) {
+              const char* dp = reinterpret_cast<const char*>(p.d_above) +
+                               (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 32 * (int)rank) * 128 * 16;
+              prefetch_l2_bulk(dp, 65536);
+            }
+          }
+          for (int c = 0; c < NCL; ++c, ++use) {
+            const int sb = use & 1;
+            mbar_wait(&sfull[sb], (use >> 1) & 1);
+            const uint8_t* sbuf = stg + sb * R_STG;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) tma_store_2d(&p.dg[dir], sbuf + g * 16384, g * H + 64 * (cg0 + c), t * p.Bp + m0);
+            bulk_commit();
+            if (use > 0) {
+              // the peer has consumed the previous chunk: its landing slot is free again and the previous staging buffer
+              // has been read completely by the copy engine (its TMA store was drained when it was issued)
+              mbar_wait(pfree, (use - 1) & 1);
+              mbar_arrive(&sstored[sb ^ 1]);
+            }
+            bulk_copy_to_peer(peer_land, smem_u32(sbuf), P_LAND, peer_pfull);
+            bulk_wait_read0();
+          }
+        }
+      }
+      if (use > 0) mbar_wait(pfree, (use - 1) & 1);           // the peer is done with everything this CTA sent
+    }
+  }
+  } else {
+    setmaxnreg_inc<112>();
+    // ================================================================= gate gradients: thread = (batch row, 16 units per chunk)
+    const int e = threadIdx.x;
+    const int quarter = warp & 3, sub = warp >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    int it = 0, use = 0;
+    for (int tile = first_tile; tile < p.tiles; tile += tile_stride) {
+      const int mt = tile % MT, dir = tile / MT, m0 = mt * 128, b = m0 + row;
+      const bool row_ok = b < p.B;
+      if (it > 0) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+      {
+        const float4* src = reinterpret_cast<const float4*>(p.dhs0) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll
+        for (int c = 0; c < NCL; ++c) {
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = __ldg(src + (int64_t)(16 * (cg0 + c) + 4 * sub + i) * 128);
+            v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+          }
+          tmem_st16(lane_base + (it & 1) * 128 + 64 * c + 16 * sub, v);
+        }
+        tmem_wait_st();
+      }
+      for (int step = p.step_begin - 1; step >= p.step_end; --step, ++it) {
+        const int t = dir == 0 ? step : T - 1 - step;
+        const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
+        const uint32_t cur = lane_base + (it & 1) * 128, nxt = lane_base + ((it & 1) ^ 1) * 128;
+        // record (4-unit group) index of this thread's first group; LOCAL chunk c, group i is at rec0 + (16 c + i) * 128
+        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * h4 + 16 * cg0 + 4 * sub) * 128 + row;
+        const float4* dab0 = HAS_DAB ? reinterpret_cast<const float4*>(p.d_above) +
+                                           (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 16 * cg0 + 4 * sub) * 128 + row
+                                     : nullptr;
+        uint2 zw[NCL * 4];
+#pragma unroll
+        for (int g = 0; g < NCL * 4; ++g)
+          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) + 1)
+                       : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+        float4 da[4];
+        if (HAS_DAB) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) da[i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (step != p.step_begin - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+        // ---------------- pass 1: dht = dh (+ d_above); buf[cur] <- dht; buf[nxt] <- dht * z
+#pragma unroll
+        for (int c = 0; c < NCL; ++c) {
+          float dh[16];
+          tmem_ld16v(cur + 64 * c + 16 * sub, dh);
+          if (HAS_DAB) {
+            float4* d4 = da;
+            if (p.drop_p > 0.f && live) {
+              const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * (cg0 + c) + 16 * sub);
+              float s8[8];
+              dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+              d4[0].x *= s8[0]; d4[0].y *= s8[1]; d4[0].z *= s8[2]; d4[0].w *= s8[3];
+              d4[1].x *= s8[4]; d4[1].y *= s8[5]; d4[1].z *= s8[6]; d4[1].w *= s8[7];
+              dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+              d4[2].x *= s8[0]; d4[2].y *= s8[1]; d4[2].z *= s8[2]; d4[2].w *= s8[3];
+              d4[3].x *= s8[4]; d4[3].y *= s8[5]; d4[3].z *= s8[6]; d4[3].w *= s8[7];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { dh[4 * i] += d4[i].x; dh[4 * i + 1] += d4[i].y; dh[4 * i + 2] += d4[i].z; dh[4 * i + 3] += d4[i].w; }
+            if (c + 1 < NCL) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                da[i] = live ? __ldg(dab0 + (int64_t)(16 * (c + 1) + i) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            tmem_st16(cur + 64 * c + 16 * sub, dh);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint2 z2 = zw[4 * c + i];
+            dh[4 * i] *= dq_u16(z2.x);
+            dh[4 * i + 1] *= dq_u16(z2.x >> 16);
+            dh[4 * i + 2] *= dq_u16(z2.y);
+            dh[4 * i + 3] *= dq_u16(z2.y >> 16);
+          }
+          tmem_st16(nxt + 64 * c + 16 * sub, dh);
+        }
+        uint4 ga0[2], gb0[2], ga1[2], gb1[2];
+        float4 hn0[2], hn1[2];
+#define TT_LOAD_HALF(GA, GB, HN, HCV)                                                                          \
+  _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                              \
+    const int64_t rec = rec0 + (int64_t)(((HCV) >> 1) * 16 + ((HCV) & 1) * 2 + i) * 128;                       \
+    GA[i] = live ? __ldg(p.g16 + rec) : make_uint4(0u, 0u, 0u, 0u);                                            \
+    GB[i] = live ? __ldg(p.g16 + p.g16_plane + rec) : make_uint4(0u, 0u, 0u, 0u);                              \
+    HN[i] = live ? __ldg(reinterpret_cast<const float4*>(p.hn) + rec) : make_float4(0.f, 0.f, 0.f, 0.f);       \
+  }
+#define TT_GRAD_HALF(GA, GB, HN, CV, CCV, SBUF)                                                                \
+  {                                                                                                            \
+    float dh[8];                                                                                               \
+    tmem_ld8(cur + 64 * (CV) + 16 * sub + 8 * (CCV), dh);                                                      \
+    tmem_wait_ld();                                                                                            \
+    float dr[8], dzv[8], dnr[8], dn[8];                                                                        \
+    _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                            \
+      const int o = 4 * i;                                                                                     \
+      const float hnv[4] = {HN[i].x, HN[i].y, HN[i].z, HN[i].w};                                               \
+      const uint32_t rw[2] = {GA[i].x, GA[i].y}, zw2[2] = {GA[i].z, GA[i].w};                                  \
+      const uint32_t nw[2] = {GB[i].x, GB[i].y}, qw[2] = {GB[i].z, GB[i].w};                                   \
+      _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                          \
+        const int sh = (j & 1) * 16;                                                                           \
+        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw2[j >> 1] >> sh);                               \
+        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);  \
+        const float d = live ? dh[o + j] : 0.f;                                                                \
+        const float dn_pre = d * (1.f - z) * (1.f - n * n);                                                    \
+        dn[o + j] = dn_pre;                                                                                    \
+        dnr[o + j] = dn_pre * r;                                                                               \
+        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);                                                           \
+        dzv[o + j] = d * q * (1.f - z);                                                                        \
+      }                                                                                                        \
+    }                                                                                                          \
+    const uint32_t off = sw128_off(row, 2 * sub + (CCV));                                                      \
+    *reinterpret_cast<uint4*>(SBUF + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7])); \
+    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7])); \
+  }
+        TT_LOAD_HALF(ga0, gb0, hn0, 0)
+        tmem_wait_st();
+        tc_fence_before();
+        named_bar_sync(1, 512);
+        if (e == 0) mbar_arrive(init_done);
+        // ---------------- pass 2: gate gradients of this CTA's two chunks
+#pragma unroll 1
+        for (int c = 0; c < NCL; ++c) {
+          const int sb = (use + c) & 1;
+          uint8_t* sbuf = stg + sb * R_STG;
+          TT_LOAD_HALF(ga1, gb1, hn1, 2 * c + 1)
+          if (e == 0 && use + c >= 2) {                          // staging buffer free: local MMAs, TMA store and the peer are done with it
+            mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);
+            mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1);
+          }
+          named_bar_sync(2, 512);
+          TT_GRAD_HALF(ga0, gb0, hn0, c, 0, sbuf)
+          if (c + 1 < NCL) { TT_LOAD_HALF(ga0, gb0, hn0, 2 * c + 2) }
+          TT_GRAD_HALF(ga1, gb1, hn1, c, 1, sbuf)
+          fence_proxy_async();
+          named_bar_sync(3, 512);
+          if (e == 0) mbar_arrive(&sfull[sb]);
+        }
+#undef TT_LOAD_HALF
+#undef TT_GRAD_HALF
+        use += NCL;
+      }
+      if (p.dhs_out && p.step_begin > p.step_end) {
+        mbar_wait(acc_full, (it - 1) & 1);
+        tc_fence_after();
+        float4* dst = reinterpret_cast<float4*>(p.dhs_out) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll
+        for (int c = 0; c < NCL; ++c) {
+          float v[16];
+          tmem_ld16v(lane_base + (it & 1) * 128 + 64 * c + 16 * sub, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[(int64_t)(16 * (cg0 + c) + 4 * sub + i) * 128] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                     // nobody leaves while the peer may still copy into / read from this CTA's shared memory
+  if (warp == R_WARP_MMA) tmem_dealloc(tmem_base, 256);
 }
 
 // ------------------------------------------------------------------------------------------ backward helpers
@@ -1608,9 +1982,22 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
   }
   static int num_sms_b = 0;
   if (!num_sms_b) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms_b, cudaDevAttrMultiProcessorCount, dev)); }
-  const int bptt_ctas = MT * nd < num_sms_b ? MT * nd : num_sms_b;
+  // CTA pairs halve the latency of a timestep but cost more SM-time (5.2 ms on 128 SMs vs 6.6 ms on 64 at B = 4096, where the
+  // idle SMs are busy with the weight-gradient GEMMs and the other tower anyway): used when the pairs fit in half the GPU
+  // (measured: 12.6 vs 13.8 ms/step at B = 2048, 9.4 vs 11.4 at B = 1024); mode 3 forces them.
+  const bool pair_bptt = H == 256 && (bwd_seq_mode() == 3 || (bwd_seq_mode() == 2 && 4 * MT * nd <= num_sms_b));
+  const int bptt_want = MT * nd * (pair_bptt ? 2 : 1);
+  const int bptt_ctas = bptt_want < num_sms_b ? bptt_want : num_sms_b;
   const int free_ctas = num_sms_b - bptt_ctas;           // SMs the BPTT kernel of the next layer leaves idle
-  SideStream* side = (g_wgrad_overlap && L > 1 && free_ctas >= 32 && bwd_seq_mode() != 0 && (H == 64 || H == 128 || H == 256)) ? side_for(s) : nullptr;
+  const bool fused_bptt = bwd_seq_mode() != 0 && (H == 64 || H == 128 || H == 256);
+  // Time segments: the persistent BPTT kernel runs the sequence as `nseg` launches (dL/dh handed over through f.dhs);
+  // the weight-gradient GEMMs over a finished segment's tokens run on the helper stream under the next segment's
+  // launch, so they leave the critical path for EVERY layer (not only for layers that have another layer below them).
+  int nseg = (g_wgrad_overlap && fused_bptt && free_ctas >= 32) ? g_bwd_segments : 1;
+  if (nseg > T / 16) nseg = T / 16;
+  if (nseg < 1) nseg = 1;
+  SideStream* side = (g_wgrad_overlap && (L > 1 || nseg > 1) && free_ctas >= 32 && fused_bptt) ? side_for(s) : nullptr;
+  if (!side) nseg = 1;
   bool pending[2] = {false, false};                      // side work still reading dgbuf[i] / csbuf[i]
   for (int l = L - 1; l >= 0; --l) {
     const int in = d.in_l(l), kp = d.kp_l(l);
@@ -1630,6 +2017,33 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     memset(&cp, 0, sizeof(cp));
     const int dgp_pitch = nd * 4 * H;
     for (int dd = 0; dd < nd; ++dd) TT_TRY(make_plane_map(&cp.dg[dd], f.dg[dd], d.ntok, 4 * H, dgp_pitch, 128, 1));
+    // weight gradients over the token rows [row0[dd], row0[dd] + rows) of direction dd (time-major rows: a time segment):
+    //   dW_hh[3H,H] (+)= dGH^T h_prev   (h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
+    //   dW_ih[3H,In] (+)= dGI^T X       (dGI = columns [0,2H) and [3H,4H) of the direction's dG columns)
+    auto issue_wgrads = [&](const int64_t* row0, int64_t rows, float beta, cudaStream_t ws, int cap) -> int {
+      for (int dd = 0; dd < nd; ++dd) {
+        const Planes dgp{(const bf16*)(f.dg[dd] + row0[dd] * dgp_pitch), nullptr, dgp_pitch};
+        {
+          UmmaGemm g{};
+          g.A[0] = dgp;
+          g.B[0] = Planes{(const bf16*)(sv.hhi[l][dd] + (dd == 0 ? 0 : (int64_t)Bp * H) + row0[dd] * H), nullptr, H};
+          g.C[0] = a->d_weights[(l * nd + dd) * 4 + 1]; g.ldc = H; g.M = 3 * H; g.N = H; g.K = (int)rows; g.nbatch = 1;
+          g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = beta; g.splitk = 0; g.f16 = 1; g.npass = 1;
+          g.max_ctas = cap;
+          TT_TRY(umma_gemm(g, ws));
+        }
+        {
+          UmmaGemm g{};
+          g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H;
+          g.B[0] = Planes{(const bf16*)(sv.xhi[l] + row0[dd] * kp), nullptr, kp};
+          g.C[0] = a->d_weights[(l * nd + dd) * 4 + 0]; g.ldc = in; g.M = 3 * H; g.N = in; g.K = (int)rows; g.nbatch = 1;
+          g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = beta; g.splitk = 0; g.f16 = 1; g.npass = 1;
+          g.max_ctas = cap;
+          TT_TRY(umma_gemm(g, ws));
+        }
+      }
+      return TT_OK;
+    };
     cp.g16 = sv.g16[l]; cp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
     cp.B = B; cp.Bp = Bp; cp.T = T; cp.H = H; cp.ndir = nd;
     cp.drop_p = (has_next && d_above) ? fw->dropout_p : 0.f;
@@ -1658,8 +2072,16 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
       bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
-      note_launch();
-      ProfScope prof(PROF_GRU_SEQ_BWD, s);
+      const int pair_grid = 2 * bp.tiles <= num_sms ? 2 * bp.tiles : (num_sms & ~1);
+#define TT_BWD_PAIR(DABV)                                                                                             \
+  do {                                                                                                                \
+    static bool attr = false;                                                                                         \
+    if (!attr) {                                                                                                      \
+      TT_CUDA(cudaFuncSetAttribute(gru_bwd_pair_kernel<DABV>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));  \
+      attr = true;                                                                                                    \
+    }                                                                                                                 \
+    gru_bwd_pair_kernel<DABV><<<pair_grid, R_THREADS, P_SMEM, s>>>(bp);                                               \
+  } while (0)
 #define TT_BWD_SEQ(NCHV, DABV)                                                                                        \
   do {                                                                                                                \
     static bool attr = false;                                                                                         \
@@ -1670,11 +2092,29 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     gru_bwd_seq_kernel<NCHV, DABV><<<grid, R_THREADS, R_SMEM, s>>>(bp);                                               \
   } while (0)
       const bool dab = d_above != nullptr;
-      if (H == 256) { if (dab) TT_BWD_SEQ(4, true); else TT_BWD_SEQ(4, false); }
-      else if (H == 128) { if (dab) TT_BWD_SEQ(2, true); else TT_BWD_SEQ(2, false); }
-      else { if (dab) TT_BWD_SEQ(1, true); else TT_BWD_SEQ(1, false); }
+      for (int seg = 0; seg < nseg; ++seg) {
+        bp.step_begin = T - (int)((int64_t)T * seg / nseg);
+        bp.step_end = T - (int)((int64_t)T * (seg + 1) / nseg);
+        bp.dhs_out = nseg > 1 && seg + 1 < nseg ? f.dhs : nullptr;
+        {
+          note_launch();
+          ProfScope prof(PROF_GRU_SEQ_BWD, s);
+          if (pair_bptt) { if (dab) TT_BWD_PAIR(true); else TT_BWD_PAIR(false); }
+          else if (H == 256) { if (dab) TT_BWD_SEQ(4, true); else TT_BWD_SEQ(4, false); }
+          else if (H == 128) { if (dab) TT_BWD_SEQ(2, true); else TT_BWD_SEQ(2, false); }
+          else { if (dab) TT_BWD_SEQ(1, true); else TT_BWD_SEQ(1, false); }
+          TT_LAUNCH_CHECK();
+        }
+        if (nseg > 1) {
+          // this segment's tokens: forward direction t in [step_end, step_begin), reverse direction t in [T-step_begin, T-step_end)
+          TT_CUDA(cudaEventRecord(side->fork, s));
+          TT_CUDA(cudaStreamWaitEvent(side->side, side->fork, 0));
+          const int64_t row0[2] = {(int64_t)bp.step_end * Bp, (int64_t)(T - bp.step_begin) * Bp};
+          TT_TRY(issue_wgrads(row0, (int64_t)(bp.step_begin - bp.step_end) * Bp, seg == 0 ? 0.f : 1.f, side->side, free_ctas));
+        }
+      }
 #undef TT_BWD_SEQ
-      TT_LAUNCH_CHECK();
+#undef TT_BWD_PAIR
     } else {
     UmmaPrepared prep;
     TT_TRY(umma_gemm_prepare(r, &prep));
@@ -1711,7 +2151,8 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }
     // weight and bias gradients of this layer: off the critical path.  With a layer below still to do they go to the
     // helper stream (capped to the SMs its BPTT kernel leaves idle), otherwise they stay on the caller's stream.
-    const bool overlap = side != nullptr && l > 0;
+    const bool segmented = nseg > 1;                       // weight gradients already queued per segment on the helper stream
+    const bool overlap = side != nullptr && (l > 0 || segmented);
     cudaStream_t ws = s;
     if (overlap) {
       TT_CUDA(cudaEventRecord(side->fork, s));
@@ -1731,28 +2172,9 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       }
       TT_LAUNCH_CHECK();
     }
-    for (int dd = 0; dd < nd; ++dd) {
-      const Planes dgp{(const bf16*)f.dg[dd], nullptr, dgp_pitch};
-      // dW_hh[3H,H] = dGH^T h_prev   (reduction over all tokens; h_prev(t) = H-plane slot t (fwd) / t+1 (rev))
-      {
-        UmmaGemm g{};
-        g.A[0] = dgp;
-        g.B[0] = Planes{(const bf16*)(sv.hhi[l][dd] + (dd == 0 ? 0 : (int64_t)Bp * H)), nullptr, H};
-        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 1]; g.ldc = H; g.M = 3 * H; g.N = H; g.K = (int)d.ntok; g.nbatch = 1;
-        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
-        g.max_ctas = cap;
-        TT_TRY(umma_gemm(g, ws));
-      }
-      // dW_ih[3H,In] = dGI^T X   (dGI = columns [0,2H) and [3H,4H) of the direction's dG columns)
-      {
-        UmmaGemm g{};
-        g.A[0] = dgp; g.a_seg = 2 * H; g.a_skip = H;
-        g.B[0] = Planes{(const bf16*)sv.xhi[l], nullptr, kp};
-        g.C[0] = a->d_weights[(l * nd + dd) * 4 + 0]; g.ldc = in; g.M = 3 * H; g.N = in; g.K = (int)d.ntok; g.nbatch = 1;
-        g.a_mn = g.b_mn = true; g.alpha = 1.f; g.alpha_ptr = f.scale + 1; g.beta = 0.f; g.splitk = 0; g.f16 = 1; g.npass = 1;
-        g.max_ctas = cap;
-        TT_TRY(umma_gemm(g, ws));
-      }
+    if (!segmented) {
+      const int64_t row0[2] = {0, 0};
+      TT_TRY(issue_wgrads(row0, d.ntok, 0.f, ws, cap));
     }
     if (overlap) { TT_CUDA(cudaEventRecord(side->done[pb], side->side)); pending[pb] = true; }
     d_above = d_below;
@@ -1773,8 +2195,14 @@ extern "C" int tt_debug_seq_mode(int32_t mode) {
   tt::g_seq_mode = mode;
   return TT_OK;
 }
+extern "C" int tt_debug_bwd_segments(int32_t n) {
+  if (n < 1 || n > 16) { tt::set_error("tt_debug_bwd_segments: 1..16"); return TT_ERR_INVALID; }
+  tt::g_bwd_segments = n;
+  return TT_OK;
+}
 extern "C" int tt_debug_bwd_seq_mode(int32_t mode) {
-  tt::g_bwd_seq_mode = mode ? 1 : 0;
+  if (mode < 0 || mode > 3) { tt::set_error("tt_debug_bwd_seq_mode: 0..3"); return TT_ERR_INVALID; }
+  tt::g_bwd_seq_mode = mode;
   return TT_OK;
 }
 
