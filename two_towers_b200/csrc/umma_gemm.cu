@@ -390,7 +390,10 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     splitk = 1;
     const int tiles = MT * NT * g.nbatch;
     if (tiles < 74 && KB >= 32) {
-      splitk = (int)ceil_div(148, tiles);
+      // ONE wave of the persistent grid: tiles * splitk <= CTAs (rounding up gave e.g. 6 tiles x 25 splits = 150 items on
+      // 148 CTAs - a second wave of two items that took as long as the first)
+      const int ctas = (g.max_ctas > 0 && g.max_ctas < 148) ? g.max_ctas : 148;
+      splitk = ctas / tiles;
       if (splitk > KB / 8) splitk = KB / 8;
       if (splitk < 1) splitk = 1;
     }
