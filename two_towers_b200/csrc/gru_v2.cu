@@ -476,14 +476,19 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
   uint64_t* empty = bars + S_STAGES;                            // [S_STAGES], 2 arrivals per use
   uint64_t* tfull = bars + 2 * S_STAGES;                        // [2]
   uint64_t* tempty = tfull + 2;                                 // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* sready = tempty + 2;                                // staging tiles written (epilogue -> store warp)
+  uint64_t* sfree = sready + 1;                                 // staging tiles read out by the TMA store (store warp -> epilogue)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sfree + 1);
   float* bhn_s = reinterpret_cast<float*>(bars + 16);           // [2][64]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int H = p.H, T = p.T, KB = H / S_BK, MT = p.Bp >> 7, US = H / S_UN;
+  constexpr int W_STORE = 4 * EWQ + 2;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < S_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 2); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 1); }
+    mbar_init(sready, 1);
+    mbar_init(sfree, 1);
     fence_barrier_init();
   }
   if (warp == W_MMA) tmem_alloc(tmem_slot, Q_TMEM_COLS);
@@ -563,6 +568,35 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
         }
       }
     }
+  } else if (warp == W_STORE) {
+    // ================================================================= h_t writer + publisher (off the epilogue threads' loop:
+    // the epilogue goes on with the CTA's next item while the stores drain and the release counter is bumped)
+    if (lane == 0) {
+      int item = 0;
+      for (int step = 0; step < T; ++step) {
+        for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++item) {
+          const int us = tile % US, mt = (tile / US) % MT, dir = tile / (US * MT);
+          const int t = dir == 0 ? step : T - 1 - step;
+          const int wslot = dir == 0 ? t + 1 : t;
+          const int m0 = mt * S_BM, u0 = us * S_UN;
+          mbar_wait(sready, item & 1);
+          tma_store_2d(&p.h_hi[dir], stg, u0, wslot * p.Bp + m0);
+          tma_store_2d(&p.h_lo[dir], stg + 16384, u0, wslot * p.Bp + m0);
+          if (p.has_next) {
+            tma_store_2d(&p.x_hi, stg + 32768, dir * H + u0, t * p.Bp + m0);
+            tma_store_2d(&p.x_lo, stg + 49152, dir * H + u0, t * p.Bp + m0);
+          }
+          bulk_commit();
+          bulk_wait_read0();                                   // staging read out: the epilogue may overwrite it
+          mbar_arrive(sfree);
+          bulk_wait0();                                        // writes complete (not only the smem reads)
+          fence_proxy_async_global();
+          __threadfence();
+          atomicAdd(sp.ready + dir * MT + mt, 1);              // publish h_t of (us, mt, dir)
+          SEQ_MARK(item, 6);
+        }
+      }
+    }
   }
   } else {
     if (EWQ == 4) setmaxnreg_inc<112>();
@@ -613,7 +647,8 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
           ph[c] = *reinterpret_cast<const uint4*>(own_hi + off);
           pl[c] = *reinterpret_cast<const uint4*>(own_lo + off);
         }
-        named_bar_sync(1, EPI_THREADS);      // all h_prev reads done, bhn_s written, previous item's staging drained
+        if (e == 0 && item > 0) mbar_wait(sfree, (item - 1) & 1);   // previous item's staging tiles have been read out
+        named_bar_sync(1, EPI_THREADS);      // all h_prev reads done, bhn_s written, staging free
         if (e == 0) mbar_arrive(&empty[own_stage]);
         const uint32_t tl = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 256 + UT * sub);
 #pragma unroll
@@ -714,21 +749,10 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
         if (e == 0) {
           SEQ_MARK(item, 5);
           mbar_arrive(&tempty[acc]);
-          tma_store_2d(&p.h_hi[dir], stg, u0, wslot * p.Bp + m0);
-          tma_store_2d(&p.h_lo[dir], stg + 16384, u0, wslot * p.Bp + m0);
-          if (p.has_next) {
-            tma_store_2d(&p.x_hi, stg + 32768, dir * H + u0, t * p.Bp + m0);
-            tma_store_2d(&p.x_lo, stg + 49152, dir * H + u0, t * p.Bp + m0);
-          }
-          bulk_commit();
-          bulk_wait0();                                        // writes complete (not only the smem reads)
-          fence_proxy_async_global();
-          __threadfence();
-          atomicAdd(sp.ready + dir * MT + mt, 1);              // publish h_t of (us, mt, dir)
-          SEQ_MARK(item, 6);
+          mbar_arrive(sready);                                 // the store warp writes h_t out and publishes it
         }
         // (the staging tiles are reused by the next item only after named barrier 1, which thread e == 0 reaches
-        //  after its stores have been read out)
+        //  after the store warp has reported them read out)
       }
     }
   }
