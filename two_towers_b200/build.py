@@ -21,6 +21,10 @@ NVCC_FLAGS = [
 ]
 
 
+if os.environ.get("TT_PHASE_MARKS") == "1":      # in-kernel %globaltimer marks for tools/step_phases.py / bwd_phases.py
+    NVCC_FLAGS.append("-DTT_PHASE_MARKS")
+
+
 def _nvcc():
     exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(exe):

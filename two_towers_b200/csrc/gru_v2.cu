@@ -456,10 +456,17 @@ struct alignas(64) SeqParams {
   int32_t tiles;                     // (H/64) * MT * ndir
 };
 
+// In-kernel %globaltimer phase marks of the two persistent kernels (tools/step_phases.py, tools/bwd_phases.py) are compiled
+// in only with -DTT_PHASE_MARKS (TT_PHASE_MARKS=1 python -m two_towers_b200.build --force): even predicated off they sat in
+// front of the named barriers of the per-item loop (ncu: the thread-0 warp stalled on them, every other warp on the barrier).
+#ifdef TT_PHASE_MARKS
 #define SEQ_MARK(item, slot)                                                              \
   do {                                                                                    \
     if (p.dbg && blockIdx.x == 0 && (item) < 256) p.dbg[(item) * 8 + (slot)] = gtimer(); \
   } while (0)
+#else
+#define SEQ_MARK(item, slot) do { } while (0)
+#endif
 
 template <int EWQ>                                              // epilogue warps per TMEM lane quarter (2 or 4)
 __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __grid_constant__ SeqParams sp) {
@@ -606,6 +613,17 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
     const int row = quarter * 32 + lane;
     const int h4 = H >> 2;
     int item = 0;
+    // b_hn of the CTA's tiles: constant over the timesteps.  With at most two tiles per CTA (slot = item & 1 = position of
+    // the tile in the CTA's round) it is loaded ONCE; it used to be a global load in front of named barrier 1 of every item.
+    const bool bhn_once = (int)blockIdx.x + 2 * (int)gridDim.x >= sp.tiles;
+    if (bhn_once) {
+      const int own = (int)blockIdx.x + (int)gridDim.x < sp.tiles ? 2 : 1;       // tiles of this CTA
+      for (int k = 0; k < 2; ++k) {                                              // one tile: both slots hold it
+        const int tile = (int)blockIdx.x + (k % own) * (int)gridDim.x;
+        if (e < S_UN && tile < sp.tiles) bhn_s[k * S_UN + e] = __ldg(p.b_hh[tile / (US * MT)] + 2 * H + (tile % US) * S_UN + e);
+      }
+      named_bar_sync(1, EPI_THREADS);
+    }
     for (int step = 0; step < T; ++step) {
       for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++item) {
         const int us = tile % US, mt = (tile / US) % MT, dir = tile / (US * MT);
@@ -629,7 +647,7 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
           }
         }
         float* bh = bhn_s + (item & 1) * S_UN;
-        if (e < S_UN) bh[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
+        if (!bhn_once && e < S_UN) bh[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
         const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
         // ring position of the own A tile (last k-block of this item)
         const int own_pos = (item + 1) * KB - 1, own_stage = own_pos % S_STAGES;
@@ -894,10 +912,14 @@ struct alignas(64) BwdSeqParams {
   int32_t step_begin, step_end;
   float* dhs_out;
 };
+#ifdef TT_PHASE_MARKS
 #define BWD_MARK(itv, slot)                                                              \
   do {                                                                                   \
     if (p.dbg && blockIdx.x == 0 && (itv) < 64) p.dbg[(itv) * 16 + (slot)] = gtimer(); \
   } while (0)
+#else
+#define BWD_MARK(itv, slot) do { } while (0)
+#endif
 
 __device__ __forceinline__ void tmem_ld16v(uint32_t taddr, float (&v)[16]) {
   uint32_t r[16];
