@@ -371,6 +371,7 @@ def run_ours(args):
     nb = 4
     host = [(make_ids(B, TQ, V, gen).pin_memory(), make_ids(B, TD, V, gen).pin_memory()) for _ in range(nb)]
     resident = [(q.to(dev), d.to(dev)) for q, d in host]
+    resident_shape = host[0]
 
     def step(q, d):
         opt.zero_grad(set_to_none=True)
@@ -432,11 +433,19 @@ def run_ours(args):
     # (the next step's ids are copied on a copy stream while the current step computes - still one H2D per step
     #  inside the timed region)
     copy_stream = torch.cuda.Stream(dev)
+    # double-buffered device id slots, allocated once (a fresh allocation on the copy stream every step made the caching
+    # allocator's cross-stream bookkeeping part of the timed region: occasional 100+ ms outliers)
+    slots = [(torch.empty_like(resident_shape[0], device=dev), torch.empty_like(resident_shape[1], device=dev)) for _ in range(2)]
+    slot_free = [None, None]                 # event: the step that read the slot has been queued and has finished
 
     def upload(i):
         q, d = host[i % nb]
+        qd, dd = slots[i & 1]
         with torch.cuda.stream(copy_stream):
-            qd, dd = q.to(dev, non_blocking=True), d.to(dev, non_blocking=True)
+            if slot_free[i & 1] is not None:
+                copy_stream.wait_event(slot_free[i & 1])
+            qd.copy_(q, non_blocking=True)
+            dd.copy_(d, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy_stream)
         return qd, dd, ev
@@ -459,9 +468,10 @@ def run_ours(args):
         if i + 1 < args.steps:
             nxt = upload(i + 1)
         st.wait_event(ev)
-        qd.record_stream(st); dd.record_stream(st)
         tb = time.perf_counter()
         loss, _ = step(qd, dd)
+        slot_free[i & 1] = torch.cuda.Event()
+        slot_free[i & 1].record(st)
         tc = time.perf_counter()
         loss_host[i & 1].copy_(loss.detach(), non_blocking=True)
         loss_ev[i & 1].record(st)
