@@ -51,6 +51,8 @@ static inline uint64_t align_up(uint64_t a, uint64_t b) { return (a + b - 1) / b
 // bump allocator over the caller's workspace
 // fp32 [rows][cols] -> fp16 hi/lo operand planes [rows][pitch] (pad columns zero); defined in score.cu
 int split_rows_f16(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, cudaStream_t s);
+int split_rows_f16_scaled(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, const float* row_scale,
+                          cudaStream_t s);
 
 struct Workspace {
   char* base;

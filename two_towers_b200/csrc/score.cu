@@ -73,11 +73,12 @@ __global__ void ce_grad_kernel(float* __restrict__ S, int ld, int Bl, int c0, in
 
 // fp32 [rows][cols] -> fp16 hi/lo planes [rows][pitch] (pad columns zero)
 __global__ void split_rows_f16_kernel(const float* __restrict__ x, int64_t rows, int cols, int64_t pitch,
-                                      __half* __restrict__ hi, __half* __restrict__ lo) {
+                                      __half* __restrict__ hi, __half* __restrict__ lo, const float* __restrict__ row_scale = nullptr) {
   const int64_t total = rows * pitch;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % pitch);
-    const float v = c < cols ? x[(i / pitch) * cols + c] : 0.f;
+    float v = c < cols ? x[(i / pitch) * cols + c] : 0.f;
+    if (row_scale) v *= row_scale[i / pitch];
     __half a, b;
     umma::split_f16(v, a, b);
     hi[i] = a; lo[i] = b;
@@ -105,6 +106,14 @@ __global__ void ce_grad_planes_kernel(const float* __restrict__ S, int ld, int B
 int split_rows_f16(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, cudaStream_t s) {
   if (rows <= 0) return TT_OK;
   note_launch(); split_rows_f16_kernel<<<592, 256, 0, s>>>(x, rows, cols, pitch, (__half*)hi, (__half*)lo);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+// same with every row multiplied by row_scale[row] first (row_scale may be null)
+int split_rows_f16_scaled(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, const float* row_scale,
+                          cudaStream_t s) {
+  if (rows <= 0) return TT_OK;
+  note_launch(); split_rows_f16_kernel<<<592, 256, 0, s>>>(x, rows, cols, pitch, (__half*)hi, (__half*)lo, row_scale);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }

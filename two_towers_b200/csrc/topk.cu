@@ -207,7 +207,9 @@ __global__ void mrr_ranks_kernel(const int64_t* __restrict__ topk_idx, const int
 
 
 // ------------------------------------------------------------------------------------------ tensor route
-constexpr int kCandSlack = 8;
+constexpr int kCandSlack = 8;                                // candidates beyond k (fewer when k + 8 would exceed the engine's 16)
+constexpr int kSelMax = 16;                                  // list entries per row the selection epilogue keeps (umma_gemm.cu)
+static inline int cand_k2(int k) { return k + kCandSlack <= kSelMax ? k + kCandSlack : kSelMax; }
 constexpr float kScoreErr = 1.220703125e-4f;                 // 2^-13: bound on |approx - exact| / (|x| |y|), 4x margin
 
 __global__ void list_init_kernel(float* __restrict__ lv, int* __restrict__ li, int64_t n) {
@@ -221,70 +223,35 @@ __global__ void min_pos_kernel(const float* __restrict__ v, int64_t n, unsigned 
   for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
   if ((threadIdx.x & 31) == 0) atomicMin(out, __float_as_uint(m));       // positive floats order like their bit patterns
 }
-// one warp per row of the approximate score tile S[nq][ld] (columns c0 .. c0+nc of the corpus): fold it into the row's
-// running candidate list (lane r = rank r, K2 entries used)
-__global__ void select_rows_kernel(const float* __restrict__ S, int64_t ld, int q0, int nq, int64_t c0, int nc, int cosine,
-                                   const float* __restrict__ invx, const float* __restrict__ invy, int64_t mask_pos_offset,
-                                   int K2, float* __restrict__ list_v, int* __restrict__ list_i) {
-  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (r >= nq) return;
-  const int row = q0 + r;
-  float lv = list_v[(int64_t)row * 32 + lane];
-  int li = list_i[(int64_t)row * 32 + lane];
-  float tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
-  int ti = __shfl_sync(0xffffffffu, li, K2 - 1);
-  const float rinv = cosine ? invx[row] : 1.f;
-  const float* s = S + (int64_t)r * ld;
-  // 128 columns per iteration (one 16-byte load per lane); the common case - nothing beats the row's K2-th best - costs
-  // one vote.  ld and c0 are multiples of 4, so the vector loads are aligned; columns >= nc of the tile row are masked.
-  float4 vnext = 4 * lane < nc ? *reinterpret_cast<const float4*>(s + 4 * lane) : make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int c = 0; c < nc; c += 128) {
-    const int cl0 = c + 4 * lane;
-    const int64_t cg0 = c0 + cl0;
-    float sc[4];
-    {
-      const float4 v = vnext;                                  // loaded one iteration ahead
-      if (cl0 + 128 < nc) vnext = *reinterpret_cast<const float4*>(s + cl0 + 128);
-      sc[0] = v.x; sc[1] = v.y; sc[2] = v.z; sc[3] = v.w;
-    }
-    if (cosine) {
-      float iy[4];
-      if (cl0 + 3 < nc) {
-        const float4 w = *reinterpret_cast<const float4*>(invy + cg0);
-        iy[0] = w.x; iy[1] = w.y; iy[2] = w.z; iy[3] = w.w;
-      } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) iy[j] = cl0 + j < nc ? invy[cg0 + j] : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) sc[j] = (sc[j] * rinv) * iy[j];
-    }
-    bool any = false;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (mask_pos_offset >= 0 && cg0 + j == mask_pos_offset + row) sc[j] = -1.f;
-      if (sc[j] != sc[j]) sc[j] = INFINITY;                  // NaN (fp16 overflow of an operand): force the exact route
-      if (cl0 + j >= nc) sc[j] = -INFINITY;
-      any |= sc[j] > -INFINITY && better(sc[j], (int)(cg0 + j), tv, ti);
-    }
-    if (!__ballot_sync(0xffffffffu, any)) continue;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      unsigned m = __ballot_sync(0xffffffffu, sc[j] > -INFINITY && better(sc[j], (int)(cg0 + j), tv, ti));
-      while (m) {
-        const int b = __ffs(m) - 1;
-        m &= m - 1;
-        const float cv = __shfl_sync(0xffffffffu, sc[j], b);
-        const int ci = (int)(c0 + c + 4 * b + j);
-        if (better(cv, ci, tv, ti)) {
-          list_insert(lv, li, cv, ci, lane);
-          tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
-          ti = __shfl_sync(0xffffffffu, li, K2 - 1);
-        }
+// one warp per row: fold the per-(CTA, column half) candidate lists the GEMM engine's selection epilogue wrote
+// (part_v / part_i [Q][slots][32], unused entries = (-inf, INT_MAX)) into the row's K2 best (lane r = rank r).
+// rscale (cosine: 1/max(|x|,eps) per row, the scores arrive scaled by |x|) turns the kept scores into the units of the
+// acceptance test.
+__global__ void merge_parts_kernel(const float* __restrict__ part_v, const int* __restrict__ part_i, int Q, int slots, int K2,
+                                   const float* __restrict__ rscale, float* __restrict__ list_v, int* __restrict__ list_i) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= Q) return;
+  float lv = -INFINITY, tv = -INFINITY;
+  int li = INT_MAX, ti = INT_MAX;
+  const float* pv = part_v + (int64_t)row * slots * 32;
+  const int* pi = part_i + (int64_t)row * slots * 32;
+  for (int sl = 0; sl < slots; ++sl) {
+    const float cvl = pv[sl * 32 + lane];
+    const int cil = pi[sl * 32 + lane];
+    unsigned m = __ballot_sync(0xffffffffu, cil != INT_MAX && better(cvl, cil, tv, ti));
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1;
+      const float cv = __shfl_sync(0xffffffffu, cvl, b);
+      const int ci = __shfl_sync(0xffffffffu, cil, b);
+      if (better(cv, ci, tv, ti)) {
+        list_insert(lv, li, cv, ci, lane);
+        tv = __shfl_sync(0xffffffffu, lv, K2 - 1);
+        ti = __shfl_sync(0xffffffffu, li, K2 - 1);
       }
     }
   }
-  list_v[(int64_t)row * 32 + lane] = lv;
+  list_v[(int64_t)row * 32 + lane] = rscale ? lv * rscale[row] : lv;
   list_i[(int64_t)row * 32 + lane] = li;
 }
 // one warp per row: exact chain for each candidate, exact order, acceptance test
@@ -345,23 +312,12 @@ using namespace tt;
 
 extern "C" {
 
-// tensor route tiling: S tile = QT x NC fp32 <= 64 MiB (TT_TOPK_TILE_MB), so that the tile written by the GEMM is still in the 126 MB L2
-// when the selection kernel reads it
-static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma_available() && N >= 256 && N < INT_MAX - 64 && k + kCandSlack <= 32; }
+// tensor route: queries in chunks of QT rows; the approximate scores are consumed inside the GEMM engine's epilogue
+static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma_available() && N >= 256 && N < INT_MAX - 64 && k + 4 <= kSelMax; }
 static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
-static inline int64_t topk_tile_bytes() {
-  static int64_t v = []() { const char* e = getenv("TT_TOPK_TILE_MB"); int mb = e ? atoi(e) : 0; return (int64_t)(mb > 0 ? mb : 64) << 20; }();
-  return v;
-}
-static inline int64_t topk_nc(int Q, int64_t N) {
-  int64_t nc = topk_tile_bytes() / (4ll * topk_qt(Q));
-  nc = nc / 256 * 256;
-  if (nc > 65536) nc = 65536;
-  return nc < N ? nc : (N + 7) / 8 * 8;
-}
 struct TopkWs {
   float *invx, *invy; unsigned int* ymin; float* pv; int64_t* pi;
-  __half *xh, *xl, *yh, *yl; float* S; float* lv; int* li; int* need; int64_t dp;
+  __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp;
 };
 static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, TopkWs* o) {
   const bool tc = topk_tc(N, k);
@@ -375,7 +331,13 @@ static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, T
     o->ymin = w.take<unsigned int>(64);
     o->xh = w.take<__half>((int64_t)Q * o->dp); o->xl = w.take<__half>((int64_t)Q * o->dp);
     o->yh = w.take<__half>(N * o->dp); o->yl = w.take<__half>(N * o->dp);
-    o->S = w.take<float>((int64_t)topk_qt(Q) * topk_nc(Q, N));
+    // candidate lists of the selection epilogue: [rows of a query chunk][slots][32]; full chunks and the last, shorter one
+    const int QT = topk_qt(Q), rem = Q % QT;
+    int64_t rows_slots = (int64_t)QT * umma_sel_slots(QT, N);
+    if (rem) { const int64_t r2 = (int64_t)rem * umma_sel_slots(rem, N); rows_slots = r2 > rows_slots ? r2 : rows_slots; }
+    o->slots = rows_slots;                                      // rows x slots capacity (checked per chunk)
+    o->part_v = w.take<float>(rows_slots * 32);
+    o->part_i = w.take<int>(rows_slots * 32);
     o->lv = w.take<float>((int64_t)Q * 32); o->li = w.take<int>((int64_t)Q * 32); o->need = w.take<int>(Q);
   }
 }
@@ -407,28 +369,29 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
   const int* need = nullptr;
   if (tc) {
     // ---- tensor route: approximate tile scores -> candidates -> exact re-score -> acceptance
-    const int K2 = k + kCandSlack, QT = topk_qt(Q);
-    const int64_t NC = topk_nc(Q, N);
+    const int K2 = cand_k2(k), QT = topk_qt(Q);
     TT_CUDA(cudaMemsetAsync(t.ymin, 0x7f, sizeof(unsigned int), s));
     note_launch(); min_pos_kernel<<<296, 256, 0, s>>>(invy, N, t.ymin);
-    note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)Q * 32, 256), 256, 0, s>>>(t.lv, t.li, (int64_t)Q * 32);
     TT_TRY(split_rows_f16(x, Q, D, t.dp, t.xh, t.xl, s));
-    TT_TRY(split_rows_f16(y, N, D, t.dp, t.yh, t.yl, s));
+    // cosine: the corpus rows go into the planes already divided by their norm (the exact re-score uses the fp32 rows)
+    TT_TRY(split_rows_f16_scaled(y, N, D, t.dp, t.yh, t.yl, mode == 1 ? invy : nullptr, s));
     for (int q0 = 0; q0 < Q; q0 += QT) {
       const int nq = Q - q0 < QT ? Q - q0 : QT;
-      for (int64_t c0 = 0; c0 < N; c0 += NC) {
-        const int nc = (int)(N - c0 < NC ? N - c0 : NC);
-        UmmaGemm g{};
-        g.A[0] = Planes{(const bf16*)t.xh, (const bf16*)t.xl, t.dp};
-        g.B[0] = Planes{(const bf16*)t.yh, (const bf16*)t.yl, t.dp};
-        g.C[0] = t.S; g.ldc = NC; g.M = nq; g.N = nc; g.K = D; g.nbatch = 1;
-        g.a_rows = Q; g.a_row0 = q0; g.b_rows = N; g.b_row0 = (int32_t)c0;
-        g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
-        TT_TRY(umma_gemm(g, s));
-        note_launch();
-        select_rows_kernel<<<(unsigned)ceil_div(nq, 8), 256, 0, s>>>(t.S, NC, q0, nq, c0, nc, mode, invx, invy, mask_pos_offset, K2,
-                                                                    t.lv, t.li);
-      }
+      const int use_slots = umma_sel_slots(nq, N);
+      TT_CHECK_ARG((int64_t)nq * use_slots <= t.slots, "rows_topk: part buffer too small");
+      note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)nq * use_slots * 32, 256), 256, 0, s>>>(t.part_v, t.part_i, (int64_t)nq * use_slots * 32);
+      UmmaGemm g{};
+      g.A[0] = Planes{(const bf16*)(t.xh + (int64_t)q0 * t.dp), (const bf16*)(t.xl + (int64_t)q0 * t.dp), t.dp};
+      g.B[0] = Planes{(const bf16*)t.yh, (const bf16*)t.yl, t.dp};
+      g.M = nq; g.N = (int)N; g.K = D; g.nbatch = 1;
+      g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
+      g.epi = 2; g.sel_v = t.part_v; g.sel_i = t.part_i; g.sel_k2 = K2; g.sel_slots = use_slots;
+      g.sel_invx = mode == 1 ? invx + q0 : nullptr;
+      g.sel_mask_off = mask_pos_offset >= 0 ? mask_pos_offset + q0 : -1;
+      TT_TRY(umma_gemm(g, s));
+      note_launch();
+      merge_parts_kernel<<<(unsigned)ceil_div(nq, 8), 256, 0, s>>>(t.part_v, t.part_i, nq, use_slots, K2, mode == 1 ? invx + q0 : nullptr,
+                                                                  t.lv + (int64_t)q0 * 32, t.li + (int64_t)q0 * 32);
     }
     note_launch();
     rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, t.ymin, mask_pos_offset,

@@ -5,6 +5,8 @@
 // swizzled shared memory by TMA (hi and lo planes of A and B per stage), fp32 accumulators double-buffered in TMEM
 // so the epilogue of tile i overlaps the main loop of tile i+1.  Per k-block the issuer runs
 // 3 (hi*hi, lo*hi, hi*lo) x 4 (UMMA_K = 16) tcgen05.mma into the same accumulator.
+#include <limits.h>
+#include <string.h>
 #include "umma.cuh"
 #include "umma_gemm.cuh"
 
@@ -25,7 +27,47 @@ struct alignas(64) UmmaParams {
   uint32_t idesc;
   int32_t a_row0[2], b_row0, a_seg, a_skip, a_seg2;
   int32_t epi, rm_Bp, rm_B, rm_T, tl_Bp, tl_G, tl_Hc;
+  float* sel_v; int* sel_i; const float* sel_invx;
+  int64_t sel_mask_off;
+  int32_t sel_k2, sel_slots, sel_S, sel_cpr;   // epi == 2: S column ranges of sel_cpr column tiles per row tile
 };
+__device__ __forceinline__ bool sel_better(float v, int i, float v2, int i2) { return v > v2 || (v == v2 && i < i2); }
+constexpr int kSelStride = 256;          // epilogue threads
+constexpr int kSelCap = 16;              // list entries per thread held in shared memory (K2 <= kSelCap)
+// cold path of the selection epilogue: the columns flagged in `m` (bit j = column gn0 + j of this thread's row) are not
+// below the row's current K2-th best.  Kept out of line: inlined into the 32-way unrolled filter it made the hot loop
+// stream ~30 KB of code through the instruction cache per 32 columns.
+__device__ __noinline__ void sel_insert_flagged(const float* __restrict__ v, uint32_t m, int gn0, int N, int64_t mcol, float mval,
+                                                int K2, float* lv, int* li, float* tv_io, int* ti_io) {
+  // lv / li: this thread's sorted list in SHARED memory, entry r at [r * kSelStride] (thread-local arrays would live in
+  // L2: with ~200 KB of the SM's 256 KB carved out as shared memory almost no L1 is left, and one insertion - a serial
+  // chain of up to K2 dependent load / store pairs - cost microseconds)
+  float tv = *tv_io;
+  int ti = *ti_io;
+  while (m) {
+    const int j = __ffs(m) - 1;
+    m &= m - 1;
+    const int col = gn0 + j;
+    if (col >= N) break;                                     // bits are in column order
+    float sc = v[j];
+    if (col == mcol) sc = mval;
+    if (sc != sc) sc = INFINITY;
+    if (sel_better(sc, col, tv, ti)) {
+      int q = K2 - 1;
+      while (q > 0) {
+        const float pv = lv[(q - 1) * kSelStride];
+        const int pi = li[(q - 1) * kSelStride];
+        if (!sel_better(sc, col, pv, pi)) break;
+        lv[q * kSelStride] = pv; li[q * kSelStride] = pi;
+        --q;
+      }
+      lv[q * kSelStride] = sc; li[q * kSelStride] = col;
+      tv = lv[(K2 - 1) * kSelStride]; ti = li[(K2 - 1) * kSelStride];
+    }
+  }
+  *tv_io = tv;
+  *ti_io = ti;
+}
 
 template <int BN, int NPASS>
 struct Cfg {
@@ -36,7 +78,12 @@ struct Cfg {
   static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 6 ? 6 : (200 * 1024) / STAGE_BYTES;
   static constexpr int TMEM_COLS = (2 * BN <= 256) ? 256 : 512;
   static constexpr int TR_BYTES = 8 * 32 * 32 * 4;           // one 32x32 fp32 transpose tile per epilogue warp
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + TR_BYTES;
+  // selection epilogue: per-thread candidate lists (kSelCap x (fp32 + int32) x 256 threads = 32 KB) share the transpose
+  // area and extend it where the stage ring leaves room
+  static constexpr int SEL_BYTES = kSelCap * kSelStride * 8;
+  static constexpr bool SEL_OK = STAGES * STAGE_BYTES + 1024 + 256 + SEL_BYTES <= 232448;
+  static constexpr int TAIL_BYTES = SEL_OK ? SEL_BYTES : TR_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + TAIL_BYTES;
 };
 
 template <int BN, bool A_MN, bool B_MN, int NPASS>
@@ -56,6 +103,18 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   const int MT = (p.M + UBM - 1) / UBM, NT = (p.N + BN - 1) / BN, KB = (p.K + UBK - 1) / UBK;
   const int kb_per = (KB + p.splitk - 1) / p.splitk;
   const int items = p.nbatch * p.splitk * MT * NT;
+  // work walk: items strided over the persistent grid; epi == 2: units = (row tile, column range) strided over the grid,
+  // each unit a run of consecutive column tiles of ONE row tile (the per-row candidate lists live across the run).  Unit
+  // u = range * MT + row tile, so the CTAs running at the same time sweep the same columns and share them through L2.
+  const bool epi2 = p.epi == 2;
+  const int units = epi2 ? MT * p.sel_S : items;
+#define TT_WALK_BEGIN                                                                      \
+  for (int u_ = blockIdx.x; u_ < units; u_ += gridDim.x) {                                 \
+    const int nb0_ = epi2 ? (u_ / MT) * p.sel_cpr : 0;                                     \
+    const int nb1_ = epi2 ? min(NT, nb0_ + p.sel_cpr) : 1;                                 \
+    for (int nb_ = nb0_; nb_ < nb1_; ++nb_) {                                              \
+      const int it = epi2 ? (u_ % MT) * NT + nb_ : u_;
+#define TT_WALK_END }}
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -76,7 +135,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         if (NPASS == 3) { tma_prefetch_desc(&p.a_lo[b]); tma_prefetch_desc(&p.b_lo[b]); }
       }
       int stage = 0, phase = 0;
-      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      TT_WALK_BEGIN
         const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
         const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -112,7 +171,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           }
           if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
         }
-      }
+      TT_WALK_END
     }
   } else if (warp == 1) {
     // ================================================================= MMA issuer
@@ -123,7 +182,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       constexpr uint32_t a_lbo = A_MN ? 8192 : 16, a_step = A_MN ? 2048 : 32;
       constexpr uint32_t b_lbo = B_MN ? 8192 : 16, b_step = B_MN ? 2048 : 32;
       int stage = 0, phase = 0, tile = 0;
-      for (int it = blockIdx.x; it < items; it += gridDim.x, ++tile) {
+      TT_WALK_BEGIN
         const int sp = (it / (NT * MT)) % p.splitk;
         const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
         const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
@@ -151,7 +210,8 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
         }
         mma_commit(&tfull[acc]);              // accumulator complete -> epilogue
-      }
+        ++tile;
+      TT_WALK_END
     }
   } else {
     // ================================================================= epilogue (warps 2..5)
@@ -160,13 +220,59 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     const int row = quarter * 32 + lane;
     const float alpha = p.alpha * (p.alpha_ptr ? __ldg(p.alpha_ptr) : 1.f);
     int tile = 0;
-    for (int it = blockIdx.x; it < items; it += gridDim.x, ++tile) {
+    // epi == 2 state: this thread's K2 best of (row, its half of the columns) for the current row tile, sorted
+    float* lv = tr_smem + (threadIdx.x - 64);                                 // [r * kSelStride]
+    int* li = reinterpret_cast<int*>(tr_smem + kSelCap * kSelStride) + (threadIdx.x - 64);
+    float tv = -INFINITY;
+    int ti = INT_MAX, cur_u = -1;
+    auto sel_flush = [&](int u_done) {                       // unit = (column range, row tile)
+      if (u_done < 0) return;
+      const int gmf = (u_done % MT) * UBM + row;
+      if (gmf >= p.M) return;
+      const int part = u_done / MT;
+      const int64_t o = ((int64_t)gmf * p.sel_slots + 2 * part + chalf) * 32;
+      for (int r = 0; r < p.sel_k2; ++r) { p.sel_v[o + r] = lv[r * kSelStride]; p.sel_i[o + r] = li[r * kSelStride]; }
+    };
+    TT_WALK_BEGIN
       const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
       const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
       const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+      ++tile;
+      if (epi2 && u_ != cur_u) {
+        sel_flush(cur_u);
+        cur_u = u_;
+        for (int r = 0; r < kSelCap; ++r) { lv[r * kSelStride] = -INFINITY; li[r * kSelStride] = INT_MAX; }
+        tv = -INFINITY; ti = INT_MAX;
+      }
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const int gm = m_blk * UBM + row;
+      if (p.epi == 2) {
+        const bool rok = gm < p.M;
+        const int64_t mcol = p.sel_mask_off >= 0 ? p.sel_mask_off + gm : -1;
+        const float mval = (p.sel_invx && rok) ? -1.f / __ldg(p.sel_invx + gm) : -1.f;
+        const int K2 = p.sel_k2;
+#pragma unroll 1
+        for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
+          const int gn0 = n_blk * BN + c0;
+          if (!rok || gn0 >= p.N) continue;
+          uint32_t m = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m |= !(v[j] < tv) ? (1u << j) : 0u;      // also set for NaN
+          if (gn0 <= mcol && mcol < gn0 + 32) m |= 1u << (int)(mcol - gn0);       // the masked column is judged by its mask value
+          if (m) {
+            float tmp[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) tmp[j] = v[j];
+            sel_insert_flagged(tmp, m, gn0, p.N, mcol, mval, K2, lv, li, &tv, &ti);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty[acc]);
+        continue;
+      }
       const float* bias = p.bias[bz];
       bool row_ok = gm < p.M;
       float* crow;
@@ -266,7 +372,8 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       }
       tc_fence_before();
       mbar_arrive(&tempty[acc]);
-    }
+    TT_WALK_END
+    if (epi2) sel_flush(cur_u);
   }
   tc_fence_before();
   __syncthreads();
@@ -332,7 +439,7 @@ static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t
     TT_CUDA(cudaGetDevice(&dev));
     TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  const int cap = (max_ctas > 0 && max_ctas < num_sms) ? max_ctas : num_sms;
+  const int cap = (max_ctas > 0 && max_ctas < num_sms && p.epi != 2) ? max_ctas : num_sms;
   const int grid = items < cap ? items : cap;
   note_launch();
   ProfScope prof(PROF_GEMM_TC, s);
@@ -343,6 +450,22 @@ static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t
 
 static_assert(sizeof(UmmaParams) <= sizeof(((UmmaPrepared*)0)->blob), "UmmaPrepared blob too small");
 
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+// slots per row of the selection epilogue's output for an [M, N] problem (must mirror umma_gemm_prepare)
+int umma_sel_slots(int32_t M, int64_t N) {
+  const int64_t MT = ceil_div(M, UBM), BN = N <= 128 ? 128 : 256, NT = ceil_div(N, BN);
+  int64_t S = sm_count() / MT < 1 ? 1 : sm_count() / MT;
+  if (S > NT) S = NT;
+  return (int)(2 * S);
+}
+
 int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   memset(out, 0, sizeof(*out));
   if (g.M <= 0 || g.N <= 0) { out->kind = -1; return TT_OK; }
@@ -351,7 +474,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   const int MT = (int)ceil_div(g.M, UBM), KB = (int)ceil_div(g.K, UBK);
   // BN = 128 when N is small, or when 256-wide tiles would leave most SMs idle
   int BN = g.N <= 128 ? 128 : 256;
-  if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0) BN = 128;
+  if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0 && g.epi != 2) BN = 128;
   UmmaParams& p = *reinterpret_cast<UmmaParams*>(out->blob);
   const int f16 = g.f16;
   const int64_t skipA = g.a_seg > 0 ? (int64_t)g.a_skip * (g.a_seg2 > 0 ? 2 : 1) : 0;
@@ -385,6 +508,17 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     TT_CHECK_ARG(g.splitk == 1 && (g.tl_Bp % 128) == 0 && (g.tl_Hc % 4) == 0 && (g.N % 4) == 0 && (g.M % 128) == 0,
                  "umma_gemm: tiled epilogue needs splitk 1, Bp %% 128 == 0, Hc %% 4 == 0");
   const int NT = (int)ceil_div(g.N, BN);
+  if (g.epi == 2) {
+    TT_CHECK_ARG(g.splitk == 1 && g.nbatch == 1 && !g.a_mn && !g.b_mn && g.sel_v && g.sel_i && g.sel_k2 >= 1 && g.sel_k2 <= kSelCap &&
+                     npass == 3,
+                 "umma_gemm: selection epilogue needs K-major operands, 3 passes, splitk 1, nbatch 1, 1 <= K2 <= 16");
+    p.sel_S = sm_count() / MT < 1 ? 1 : sm_count() / MT;
+    if (p.sel_S > NT) p.sel_S = NT;
+    p.sel_cpr = (int)ceil_div(NT, p.sel_S);
+    TT_CHECK_ARG(g.sel_slots >= 2 * p.sel_S, "umma_gemm: sel_slots too small");
+    p.sel_v = g.sel_v; p.sel_i = g.sel_i; p.sel_invx = g.sel_invx; p.sel_mask_off = g.sel_mask_off;
+    p.sel_k2 = g.sel_k2; p.sel_slots = g.sel_slots;
+  }
   int splitk = g.splitk;
   if (splitk <= 0) {
     splitk = 1;
@@ -403,6 +537,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   while (splitk > 1 && (int)ceil_div(KB, ceil_div(KB, splitk)) < splitk) --splitk;
   p.splitk = splitk;
   out->items = MT * NT * g.nbatch * splitk;
+  if (g.epi == 2) out->items = MT * p.sel_S;                 // grid = work units (row tile, column range)
   const int major = (!g.a_mn && !g.b_mn) ? 0 : (g.a_mn && g.b_mn) ? 1 : (!g.a_mn && g.b_mn) ? 2 : 3;
   if (major == 3) {
     set_error("umma_gemm: operand major / pass combination not instantiated");

@@ -46,11 +46,22 @@ struct UmmaGemm {
   int32_t a_seg, a_skip;    // A column remap: logical index i >= a_seg reads plane column i + a_skip
                             //   (K-major A: i = k ; MN-major A: i = m).  Both multiples of 64 (128 for MN-major).
   const float* alpha_ptr;   // optional device scalar multiplied into alpha (loss-scale undo)
-  int32_t epi;              // 0 row-major C ; 1 tiled C (see TiledOut)
+  int32_t epi;              // 0 row-major C ; 1 tiled C (see TiledOut) ; 2 no C: per-row candidate selection (below)
   int32_t rm_Bp, rm_B, rm_T;  // row-major epilogue: rows are time-major m = t*Bp + b -> C row b*T + t; b >= rm_B skipped
   int32_t tl_Bp, tl_G, tl_Hc; // tiled epilogue: C[(((t*MT + mt)*G + g)*(Hc/4) + u/4)*512 + row*4 + u%4],
                               //   t = m / Bp, mt = (m % Bp) / 128, row = m % 128, g = n / Hc, u = n % Hc, MT = Bp / 128
+  // ---- epi == 2: fused row top-K2 selection (K-H / K-F retrieval scan).  Scores never leave the SM: each epilogue thread
+  // (one accumulator row, half of the tile's columns) keeps the K2 best (score desc, column asc) of the columns it has
+  // seen for the current 128-row tile; a CTA walks a contiguous range of column tiles of one row tile and writes its lists
+  // to sel_v / sel_i [M][sel_slots][32] (slot = 2 * part + column half; unused entries keep the caller's initialisation).
+  // Column sel_mask_off + row (if sel_mask_off >= 0) scores -1 (times 1/sel_invx[row] when sel_invx is given: the scores
+  // are cosines scaled by |x|); NaN scores become +inf so the row fails the caller's acceptance test.
+  // Needs K-major operands, splitk 1, nbatch 1; umma_sel_slots() gives sel_slots for a problem shape.
+  float* sel_v; int* sel_i; const float* sel_invx;
+  int64_t sel_mask_off;
+  int32_t sel_k2, sel_slots;
 };
+int umma_sel_slots(int32_t M, int64_t N);
 int umma_gemm(const UmmaGemm& g, cudaStream_t s);
 // encode the tensor maps / pick the configuration once, launch many times (per-timestep GEMMs only change the first
 // plane row of A, given per batched problem)
