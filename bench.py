@@ -310,8 +310,17 @@ def eval_leg(args, dev, rank, world, group):
     noisy = torch.nn.functional.normalize(q + 0.5 * torch.randn(Q, D, device=dev, generator=g) / D ** 0.5, dim=1)
     docs[(rel % Nl)[mine]] = noisy[mine]
 
+    # the corpus index (row norms + hi/lo planes of the shard) is built once, like the reference's doc_encodings
+    # (simple_two_tower.py:318-331, app.py:38-60); its one-off cost is reported beside the per-scan time
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    index = tt.CorpusIndex(docs, cosine=True, index_base=rank * Nl)       # warm-up of the build kernels
+    torch.cuda.synchronize()
+    b0.record()
+    index = tt.CorpusIndex(docs, cosine=True, index_base=rank * Nl)
+    b1.record()
+
     def run():
-        val, idx = tt.sharded_search_topk(q, docs, rank * Nl, k=10, group=group)
+        val, idx = tt.sharded_search_topk(q, index, rank * Nl, k=10, group=group)
         return tt.mrr_recall(idx, rel)
 
     run()
@@ -331,8 +340,10 @@ def eval_leg(args, dev, rank, world, group):
     return {"metric": "eval queries/sec (score + top-10 + shard merge + MRR@10)", "value": Q / (ms * 1e-3), "unit": "queries/s",
             "queries": Q, "docs_per_gpu": Nl, "docs_total": Nl * world, "dim": D, "ms": ms, "mrr10": m["MRR"],
             "recall10": m["R@10"], "algorithmic_tflops": 2.0 * Q * Nl * world * D / (ms * 1e-3) / 1e12,
+            "index_build_ms": b0.elapsed_time(b1),
             "note": "bounded sample of BASELINE configs[4] (1e5 queries x 8.8 M docs): same shard size, fewer queries; "
-                    "includes the fp32 -> fp16 hi/lo conversion of the corpus shard on every call"}
+                    "the corpus index (norms + fp16 hi/lo planes of the shard) is built once outside the timed scans "
+                    "(index_build_ms), as the reference encodes its corpus once"}
 
 
 def run_ours(args):

@@ -222,6 +222,21 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
                  int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx,
                  void* workspace, uint64_t workspace_bytes, void* stream);
 
+/* K-H with a prebuilt corpus index.  The reference encodes the corpus once and then searches it query by query
+ * (simple_two_tower.py:318-340, validate_enhanced.py:61-80, app.py:38-60,94-101); the per-corpus part of tt_rows_topk
+ * (row norms and the 16-bit hi/lo planes the tensor route scores against) is likewise built once into a caller-owned
+ * device buffer of tt_corpus_index_bytes(N, D) bytes and reused by every tt_rows_topk_indexed call on the same y, N, D
+ * and mode (cosine planes hold normalised rows: an index is valid for the mode it was built with only).
+ * Results are bit-identical to tt_rows_topk. */
+uint64_t tt_corpus_index_bytes(int64_t N, int32_t D);
+int tt_corpus_index_build(const float* y, int64_t N, int32_t D, int32_t mode, void* index, uint64_t index_bytes,
+                          void* stream);
+uint64_t tt_rows_topk_indexed_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode);
+int tt_rows_topk_indexed(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
+                         int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx,
+                         const void* index, uint64_t index_bytes, void* workspace, uint64_t workspace_bytes,
+                         void* stream);
+
 /* K-I  merge S per-shard top-k lists ([S,Q,k] each, as all-gathered) into the global top-k:
  * order by score descending, then lowest global id.  Entries with idx < 0 are ignored. */
 int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k,
@@ -331,6 +346,9 @@ int tt_debug_wgrad_overlap(int32_t on);
  * which takes them off the critical path for every layer.  Needs tt_debug_wgrad_overlap(1); sequences shorter than 16*n
  * steps use fewer segments. */
 int tt_debug_bwd_segments(int32_t n);
+/* Selection epilogue of the retrieval scan (tt_rows_topk*, D <= 128): 1 (default) keeps the query tile of a work unit in
+ * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile.  Results are identical. */
+int tt_debug_sel_resident(int32_t on);
 
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);

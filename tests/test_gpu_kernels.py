@@ -456,6 +456,12 @@ def test_rows_topk_tensor_route_equals_exact_scan(cosine):
         lib.tt_set_engine(2)
     tv, ti = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine, mask_pos_offset=5, index_base=1000)
     assert torch.equal(ti, ei) and torch.equal(tv, ev)
+    try:                                       # query tile streamed with every corpus tile instead of kept in shared memory
+        lib.tt_debug_sel_resident(0)
+        sv, si = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine, mask_pos_offset=5, index_base=1000)
+    finally:
+        lib.tt_debug_sel_resident(1)
+    assert torch.equal(si, ei) and torch.equal(sv, ev)
     assert ti[0].tolist() == [1050] + list(range(1100, 1107))
 
 
@@ -497,6 +503,45 @@ def test_sharded_topk_merge_equals_global_and_index_base():
     # shards given in another order still merge to the same answer (lowest GLOBAL id wins ties)
     mv2, mi2 = Fn.topk_merge(torch.stack(vals[::-1]), torch.stack(idxs[::-1]))
     assert torch.equal(mi2, gi)
+
+
+@pytest.mark.parametrize("cosine", [False, True])
+@pytest.mark.parametrize("N", [100, 20000])
+def test_corpus_index_gives_identical_results_and_is_reusable(cosine, N):
+    """tt_corpus_index_build + tt_rows_topk_indexed == tt_rows_topk bit for bit (tensor route at N = 20000, exact scan at
+    N = 100 where the index holds norms only), for several query batches against ONE index, with a masked positive,
+    an index base, ties that overflow the candidate slots, and with the exact engine selected after the build."""
+    import two_towers_b200 as tt
+    from two_towers_b200 import _lib as L
+    rng = np.random.default_rng(1234 + N)
+    D, k = 128, 8
+    y = rng.standard_normal((N, D)).astype(np.float32) * rng.uniform(0.2, 3.0, (N, 1)).astype(np.float32)
+    y[60:90] = y[50]
+    yt = _t(y)
+    index = tt.CorpusIndex(yt, cosine=cosine, index_base=700)
+    assert len(index) == N
+    for Q, seed in ((1, 0), (300, 1), (130, 2)):
+        x = np.random.default_rng(seed).standard_normal((Q, D)).astype(np.float32)
+        x[0] = y[50]
+        xt = _t(x)
+        for off in (-1, 5):
+            wv, wi = Fn.rows_topk(xt, yt, k, cosine=cosine, mask_pos_offset=off, index_base=700)
+            gv, gi = index.search(xt, k, mask_pos_offset=off)
+            assert torch.equal(gi, wi) and torch.equal(gv, wv)
+    sv, si = tt.search_topk(xt, index, k=k, cosine=cosine)
+    assert torch.equal(si, Fn.rows_topk(xt, yt, k, cosine=cosine, index_base=700)[1])
+    with pytest.raises(ValueError):
+        tt.search_topk(xt, index, k=k, cosine=not cosine)
+    lib = L.lib()
+    try:
+        lib.tt_set_engine(0)                 # exact scan reading the index's norms
+        ev, ei = index.search(xt, k)
+    finally:
+        lib.tt_set_engine(2)
+    assert torch.equal(ei, si) and torch.equal(ev, sv)
+    # a buffer that is too small is refused, not overrun
+    with pytest.raises(RuntimeError):
+        Fn.rows_topk_indexed(xt, yt, index.buffer[:64], k, cosine=cosine)
 
 
 def test_mrr_ranks_and_recall():

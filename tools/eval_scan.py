@@ -10,13 +10,30 @@ dev = torch.device("cuda")
 g = torch.Generator(device=dev).manual_seed(1)
 q = torch.nn.functional.normalize(torch.randn(Q, 128, device=dev, generator=g), dim=1)
 docs = torch.nn.functional.normalize(torch.randn(N, 128, device=dev, generator=g), dim=1)
-tt.search_topk(q, docs, 10)
-torch.cuda.synchronize()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record()
-for _ in range(reps):
-    v, i = tt.search_topk(q, docs, 10)
-e1.record()
-torch.cuda.synchronize()
-ms = e0.elapsed_time(e1) / reps
-print(f"Q={Q} N={N}: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s, {2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic")
+from two_towers_b200 import _lib as L
+
+
+def timed(fn):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps, out
+
+
+index = tt.CorpusIndex(docs, cosine=True)
+ref = None
+for resident in (1, 0, 1):
+    L.lib().tt_debug_sel_resident(resident)
+    for name, fn in (("per-call corpus conversion", lambda: tt.search_topk(q, docs, 10)),
+                     ("prebuilt CorpusIndex", lambda: tt.search_topk(q, index, 10))):
+        ms, (v, i) = timed(fn)
+        if ref is None:
+            ref = (v.clone(), i.clone())
+        same = torch.equal(i, ref[1]) and torch.equal(v, ref[0])
+        print(f"Q={Q} N={N} resident_A={resident} {name}: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s, "
+              f"{2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic, identical={same}")

@@ -107,6 +107,10 @@ SIGNATURES = {
     "tt_hinge_bwd_dev": (C.c_int, [P, P, P, i32, i32, i32, F, F, P, P, P, P, P]),
     "tt_rows_topk_workspace": (u64, [i32, i64, i32, i32]),
     "tt_rows_topk": (C.c_int, [P, i32, P, i64, i32, i32, i32, i64, i64, P, P, P, u64, P]),
+    "tt_corpus_index_bytes": (u64, [i64, i32]),
+    "tt_corpus_index_build": (C.c_int, [P, i64, i32, i32, P, u64, P]),
+    "tt_rows_topk_indexed_workspace": (u64, [i32, i64, i32, i32]),
+    "tt_rows_topk_indexed": (C.c_int, [P, i32, P, i64, i32, i32, i32, i64, i64, P, P, P, u64, P, u64, P]),
     "tt_topk_merge": (C.c_int, [P, P, i32, i32, i32, P, P, P]),
     "tt_mrr_ranks": (C.c_int, [P, P, i32, i32, P, P, P]),
     "tt_hinge_fwd": (C.c_int, [P, P, P, i32, i32, i32, F, P, P]),
@@ -120,6 +124,7 @@ SIGNATURES = {
     "tt_debug_bwd_seq_mode": (C.c_int, [i32]),
     "tt_debug_wgrad_overlap": (C.c_int, [i32]),
     "tt_debug_bwd_segments": (C.c_int, [i32]),
+    "tt_debug_sel_resident": (C.c_int, [i32]),
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
     "tt_opt_step_workspace": (u64, [i32]),
     "tt_opt_step": (C.c_int, [P, P]),

@@ -48,12 +48,12 @@ struct ProfScope {
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline uint64_t align_up(uint64_t a, uint64_t b) { return (a + b - 1) / b * b; }
 
-// bump allocator over the caller's workspace
 // fp32 [rows][cols] -> fp16 hi/lo operand planes [rows][pitch] (pad columns zero); defined in score.cu
 int split_rows_f16(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, cudaStream_t s);
 int split_rows_f16_scaled(const float* x, int64_t rows, int cols, int64_t pitch, void* hi, void* lo, const float* row_scale,
                           cudaStream_t s);
 
+// bump allocator over the caller's workspace
 struct Workspace {
   char* base;
   uint64_t size, used;
@@ -122,6 +122,7 @@ struct GemmArgs {
   int32_t nbatch, splitk;
   int32_t seg_len, seg_stride, a_seg_off, b_seg_off;
   float alpha, beta;
+  int32_t shared_c;   // set by gemm_f32: the two batched problems add into ONE C (C[0] == C[1]) -> atomic accumulation
 };
 int gemm_f32(const GemmArgs& g, cudaStream_t s);
 

@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(NT) gemm_f32_kernel(GemmArgs g) {
       const int n = bn + tile_col(tx, j);
       if (n >= g.N) continue;
       float v = g.alpha * acc[i][j];
-      if (g.splitk > 1) {
+      if (g.splitk > 1 || g.shared_c) {
         if (split == 0 && bias) v += bias[n];
         atomicAdd(crow + n, v);
       } else {
@@ -145,10 +145,13 @@ int gemm_f32(const GemmArgs& gin, cudaStream_t s) {
       if (g.splitk < 1) g.splitk = 1;
     }
   }
-  if (g.splitk > 1) {
+  // two problems summed into one C (e.g. the two halves of a concatenated reduction dimension as ONE launch with twice
+  // the CTAs): x + y is commutative, so the result does not depend on which CTA arrives first
+  g.shared_c = g.nbatch == 2 && g.C[0] == g.C[1];
+  if (g.splitk > 1 || g.shared_c) {
     // atomics accumulate into C: pre-scale it by beta (0 -> clear)
     if (g.beta != 1.f) {
-      for (int b = 0; b < g.nbatch; ++b) {
+      for (int b = 0; b < (g.shared_c ? 1 : g.nbatch); ++b) {
         int64_t n = (int64_t)g.M * g.N;
         tt::note_launch(); scale_rows_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(g.C[b], g.ldc, g.M, g.N, g.beta);
       }

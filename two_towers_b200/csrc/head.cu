@@ -106,6 +106,11 @@ static inline GemmArgs nn_gemm(const float* A, int64_t lda, const float* Bm, int
   return g;
 }
 
+// second problem of the same shape in the same launch
+static inline void pair_with(GemmArgs& g, const float* A, const float* Bm, float* C) {
+  g.A[1] = A; g.B[1] = Bm; g.C[1] = C; g.bias[1] = nullptr; g.nbatch = 2;
+}
+
 static int check_head(const tt_head* a) {
   TT_CHECK_ARG(a && a->B > 0 && a->In > 0 && (a->In % 2) == 0 && a->P1 > 0 && a->D2 >= 0, "head: bad dims");
   TT_CHECK_ARG(a->v_lo && a->v_hi && a->w1 && a->b1 && a->ln_w && a->ln_b && a->y1 && a->stats && a->y2, "head: null buffer");
@@ -140,8 +145,12 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   TT_TRY(check_head(a));
   cudaStream_t s = (cudaStream_t)stream;
   const int B = a->B, In = a->In, P = a->P1, D2 = a->D2, Hh = In / 2;
-  TT_TRY(gemm_f32(nt_gemm(a->v_lo, Hh, a->w1, In, a->y1, P, a->b1, B, P, Hh, 0.f), s));
-  TT_TRY(gemm_f32(nt_gemm(a->v_hi, Hh, a->w1 + Hh, In, a->y1, P, nullptr, B, P, Hh, 1.f), s));
+  {
+    // y1 = v_lo W1[:, :Hh]^T + v_hi W1[:, Hh:]^T + b1: the two halves of the concatenated input as one launch
+    GemmArgs g = nt_gemm(a->v_lo, Hh, a->w1, In, a->y1, P, a->b1, B, P, Hh, 0.f);
+    pair_with(g, a->v_hi, a->w1 + Hh, a->y1);
+    TT_TRY(gemm_f32(g, s));
+  }
   const float pdrop = a->dropout_p;
   tt::note_launch(); ln_relu_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(a->y1, a->ln_w, a->ln_b, a->y2, a->stats, B, P, 1e-5f, pdrop,
                                                               pdrop > 0.f ? 1.f / (1.f - pdrop) : 1.f, a->seed, a->offset);
@@ -205,10 +214,15 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
   TT_TRY(colsum_f32(gm, P, B, P, a->d_ln_b, s));
   TT_TRY(colsum_f32(gx, P, B, P, a->d_ln_w, s));
   TT_TRY(colsum_f32(d_y1, P, B, P, a->d_b1, s));
-  TT_TRY(gemm_f32(tn_gemm(d_y1, P, f->v_lo, Hh, a->d_w1, In, P, Hh, B), s));
-  TT_TRY(gemm_f32(tn_gemm(d_y1, P, f->v_hi, Hh, a->d_w1 + Hh, In, P, Hh, B), s));
-  TT_TRY(gemm_f32(nn_gemm(d_y1, P, f->w1, In, a->d_v_lo, Hh, B, Hh, P, 0.f), s));
-  TT_TRY(gemm_f32(nn_gemm(d_y1, P, f->w1 + Hh, In, a->d_v_hi, Hh, B, Hh, P, 0.f), s));
+  {
+    // the two column halves of d_w1, and the two halves of d_v, as one launch each (disjoint outputs)
+    GemmArgs g = tn_gemm(d_y1, P, f->v_lo, Hh, a->d_w1, In, P, Hh, B);
+    pair_with(g, d_y1, f->v_hi, a->d_w1 + Hh);
+    TT_TRY(gemm_f32(g, s));
+    g = nn_gemm(d_y1, P, f->w1, In, a->d_v_lo, Hh, B, Hh, P, 0.f);
+    pair_with(g, d_y1, f->w1 + Hh, a->d_v_hi);
+    TT_TRY(gemm_f32(g, s));
+  }
   return TT_OK;
 }
 

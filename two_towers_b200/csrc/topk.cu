@@ -319,18 +319,30 @@ struct TopkWs {
   float *invx, *invy; unsigned int* ymin; float* pv; int64_t* pi;
   __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp;
 };
-static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, TopkWs* o) {
+// The per-corpus part of the scan (tt_corpus_index_build): row norms, their minimum, and the hi/lo planes of the tensor route
+struct CorpusIdx { float* invy; unsigned int* ymin; __half *yh, *yl; int64_t dp; bool planes; };
+static inline bool corpus_planes(int64_t N) { return umma_available() && N >= 256 && N < INT_MAX - 64; }
+static void carve_corpus(Workspace& w, int64_t N, int D, CorpusIdx* o) {
+  o->dp = plane_pitch(D);
+  o->invy = w.take<float>(N);
+  o->ymin = w.take<unsigned int>(64);
+  o->planes = corpus_planes(N);
+  o->yh = o->yl = nullptr;
+  if (o->planes) { o->yh = w.take<__half>(N * o->dp); o->yl = w.take<__half>(N * o->dp); }
+}
+static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, TopkWs* o, bool own_corpus = true) {
   const bool tc = topk_tc(N, k);
   o->invx = o->invy = nullptr;
-  if (mode == 1 || tc) { o->invx = w.take<float>(Q); o->invy = w.take<float>(N); }
+  if (mode == 1 || tc) { o->invx = w.take<float>(Q); if (own_corpus) o->invy = w.take<float>(N); }
   const int S = topk_splits(Q, N);
   o->pv = nullptr; o->pi = nullptr;
   if (S > 1) { o->pv = w.take<float>((int64_t)S * Q * 32); o->pi = w.take<int64_t>((int64_t)S * Q * 32); }
   if (tc) {
     o->dp = plane_pitch(D);
-    o->ymin = w.take<unsigned int>(64);
+    o->ymin = nullptr; o->yh = o->yl = nullptr;
+    if (own_corpus) o->ymin = w.take<unsigned int>(64);
     o->xh = w.take<__half>((int64_t)Q * o->dp); o->xl = w.take<__half>((int64_t)Q * o->dp);
-    o->yh = w.take<__half>(N * o->dp); o->yl = w.take<__half>(N * o->dp);
+    if (own_corpus) { o->yh = w.take<__half>(N * o->dp); o->yl = w.take<__half>(N * o->dp); }
     // candidate lists of the selection epilogue: [rows of a query chunk][slots][32]; full chunks and the last, shorter one
     const int QT = topk_qt(Q), rem = Q % QT;
     int64_t rows_slots = (int64_t)QT * umma_sel_slots(QT, N);
@@ -349,32 +361,74 @@ uint64_t tt_rows_topk_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode) {
   return w.used + 256;
 }
 
-int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
-                 int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx, void* workspace,
-                 uint64_t workspace_bytes, void* stream) {
+uint64_t tt_rows_topk_indexed_workspace(int32_t Q, int64_t N, int32_t D, int32_t mode) {
+  Workspace w(nullptr, 0);
+  TopkWs t;
+  carve_topk(w, Q, N, D, mode, 1, &t, false);
+  return w.used + 256;
+}
+
+uint64_t tt_corpus_index_bytes(int64_t N, int32_t D) {
+  Workspace w(nullptr, 0);
+  CorpusIdx c;
+  carve_corpus(w, N > 0 ? N : 0, D, &c);
+  return w.used + 256;
+}
+
+// per-corpus work of the scan: row norms (+ their minimum: the error bound of the dot mode) and the planes of the tensor route
+static int corpus_prepare(const float* y, int64_t N, int D, int mode, const CorpusIdx& c, cudaStream_t s) {
+  if (N <= 0) return TT_OK;
+  note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, c.invy);
+  TT_CUDA(cudaMemsetAsync(c.ymin, 0x7f, sizeof(unsigned int), s));
+  note_launch(); min_pos_kernel<<<296, 256, 0, s>>>(c.invy, N, c.ymin);
+  // cosine: the corpus rows go into the planes already divided by their norm (the exact re-score uses the fp32 rows)
+  if (c.planes) TT_TRY(split_rows_f16_scaled(y, N, D, c.dp, c.yh, c.yl, mode == 1 ? c.invy : nullptr, s));
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+int tt_corpus_index_build(const float* y, int64_t N, int32_t D, int32_t mode, void* index, uint64_t index_bytes, void* stream) {
+  TT_CHECK_ARG(y && index && N >= 0 && D > 0, "corpus_index_build: bad args");
+  TT_CHECK_ARG(mode == 0 || mode == 1, "corpus_index_build: mode must be 0 (dot) or 1 (cosine)");
+  Workspace w(index, index_bytes);
+  CorpusIdx c;
+  carve_corpus(w, N, D, &c);
+  if (!w.ok()) { set_error("corpus_index_build: index buffer too small"); return TT_ERR_WORKSPACE; }
+  return corpus_prepare(y, N, D, mode, c, (cudaStream_t)stream);
+}
+
+static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
+                          int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx, const void* index,
+                          uint64_t index_bytes, void* workspace, uint64_t workspace_bytes, void* stream) {
   TT_CHECK_ARG(x && y && out_val && out_idx && Q > 0 && N >= 0 && D > 0, "rows_topk: bad args");
   TT_CHECK_ARG(k >= 1 && k <= 32, "rows_topk: k=%d must be in [1,32]", k);
   TT_CHECK_ARG(mode == 0 || mode == 1, "rows_topk: mode must be 0 (dot) or 1 (cosine)");
   cudaStream_t s = (cudaStream_t)stream;
   Workspace w(workspace, workspace_bytes);
   TopkWs t;
-  carve_topk(w, Q, N, D, mode, k, &t);
+  carve_topk(w, Q, N, D, mode, k, &t, index == nullptr);
   if (!w.ok()) { set_error("rows_topk: workspace too small"); return TT_ERR_WORKSPACE; }
   const bool tc = topk_tc(N, k);
-  float* invx = t.invx; float* invy = t.invy;
-  if (invx) {
-    tt::note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, D, 1e-8f, invx);
-    if (N > 0) { note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy); }
+  CorpusIdx c;
+  if (index) {
+    Workspace wi(const_cast<void*>(index), index_bytes);
+    carve_corpus(wi, N, D, &c);
+    if (!wi.ok()) { set_error("rows_topk: corpus index too small for N=%lld D=%d", (long long)N, D); return TT_ERR_WORKSPACE; }
+    TT_CHECK_ARG(!tc || c.planes, "rows_topk: corpus index has no planes");
+  } else {
+    c.invy = t.invy; c.ymin = t.ymin; c.yh = t.yh; c.yl = t.yl; c.dp = plane_pitch(D); c.planes = tc;
+  }
+  float* invx = t.invx; float* invy = c.invy;
+  if (invx) { tt::note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, D, 1e-8f, invx); }
+  if (!index && invx && N > 0) {
+    if (tc) TT_TRY(corpus_prepare(y, N, D, mode, c, s));
+    else { note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy); }
   }
   const int* need = nullptr;
   if (tc) {
     // ---- tensor route: approximate tile scores -> candidates -> exact re-score -> acceptance
     const int K2 = cand_k2(k), QT = topk_qt(Q);
-    TT_CUDA(cudaMemsetAsync(t.ymin, 0x7f, sizeof(unsigned int), s));
-    note_launch(); min_pos_kernel<<<296, 256, 0, s>>>(invy, N, t.ymin);
     TT_TRY(split_rows_f16(x, Q, D, t.dp, t.xh, t.xl, s));
-    // cosine: the corpus rows go into the planes already divided by their norm (the exact re-score uses the fp32 rows)
-    TT_TRY(split_rows_f16_scaled(y, N, D, t.dp, t.yh, t.yl, mode == 1 ? invy : nullptr, s));
     for (int q0 = 0; q0 < Q; q0 += QT) {
       const int nq = Q - q0 < QT ? Q - q0 : QT;
       const int use_slots = umma_sel_slots(nq, N);
@@ -382,7 +436,7 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
       note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)nq * use_slots * 32, 256), 256, 0, s>>>(t.part_v, t.part_i, (int64_t)nq * use_slots * 32);
       UmmaGemm g{};
       g.A[0] = Planes{(const bf16*)(t.xh + (int64_t)q0 * t.dp), (const bf16*)(t.xl + (int64_t)q0 * t.dp), t.dp};
-      g.B[0] = Planes{(const bf16*)t.yh, (const bf16*)t.yl, t.dp};
+      g.B[0] = Planes{(const bf16*)c.yh, (const bf16*)c.yl, c.dp};
       g.M = nq; g.N = (int)N; g.K = D; g.nbatch = 1;
       g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
       g.epi = 2; g.sel_v = t.part_v; g.sel_i = t.part_i; g.sel_k2 = K2; g.sel_slots = use_slots;
@@ -394,7 +448,7 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
                                                                   t.lv + (int64_t)q0 * 32, t.li + (int64_t)q0 * 32);
     }
     note_launch();
-    rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, t.ymin, mask_pos_offset,
+    rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, c.ymin, mask_pos_offset,
                                                                 index_base, t.lv, t.li, out_val, out_idx, t.need);
     TT_LAUNCH_CHECK();
     need = t.need;
@@ -410,6 +464,26 @@ int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D
                                       S > 1 ? pv : out_val, S > 1 ? pi : out_idx, need);
   if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx, need); }
   TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
+int tt_rows_topk(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
+                 int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx, void* workspace,
+                 uint64_t workspace_bytes, void* stream) {
+  return rows_topk_impl(x, Q, y, N, D, k, mode, mask_pos_offset, index_base, out_val, out_idx, nullptr, 0, workspace,
+                        workspace_bytes, stream);
+}
+
+int tt_rows_topk_indexed(const float* x, int32_t Q, const float* y, int64_t N, int32_t D, int32_t k, int32_t mode,
+                         int64_t mask_pos_offset, int64_t index_base, float* out_val, int64_t* out_idx, const void* index,
+                         uint64_t index_bytes, void* workspace, uint64_t workspace_bytes, void* stream) {
+  TT_CHECK_ARG(index != nullptr, "rows_topk_indexed: null index");
+  return rows_topk_impl(x, Q, y, N, D, k, mode, mask_pos_offset, index_base, out_val, out_idx, index, index_bytes, workspace,
+                        workspace_bytes, stream);
+}
+
+int tt_debug_sel_resident(int32_t on) {
+  tt::umma_set_sel_resident(on);
   return TT_OK;
 }
 

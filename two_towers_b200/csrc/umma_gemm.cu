@@ -30,6 +30,8 @@ struct alignas(64) UmmaParams {
   float* sel_v; int* sel_i; const float* sel_invx;
   int64_t sel_mask_off;
   int32_t sel_k2, sel_slots, sel_S, sel_cpr;   // epi == 2: S column ranges of sel_cpr column tiles per row tile
+  int32_t a_res;   // epi == 2, K <= 128: the unit's A tile (every k-block, both planes) stays in shared memory for the whole
+                   //   run of column tiles; the stage ring carries B only (L2 -> SM traffic per tile 192 -> 128 KB)
 };
 __device__ __forceinline__ bool sel_better(float v, int i, float v2, int i2) { return v > v2 || (v == v2 && i < i2); }
 constexpr int kSelStride = 256;          // epilogue threads
@@ -97,6 +99,13 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]
   uint64_t* tempty = tfull + 2;                // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* afull = bars + 24;                 // resident-A mode: A tile of the unit loaded / no longer read
+  uint64_t* aempty = bars + 25;
+  // resident-A layout: [k-block][hi 16 KB | lo 16 KB] at the start of the ring area, then B stages of NPLANES * B_BYTES
+  constexpr int RES_A_BYTES = 2 * C_::NPLANES * C_::A_BYTES;
+  constexpr int RES_STAGE_BYTES = C_::NPLANES * C_::B_BYTES;
+  constexpr int RES_STAGES_ = (C_::STAGES * C_::STAGE_BYTES - RES_A_BYTES) / RES_STAGE_BYTES;
+  constexpr int RES_STAGES = RES_STAGES_ > C_::STAGES ? C_::STAGES : RES_STAGES_;
   float* tr_smem = reinterpret_cast<float*>(smem + C_::STAGES * C_::STAGE_BYTES + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -119,6 +128,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   if (threadIdx.x == 0) {
     for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
+    mbar_init(afull, 1); mbar_init(aempty, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
@@ -134,10 +144,31 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         tma_prefetch_desc(&p.a_hi[b]); tma_prefetch_desc(&p.b_hi[b]);
         if (NPASS == 3) { tma_prefetch_desc(&p.a_lo[b]); tma_prefetch_desc(&p.b_lo[b]); }
       }
-      int stage = 0, phase = 0;
+      int stage = 0, phase = 0, unit_n = 0;
       TT_WALK_BEGIN
         const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
         const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
+        if (!A_MN && !B_MN && p.a_res) {
+          if (nb_ == nb0_) {                   // new unit: its A tile, once the MMAs of the previous unit have read theirs
+            mbar_wait(aempty, (unit_n & 1) ^ 1);
+            ++unit_n;
+            mbar_arrive_expect_tx(afull, KB * C_::NPLANES * C_::A_BYTES);
+            for (int kb = 0; kb < KB; ++kb) {
+              uint8_t* sa = smem + kb * C_::NPLANES * C_::A_BYTES;
+              tma_load_2d(&p.a_hi[0], afull, sa, kb * UBK, m_blk * UBM + p.a_row0[0]);
+              if (NPASS == 3) tma_load_2d(&p.a_lo[0], afull, sa + C_::A_BYTES, kb * UBK, m_blk * UBM + p.a_row0[0]);
+            }
+          }
+          for (int kb = 0; kb < KB; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* sb = smem + RES_A_BYTES + stage * RES_STAGE_BYTES;
+            mbar_arrive_expect_tx(&full[stage], RES_STAGE_BYTES);
+            tma_load_2d(&p.b_hi[0], &full[stage], sb, kb * UBK, n_blk * BN + p.b_row0);
+            if (NPASS == 3) tma_load_2d(&p.b_lo[0], &full[stage], sb + C_::B_BYTES, kb * UBK, n_blk * BN + p.b_row0);
+            if (++stage == RES_STAGES) { stage = 0; phase ^= 1; }
+          }
+          continue;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* st = smem + stage * C_::STAGE_BYTES;
@@ -181,7 +212,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       // 8-k groups 1024 B apart (SBO).  One UMMA_K=16 step advances 32 B (K-major) or 2048 B (MN-major).
       constexpr uint32_t a_lbo = A_MN ? 8192 : 16, a_step = A_MN ? 2048 : 32;
       constexpr uint32_t b_lbo = B_MN ? 8192 : 16, b_step = B_MN ? 2048 : 32;
-      int stage = 0, phase = 0, tile = 0;
+      int stage = 0, phase = 0, tile = 0, unit_n = 0;
       TT_WALK_BEGIN
         const int sp = (it / (NT * MT)) % p.splitk;
         const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
@@ -189,6 +220,32 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
+        if (!A_MN && !B_MN && p.a_res) {
+          if (nb_ == nb0_) { mbar_wait(afull, unit_n & 1); ++unit_n; }
+          for (int kb = 0; kb < KB; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            const uint32_t sa_hi = smem_u32(smem + kb * C_::NPLANES * C_::A_BYTES), sa_lo = sa_hi + C_::A_BYTES;
+            const uint32_t sb_hi = smem_u32(smem + RES_A_BYTES + stage * RES_STAGE_BYTES), sb_lo = sb_hi + C_::B_BYTES;
+#pragma unroll
+            for (int term = 0; term < NPASS; ++term) {
+              const uint32_t sa = term == 1 ? sa_lo : sa_hi;
+              const uint32_t sb = term == 2 ? sb_lo : sb_hi;
+#pragma unroll
+              for (int k = 0; k < UBK / 16; ++k) {
+                const uint64_t ad = make_smem_desc(sa + k * a_step, a_lbo, 1024);
+                const uint64_t bd = make_smem_desc(sb + k * b_step, b_lbo, 1024);
+                mma_bf16_ss(d_tmem, ad, bd, idesc, (kb > 0 || term > 0 || k > 0) ? 1u : 0u);
+              }
+            }
+            mma_commit(&empty[stage]);
+            if (++stage == RES_STAGES) { stage = 0; phase ^= 1; }
+          }
+          mma_commit(&tfull[acc]);
+          if (nb_ == nb1_ - 1) mma_commit(aempty);     // the unit's A tile may be replaced once everything issued so far has read it
+          ++tile;
+          continue;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
@@ -459,6 +516,9 @@ static int sm_count() {
   return n;
 }
 // slots per row of the selection epilogue's output for an [M, N] problem (must mirror umma_gemm_prepare)
+static int g_sel_resident = 1;
+void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; }
+
 int umma_sel_slots(int32_t M, int64_t N) {
   const int64_t MT = ceil_div(M, UBM), BN = N <= 128 ? 128 : 256, NT = ceil_div(N, BN);
   int64_t S = sm_count() / MT < 1 ? 1 : sm_count() / MT;
@@ -518,6 +578,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     TT_CHECK_ARG(g.sel_slots >= 2 * p.sel_S, "umma_gemm: sel_slots too small");
     p.sel_v = g.sel_v; p.sel_i = g.sel_i; p.sel_invx = g.sel_invx; p.sel_mask_off = g.sel_mask_off;
     p.sel_k2 = g.sel_k2; p.sel_slots = g.sel_slots;
+    p.a_res = (g_sel_resident && BN == 256 && KB <= 2) ? 1 : 0;
   }
   int splitk = g.splitk;
   if (splitk <= 0) {

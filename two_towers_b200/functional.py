@@ -347,6 +347,37 @@ def rows_topk(x, y, k, cosine=True, mask_pos_offset=-1, index_base=0):
 
 
 @torch.no_grad()
+def corpus_index_build(y, cosine=True):
+    """Per-corpus part of rows_topk (row norms + hi/lo planes), built once: returns an opaque uint8 device buffer."""
+    lib = L.lib()
+    if not y.is_cuda:
+        raise RuntimeError("two_towers_b200: corpus index needs a CUDA tensor (no CPU fallback)")
+    N, D = y.shape
+    buf = torch.empty(lib.tt_corpus_index_bytes(N, D), dtype=torch.uint8, device=y.device)
+    with torch.cuda.device(y.device):
+        L.check(lib.tt_corpus_index_build(L.ptr(y), N, D, 1 if cosine else 0, buf.data_ptr(), buf.numel(), L.stream()),
+                "tt_corpus_index_build")
+    return buf
+
+
+@torch.no_grad()
+def rows_topk_indexed(x, y, index, k, cosine=True, mask_pos_offset=-1, index_base=0):
+    """rows_topk against a corpus whose index (corpus_index_build(y, cosine)) already exists; bit-identical results."""
+    lib = L.lib()
+    x = L.f32c(x)
+    Q, D = x.shape
+    N = y.shape[0]
+    mode = 1 if cosine else 0
+    val = torch.empty(Q, k, device=x.device, dtype=torch.float32)
+    idx = torch.empty(Q, k, device=x.device, dtype=torch.int64)
+    ws = L.workspace(lib.tt_rows_topk_indexed_workspace(Q, N, D, mode), x.device)
+    L.check(lib.tt_rows_topk_indexed(L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base),
+                                     L.ptr(val), L.ptr(idx), index.data_ptr(), index.numel(), ws.data_ptr(), ws.numel(),
+                                     L.stream()), "tt_rows_topk_indexed")
+    return val, idx
+
+
+@torch.no_grad()
 def topk_merge(vals, idx):
     """vals/idx [S,Q,k] per-shard lists -> global (vals, idx) [Q,k]."""
     lib = L.lib()

@@ -12,10 +12,38 @@ from . import distributed as dist_ops
 from . import functional as Fn
 
 
+class CorpusIndex:
+    """doc_encodings [N,D] + the per-corpus data of the scan (row norms, 16-bit hi/lo planes), built once.
+    The reference keeps `doc_encodings` and searches it query by query (simple_two_tower.py:318-340, app.py:38-60,
+    94-101); passing a CorpusIndex instead of the tensor to search_topk / sharded_search_topk skips the per-call
+    conversion of the corpus (results are bit-identical either way)."""
+
+    def __init__(self, doc_encodings, cosine=True, index_base=0):
+        from . import _lib as L
+        self.docs = L.f32c(doc_encodings)
+        self.cosine = bool(cosine)
+        self.index_base = int(index_base)
+        self.buffer = Fn.corpus_index_build(self.docs, self.cosine)
+
+    def __len__(self):
+        return self.docs.shape[0]
+
+    @torch.no_grad()
+    def search(self, query_vecs, k=10, mask_pos_offset=-1):
+        if query_vecs.dim() == 1:
+            query_vecs = query_vecs.unsqueeze(0)
+        return Fn.rows_topk_indexed(query_vecs, self.docs, self.buffer, k, cosine=self.cosine,
+                                    mask_pos_offset=mask_pos_offset, index_base=self.index_base)
+
+
 @torch.no_grad()
 def search_topk(query_vecs, doc_encodings, k=10, cosine=True, index_base=0):
-    """query_vecs [Q,D] (or [D]) vs doc_encodings [N,D] -> (scores [Q,k], indices int64 [Q,k]), best first;
-    ties go to the lowest index.  Same per-query result as cosine_similarity + topk in the reference."""
+    """query_vecs [Q,D] (or [D]) vs doc_encodings [N,D] (tensor or CorpusIndex) -> (scores [Q,k], indices int64 [Q,k]),
+    best first; ties go to the lowest index.  Same per-query result as cosine_similarity + topk in the reference."""
+    if isinstance(doc_encodings, CorpusIndex):
+        if doc_encodings.cosine != bool(cosine):
+            raise ValueError("search_topk: the CorpusIndex was built for the other score mode")
+        return doc_encodings.search(query_vecs, k)
     if query_vecs.dim() == 1:
         query_vecs = query_vecs.unsqueeze(0)
     return Fn.rows_topk(query_vecs, doc_encodings, k, cosine=cosine, index_base=index_base)
@@ -25,6 +53,8 @@ def search_topk(query_vecs, doc_encodings, k=10, cosine=True, index_base=0):
 def sharded_search_topk(query_vecs, local_docs, index_base, k=10, group=None, cosine=True):
     """Every rank holds a contiguous corpus shard starting at global id `index_base`; queries are replicated.
     Returns the identical global top-k on every rank."""
+    if isinstance(local_docs, CorpusIndex) and local_docs.index_base != int(index_base):
+        raise ValueError("sharded_search_topk: index_base differs from the CorpusIndex's")
     val, idx = search_topk(query_vecs, local_docs, k, cosine, index_base)
     W = dist_ops.world_size(group)
     if W == 1:
@@ -119,13 +149,14 @@ class SearchService:
             self.doc_embeddings = load_or_compute_doc_embeddings(model, self._enc(self.docs), cache_path, batch_size)
         if self.doc_embeddings.shape[0] != len(self.docs):
             raise ValueError("cached document embeddings do not match the document list")
+        self.index = CorpusIndex(self.doc_embeddings, cosine=True)
 
     @torch.no_grad()
     def search(self, query, top_k=None):
         k = min(top_k or self.top_k, len(self.docs))
         ids = self._enc([query]).to(self.device)
         qv = self.model.encode_query(ids)
-        scores, idx = search_topk(qv, self.doc_embeddings, k=k, cosine=True)
+        scores, idx = self.index.search(qv, k=k)
         truth = self.query_to_docs.get(query, [])
         results = []
         for r, (i, s) in enumerate(zip(idx[0].tolist(), scores[0].tolist())):
