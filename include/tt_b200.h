@@ -349,6 +349,8 @@ int tt_debug_bwd_segments(int32_t n);
 /* Selection epilogue of the retrieval scan (tt_rows_topk*, D <= 128): 1 (default) keeps the query tile of a work unit in
  * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile.  Results are identical. */
 int tt_debug_sel_resident(int32_t on);
+/* Same kernel: how many corpus tiles ahead the CTAs of a column range prefetch into L2 (0 = off). */
+int tt_debug_sel_prefetch(int32_t tiles);
 
 /* inverted dropout with the library's Philox4x32-10 stream: y = x * keep(seed, offset+i) / (1-p) */
 int tt_dropout(const float* x, float* y, int64_t n, float p, uint64_t seed, uint64_t offset, void* stream);

@@ -26,14 +26,12 @@ def timed(fn):
 
 
 index = tt.CorpusIndex(docs, cosine=True)
-ref = None
-for resident in (1, 0, 1):
+ms, ref = timed(lambda: tt.search_topk(q, docs, 10))
+print(f"Q={Q} N={N} per-call corpus conversion: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s")
+for resident, pf in ((0, 0), (1, 0), (1, 1), (1, 2), (1, 4), (1, 8), (1, 16), (1, 4)):
     L.lib().tt_debug_sel_resident(resident)
-    for name, fn in (("per-call corpus conversion", lambda: tt.search_topk(q, docs, 10)),
-                     ("prebuilt CorpusIndex", lambda: tt.search_topk(q, index, 10))):
-        ms, (v, i) = timed(fn)
-        if ref is None:
-            ref = (v.clone(), i.clone())
-        same = torch.equal(i, ref[1]) and torch.equal(v, ref[0])
-        print(f"Q={Q} N={N} resident_A={resident} {name}: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s, "
-              f"{2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic, identical={same}")
+    L.lib().tt_debug_sel_prefetch(pf)
+    ms, (v, i) = timed(lambda: tt.search_topk(q, index, 10))
+    same = torch.equal(i, ref[1]) and torch.equal(v, ref[0])
+    print(f"Q={Q} N={N} resident_A={resident} prefetch={pf} prebuilt CorpusIndex: {ms:.2f} ms per scan, "
+          f"{Q / ms * 1e3:.0f} queries/s, {2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic, identical={same}")

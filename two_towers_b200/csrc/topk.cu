@@ -486,6 +486,11 @@ int tt_debug_sel_resident(int32_t on) {
   tt::umma_set_sel_resident(on);
   return TT_OK;
 }
+int tt_debug_sel_prefetch(int32_t tiles) {
+  TT_CHECK_ARG(tiles >= 0 && tiles <= 64, "tt_debug_sel_prefetch: 0..64 column tiles");
+  tt::umma_set_sel_prefetch(tiles);
+  return TT_OK;
+}
 
 int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k, float* out_val,
                   int64_t* out_idx, void* stream) {

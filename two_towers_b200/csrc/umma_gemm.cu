@@ -30,28 +30,32 @@ struct alignas(64) UmmaParams {
   float* sel_v; int* sel_i; const float* sel_invx;
   int64_t sel_mask_off;
   int32_t sel_k2, sel_slots, sel_S, sel_cpr;   // epi == 2: S column ranges of sel_cpr column tiles per row tile
+  int32_t sel_pf;  // epi == 2, resident A: column tiles ahead that one CTA of each lockstep group prefetches into L2 (0 = off)
   int32_t a_res;   // epi == 2, K <= 128: the unit's A tile (every k-block, both planes) stays in shared memory for the whole
                    //   run of column tiles; the stage ring carries B only (L2 -> SM traffic per tile 192 -> 128 KB)
 };
 __device__ __forceinline__ bool sel_better(float v, int i, float v2, int i2) { return v > v2 || (v == v2 && i < i2); }
 constexpr int kSelStride = 256;          // epilogue threads
 constexpr int kSelCap = 16;              // list entries per thread held in shared memory (K2 <= kSelCap)
-// cold path of the selection epilogue: the columns flagged in `m` (bit j = column gn0 + j of this thread's row) are not
-// below the row's current K2-th best.  Kept out of line: inlined into the 32-way unrolled filter it made the hot loop
-// stream ~30 KB of code through the instruction cache per 32 columns.
-__device__ __noinline__ void sel_insert_flagged(const float* __restrict__ v, uint32_t m, int gn0, int N, int64_t mcol, float mval,
-                                                int K2, float* lv, int* li, float* tv_io, int* ti_io) {
-  // lv / li: this thread's sorted list in SHARED memory, entry r at [r * kSelStride] (thread-local arrays would live in
-  // L2: with ~200 KB of the SM's 256 KB carved out as shared memory almost no L1 is left, and one insertion - a serial
-  // chain of up to K2 dependent load / store pairs - cost microseconds)
+// cold path of the selection epilogue, entered by the whole (converged) warp when any lane has a column that is not below
+// its row's current K2-th best: bit j of a lane's `m` = column gn0 + j of its row.  The flagged scores are re-read from
+// tensor memory one column at a time (a warp-wide tcgen05.ld per column flagged by ANY lane - one or two per call) instead
+// of being passed in an indexable array: that array would live in local memory, i.e. in L2 with ~200 KB of the SM carved
+// out as shared memory.  Kept out of line: inlined into the filter it made the hot loop stream its code through the
+// instruction cache.
+__device__ __noinline__ void sel_insert_warp(uint32_t m, uint32_t taddr, int gn0, int N, int64_t mcol, float mval, int K2,
+                                             float* lv, int* li, float* tv_io, int* ti_io) {
+  // lv / li: this thread's sorted list in SHARED memory, entry r at [r * kSelStride]
   float tv = *tv_io;
   int ti = *ti_io;
-  while (m) {
-    const int j = __ffs(m) - 1;
-    m &= m - 1;
+  uint32_t wm = __reduce_or_sync(0xffffffffu, m);
+  while (wm) {
+    const int j = __ffs(wm) - 1;
+    wm &= wm - 1;
     const int col = gn0 + j;
-    if (col >= N) break;                                     // bits are in column order
-    float sc = v[j];
+    if (col >= N) break;                                     // bits are in column order (warp-uniform)
+    float sc = tmem_ld1(taddr + (uint32_t)j);
+    if (!((m >> j) & 1u)) continue;
     if (col == mcol) sc = mval;
     if (sc != sc) sc = INFINITY;
     if (sel_better(sc, col, tv, ti)) {
@@ -157,6 +161,14 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
               uint8_t* sa = smem + kb * C_::NPLANES * C_::A_BYTES;
               tma_load_2d(&p.a_hi[0], afull, sa, kb * UBK, m_blk * UBM + p.a_row0[0]);
               if (NPASS == 3) tma_load_2d(&p.a_lo[0], afull, sa + C_::A_BYTES, kb * UBK, m_blk * UBM + p.a_row0[0]);
+            }
+          }
+          // the corpus streams from HBM (it is several times the L2) and the ring holds one tile: the CTAs of a column range
+          // take turns to pull the tile sel_pf steps ahead into L2, so the loads below are L2 hits
+          if (p.sel_pf > 0 && nb_ + p.sel_pf < nb1_ && (nb_ + p.sel_pf) % MT == m_blk) {
+            for (int kb = 0; kb < KB; ++kb) {
+              tma_prefetch_l2_2d(&p.b_hi[0], kb * UBK, (nb_ + p.sel_pf) * BN + p.b_row0);
+              if (NPASS == 3) tma_prefetch_l2_2d(&p.b_lo[0], kb * UBK, (nb_ + p.sel_pf) * BN + p.b_row0);
             }
           }
           for (int kb = 0; kb < KB; ++kb) {
@@ -312,18 +324,29 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
 #pragma unroll 1
         for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
           float v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
+          const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0);
+          tmem_ld32(taddr, v);
           const int gn0 = n_blk * BN + c0;
-          if (!rok || gn0 >= p.N) continue;
-          uint32_t m = 0;
+          if (gn0 >= p.N) continue;
+          // hot path: one 3-input max tree over the 32 scores and ONE comparison with the row's K2-th best (NaN propagates
+          // and compares as "not below")
+          float t[12];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) m |= !(v[j] < tv) ? (1u << j) : 0u;      // also set for NaN
-          if (gn0 <= mcol && mcol < gn0 + 32) m |= 1u << (int)(mcol - gn0);       // the masked column is judged by its mask value
-          if (m) {
-            float tmp[32];
+          for (int j = 0; j < 10; ++j) t[j] = max3_nan(v[3 * j], v[3 * j + 1], v[3 * j + 2]);
+          t[10] = v[30]; t[11] = v[31];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) tmp[j] = v[j];
-            sel_insert_flagged(tmp, m, gn0, p.N, mcol, mval, K2, lv, li, &tv, &ti);
+          for (int j = 0; j < 4; ++j) t[j] = max3_nan(t[3 * j], t[3 * j + 1], t[3 * j + 2]);
+          const float mx = max3_nan(max3_nan(t[0], t[1], t[2]), t[3], t[3]);
+          const bool inmask = gn0 <= mcol && mcol < gn0 + 32;     // the masked column is judged by its mask value
+          const bool hit = rok && (!(mx < tv) || inmask);
+          if (__any_sync(0xffffffffu, hit)) {
+            uint32_t m = 0;
+            if (hit) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) m |= !(v[j] < tv) ? (1u << j) : 0u;      // also set for NaN
+              if (inmask) m |= 1u << (int)(mcol - gn0);
+            }
+            sel_insert_warp(m, taddr, gn0, p.N, mcol, mval, K2, lv, li, &tv, &ti);
           }
         }
         tc_fence_before();
@@ -516,8 +539,9 @@ static int sm_count() {
   return n;
 }
 // slots per row of the selection epilogue's output for an [M, N] problem (must mirror umma_gemm_prepare)
-static int g_sel_resident = 1;
+static int g_sel_resident = 1, g_sel_prefetch = 4;
 void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; }
+void umma_set_sel_prefetch(int tiles) { g_sel_prefetch = tiles < 0 ? 0 : tiles; }
 
 int umma_sel_slots(int32_t M, int64_t N) {
   const int64_t MT = ceil_div(M, UBM), BN = N <= 128 ? 128 : 256, NT = ceil_div(N, BN);
@@ -579,6 +603,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     p.sel_v = g.sel_v; p.sel_i = g.sel_i; p.sel_invx = g.sel_invx; p.sel_mask_off = g.sel_mask_off;
     p.sel_k2 = g.sel_k2; p.sel_slots = g.sel_slots;
     p.a_res = (g_sel_resident && BN == 256 && KB <= 2) ? 1 : 0;
+    p.sel_pf = g_sel_prefetch;
   }
   int splitk = g.splitk;
   if (splitk <= 0) {

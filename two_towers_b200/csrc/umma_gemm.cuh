@@ -62,6 +62,7 @@ struct UmmaGemm {
   int32_t sel_k2, sel_slots;
 };
 int umma_sel_slots(int32_t M, int64_t N);
+void umma_set_sel_prefetch(int tiles); // epi == 2, resident A: L2 prefetch distance in column tiles (0 = off)
 void umma_set_sel_resident(int on);   // epi == 2: keep the unit's A tile in shared memory (default on; off = stream it per tile)
 int umma_gemm(const UmmaGemm& g, cudaStream_t s);
 // encode the tensor maps / pick the configuration once, launch many times (per-timestep GEMMs only change the first
