@@ -349,6 +349,10 @@ int tt_debug_bwd_segments(int32_t n);
 /* Selection epilogue of the retrieval scan (tt_rows_topk*, D <= 128): 1 (default) keeps the query tile of a work unit in
  * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile.  Results are identical. */
 int tt_debug_sel_resident(int32_t on);
+/* Tensor passes of the candidate scan: 2 (default where D <= 128: x_hi y_hi + x_lo y_hi, acceptance bound 2^-11 + 2^-13) or
+ * 3 (adds x_hi y_lo, bound 2^-13).  The final top-k is bit-identical either way (exact re-score + acceptance test).
+ * 12 / 13: the same without the per-row lower bound the partitions of a row share (measurement only). */
+int tt_debug_sel_passes(int32_t passes);
 /* Same kernel: how many corpus tiles ahead the CTAs of a column range prefetch into L2 (0 = off). */
 int tt_debug_sel_prefetch(int32_t tiles);
 

@@ -465,6 +465,39 @@ def test_rows_topk_tensor_route_equals_exact_scan(cosine):
     assert ti[0].tolist() == [1050] + list(range(1100, 1107))
 
 
+@pytest.mark.parametrize("cosine", [False, True])
+@pytest.mark.parametrize("passes", [2, 3])
+def test_rows_topk_near_duplicates_inside_the_approximation_error(cosine, passes):
+    """Clusters of documents whose scores differ by less than the error of the tensor-engine candidate scan (2 passes:
+    2^-11, 3 passes: 2^-13): the approximate order inside a cluster is arbitrary, so the result is only right if the
+    acceptance test sends those rows to the exact scan (or the exact re-score restores the order).  Must equal the
+    exact engine bit for bit, for clusters smaller and larger than the candidate list."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(99)
+    Q, N, D, k = 200, 30000, 128, 10
+    y = rng.standard_normal((N, D)).astype(np.float32)
+    for c, (size, eps) in enumerate(((6, 3e-4), (12, 1e-4), (14, 3e-5), (40, 1e-4), (40, 2e-3))):
+        base = y[1000 * c + 17].copy()
+        for j in range(size):
+            y[1000 * c + 100 + 7 * j] = base + eps * rng.standard_normal(D).astype(np.float32)
+    x = rng.standard_normal((Q, D)).astype(np.float32)
+    for c in range(5):                                   # queries aimed at each cluster (and small variations of them)
+        for r in range(8):
+            x[8 * c + r] = y[1000 * c + 17] + 0.05 * r * rng.standard_normal(D).astype(np.float32)
+    try:
+        lib.tt_set_engine(0)
+        ev, ei = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine)
+    finally:
+        lib.tt_set_engine(2)
+    try:
+        lib.tt_debug_sel_passes(passes)
+        tv, ti = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine)
+    finally:
+        lib.tt_debug_sel_passes(2)
+    assert torch.equal(ti, ei) and torch.equal(tv, ev)
+
+
 def test_hard_negatives_match_golden_and_reference_semantics():
     g = load_golden("losses_mining")
     from two_towers_b200 import enhanced_two_tower as E

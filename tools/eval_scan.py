@@ -26,12 +26,14 @@ def timed(fn):
 
 
 index = tt.CorpusIndex(docs, cosine=True)
+L.lib().tt_debug_sel_passes(3)
 ms, ref = timed(lambda: tt.search_topk(q, docs, 10))
 print(f"Q={Q} N={N} per-call corpus conversion: {ms:.2f} ms per scan, {Q / ms * 1e3:.0f} queries/s")
-for resident, pf in ((0, 0), (1, 0), (1, 1), (1, 2), (1, 4), (1, 8), (1, 16), (1, 4)):
+for passes, resident, pf in ((13, 0, 0), (13, 1, 0), (12, 1, 0), (3, 1, 0), (2, 1, 0), (2, 1, 4), (3, 1, 0), (2, 1, 0)):
     L.lib().tt_debug_sel_resident(resident)
     L.lib().tt_debug_sel_prefetch(pf)
+    L.lib().tt_debug_sel_passes(passes)
     ms, (v, i) = timed(lambda: tt.search_topk(q, index, 10))
     same = torch.equal(i, ref[1]) and torch.equal(v, ref[0])
-    print(f"Q={Q} N={N} resident_A={resident} prefetch={pf} prebuilt CorpusIndex: {ms:.2f} ms per scan, "
+    print(f"Q={Q} N={N} passes={passes} resident_A={resident} prefetch={pf} prebuilt CorpusIndex: {ms:.2f} ms per scan, "
           f"{Q / ms * 1e3:.0f} queries/s, {2 * Q * N * 128 / ms / 1e9:.1f} TFLOP/s algorithmic, identical={same}")

@@ -211,10 +211,16 @@ constexpr int kCandSlack = 8;                                // candidates beyon
 constexpr int kSelMax = 16;                                  // list entries per row the selection epilogue keeps (umma_gemm.cu)
 static inline int cand_k2(int k) { return k + kCandSlack <= kSelMax ? k + kCandSlack : kSelMax; }
 constexpr float kScoreErr = 1.220703125e-4f;                 // 2^-13: bound on |approx - exact| / (|x| |y|), 4x margin
+// two-pass scan (x_hi y_hi + x_lo y_hi: the corpus contributes its fp16 hi plane only): rounding y to fp16 moves a score by
+// at most |x| |y - y_hi| <= 2^-11 |x| |y| (Cauchy-Schwarz over the element-wise half-ulp errors) on top of the bound above
+constexpr float kScoreErr2 = 4.8828125e-4f + kScoreErr;
+static int g_sel_passes = 2, g_sel_share = 1;
 
-__global__ void list_init_kernel(float* __restrict__ lv, int* __restrict__ li, int64_t n) {
+// candidate lists empty; the first nthr words of thr = bits of -inf (the rows' shared lower bounds)
+__global__ void list_init_kernel(float* __restrict__ lv, int* __restrict__ li, int64_t n, int* __restrict__ thr, int nthr) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) { lv[i] = -INFINITY; li[i] = INT_MAX; }
+  if (i < nthr) thr[i] = __float_as_int(-INFINITY);
 }
 __global__ void min_pos_kernel(const float* __restrict__ v, int64_t n, unsigned int* __restrict__ out) {
   float m = INFINITY;
@@ -258,7 +264,7 @@ __global__ void merge_parts_kernel(const float* __restrict__ part_v, const int* 
 __global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const float* __restrict__ Y, int D, int k, int K2,
                                     int cosine, const float* __restrict__ invx, const float* __restrict__ invy,
                                     const unsigned int* __restrict__ min_invy, int64_t mask_pos_offset, int64_t index_base,
-                                    const float* __restrict__ list_v, const int* __restrict__ list_i,
+                                    const float* __restrict__ list_v, const int* __restrict__ list_i, float score_err,
                                     float* __restrict__ out_val, int64_t* __restrict__ out_idx, int* __restrict__ need) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= Q) return;
@@ -290,7 +296,7 @@ __global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const fl
   if (at_k) e_k = __shfl_sync(0xffffffffu, ev, __ffs(at_k) - 1);
   // cosine: |x| invx and |y| invy are <= 1; dot: |x| max|y|  (invx = 1/max(|x|,1e-8))
   const float scale = cosine ? 1.f : (1.f / invx[row]) * (1.f / __uint_as_float(*min_invy));
-  const bool ok = !full || (e_k - a_min > kScoreErr * scale);               // false for NaN/inf as well
+  const bool ok = !full || (e_k - a_min > score_err * scale);               // false for NaN/inf as well
   if (lane == 0) need[row] = ok ? 0 : 1;
   if (ok && rank < k) {
     out_val[(int64_t)row * k + rank] = valid ? ev : -INFINITY;
@@ -317,7 +323,7 @@ static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma
 static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
 struct TopkWs {
   float *invx, *invy; unsigned int* ymin; float* pv; int64_t* pi;
-  __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp;
+  __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp; int* thr;
 };
 // The per-corpus part of the scan (tt_corpus_index_build): row norms, their minimum, and the hi/lo planes of the tensor route
 struct CorpusIdx { float* invy; unsigned int* ymin; __half *yh, *yl; int64_t dp; bool planes; };
@@ -351,6 +357,7 @@ static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, T
     o->part_v = w.take<float>(rows_slots * 32);
     o->part_i = w.take<int>(rows_slots * 32);
     o->lv = w.take<float>((int64_t)Q * 32); o->li = w.take<int>((int64_t)Q * 32); o->need = w.take<int>(Q);
+    o->thr = w.take<int>(Q);
   }
 }
 
@@ -428,17 +435,20 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
   if (tc) {
     // ---- tensor route: approximate tile scores -> candidates -> exact re-score -> acceptance
     const int K2 = cand_k2(k), QT = topk_qt(Q);
+    const bool two = g_sel_passes == 2 && umma_sel_two_ok(D);
     TT_TRY(split_rows_f16(x, Q, D, t.dp, t.xh, t.xl, s));
     for (int q0 = 0; q0 < Q; q0 += QT) {
       const int nq = Q - q0 < QT ? Q - q0 : QT;
       const int use_slots = umma_sel_slots(nq, N);
       TT_CHECK_ARG((int64_t)nq * use_slots <= t.slots, "rows_topk: part buffer too small");
-      note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)nq * use_slots * 32, 256), 256, 0, s>>>(t.part_v, t.part_i, (int64_t)nq * use_slots * 32);
+      note_launch(); list_init_kernel<<<(unsigned)ceil_div((int64_t)nq * use_slots * 32, 256), 256, 0, s>>>(t.part_v, t.part_i, (int64_t)nq * use_slots * 32, t.thr + q0, nq);
       UmmaGemm g{};
       g.A[0] = Planes{(const bf16*)(t.xh + (int64_t)q0 * t.dp), (const bf16*)(t.xl + (int64_t)q0 * t.dp), t.dp};
       g.B[0] = Planes{(const bf16*)c.yh, (const bf16*)c.yl, c.dp};
       g.M = nq; g.N = (int)N; g.K = D; g.nbatch = 1;
       g.alpha = 1.f; g.beta = 0.f; g.splitk = 1; g.f16 = 1; g.npass = 3;
+      g.sel_two = two ? 1 : 0;
+      g.sel_thr = g_sel_share ? t.thr + q0 : nullptr;
       g.epi = 2; g.sel_v = t.part_v; g.sel_i = t.part_i; g.sel_k2 = K2; g.sel_slots = use_slots;
       g.sel_invx = mode == 1 ? invx + q0 : nullptr;
       g.sel_mask_off = mask_pos_offset >= 0 ? mask_pos_offset + q0 : -1;
@@ -449,7 +459,7 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
     }
     note_launch();
     rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, c.ymin, mask_pos_offset,
-                                                                index_base, t.lv, t.li, out_val, out_idx, t.need);
+                                                                index_base, t.lv, t.li, two ? kScoreErr2 : kScoreErr, out_val, out_idx, t.need);
     TT_LAUNCH_CHECK();
     need = t.need;
     if (mode == 0) { invx = nullptr; invy = nullptr; }      // the exact scan applies norms only for the cosine
@@ -484,6 +494,12 @@ int tt_rows_topk_indexed(const float* x, int32_t Q, const float* y, int64_t N, i
 
 int tt_debug_sel_resident(int32_t on) {
   tt::umma_set_sel_resident(on);
+  return TT_OK;
+}
+int tt_debug_sel_passes(int32_t passes) {
+  TT_CHECK_ARG(passes == 2 || passes == 3 || passes == 12 || passes == 13, "tt_debug_sel_passes: 2 or 3 (+10: no shared row bound)");
+  tt::g_sel_passes = passes % 10;
+  tt::g_sel_share = passes < 10;
   return TT_OK;
 }
 int tt_debug_sel_prefetch(int32_t tiles) {

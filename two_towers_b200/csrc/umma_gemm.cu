@@ -30,6 +30,9 @@ struct alignas(64) UmmaParams {
   float* sel_v; int* sel_i; const float* sel_invx;
   int64_t sel_mask_off;
   int32_t sel_k2, sel_slots, sel_S, sel_cpr;   // epi == 2: S column ranges of sel_cpr column tiles per row tile
+  int* sel_thr;    // epi == 2: [M] per-row lower bound of the final K2-th best score (float bits; -inf at launch), shared by all
+                   //   partitions of a row
+  int32_t sel_two; // epi == 2, resident A: B contributes its hi plane only (hi*hi + lo*hi): 2 of the 3 passes, half the B bytes
   int32_t sel_pf;  // epi == 2, resident A: column tiles ahead that one CTA of each lockstep group prefetches into L2 (0 = off)
   int32_t a_res;   // epi == 2, K <= 128: the unit's A tile (every k-block, both planes) stays in shared memory for the whole
                    //   run of column tiles; the stage ring carries B only (L2 -> SM traffic per tile 192 -> 128 KB)
@@ -43,11 +46,15 @@ constexpr int kSelCap = 16;              // list entries per thread held in shar
 // of being passed in an indexable array: that array would live in local memory, i.e. in L2 with ~200 KB of the SM carved
 // out as shared memory.  Kept out of line: inlined into the filter it made the hot loop stream its code through the
 // instruction cache.
+struct SelState { float tv; int ti; int wpos; };   // the WORST entry of the thread's list (score, column) and its position
 __device__ __noinline__ void sel_insert_warp(uint32_t m, uint32_t taddr, int gn0, int N, int64_t mcol, float mval, int K2,
-                                             float* lv, int* li, float* tv_io, int* ti_io) {
-  // lv / li: this thread's sorted list in SHARED memory, entry r at [r * kSelStride]
-  float tv = *tv_io;
-  int ti = *ti_io;
+                                             float* lv, int* li, SelState* st, int* thr) {
+  // lv / li: this thread's K2 candidates in SHARED memory, entry r at [r * kSelStride], in NO particular order: a new
+  // candidate replaces the worst entry and the new worst is found by one pass over the K2 entries (independent loads;
+  // keeping the list sorted cost a chain of ~K2/2 dependent load-compare-store steps per insertion).
+  float tv = st->tv;
+  int ti = st->ti, wpos = st->wpos;
+  bool changed = false;
   uint32_t wm = __reduce_or_sync(0xffffffffu, m);
   while (wm) {
     const int j = __ffs(wm) - 1;
@@ -59,20 +66,21 @@ __device__ __noinline__ void sel_insert_warp(uint32_t m, uint32_t taddr, int gn0
     if (col == mcol) sc = mval;
     if (sc != sc) sc = INFINITY;
     if (sel_better(sc, col, tv, ti)) {
-      int q = K2 - 1;
-      while (q > 0) {
-        const float pv = lv[(q - 1) * kSelStride];
-        const int pi = li[(q - 1) * kSelStride];
-        if (!sel_better(sc, col, pv, pi)) break;
-        lv[q * kSelStride] = pv; li[q * kSelStride] = pi;
-        --q;
+      lv[wpos * kSelStride] = sc; li[wpos * kSelStride] = col;
+      tv = lv[0]; ti = li[0]; wpos = 0;
+#pragma unroll 4
+      for (int r = 1; r < K2; ++r) {
+        const float pv = lv[r * kSelStride];
+        const int pi = li[r * kSelStride];
+        if (sel_better(tv, ti, pv, pi)) { tv = pv; ti = pi; wpos = r; }
       }
-      lv[q * kSelStride] = sc; li[q * kSelStride] = col;
-      tv = lv[(K2 - 1) * kSelStride]; ti = li[(K2 - 1) * kSelStride];
+      changed = true;
     }
   }
-  *tv_io = tv;
-  *ti_io = ti;
+  st->tv = tv; st->ti = ti; st->wpos = wpos;
+  // publish the row's K2-th best so far: every other partition of the row (the other column half in this CTA, other column
+  // ranges in other CTAs) may skip scores below it.  Positive floats order like their bit patterns; the word starts at -inf.
+  if (changed && thr && tv > 0.f) atomicMax(thr, __float_as_int(tv));
 }
 
 template <int BN, int NPASS>
@@ -103,13 +111,15 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]
   uint64_t* tempty = tfull + 2;                // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint64_t* afull = bars + 24;                 // resident-A mode: A tile of the unit loaded / no longer read
-  uint64_t* aempty = bars + 25;
+  uint64_t* afull = bars + 26;                 // resident-A mode: A tile of the unit loaded / no longer read
+  uint64_t* aempty = bars + 27;
+  uint64_t* rfull = bars + 17;                 // resident-A mode: its own B ring barriers [4] (the ring may be deeper than STAGES)
+  uint64_t* rempty = bars + 21;                // [4]
   // resident-A layout: [k-block][hi 16 KB | lo 16 KB] at the start of the ring area, then B stages of NPLANES * B_BYTES
   constexpr int RES_A_BYTES = 2 * C_::NPLANES * C_::A_BYTES;
-  constexpr int RES_STAGE_BYTES = C_::NPLANES * C_::B_BYTES;
-  constexpr int RES_STAGES_ = (C_::STAGES * C_::STAGE_BYTES - RES_A_BYTES) / RES_STAGE_BYTES;
-  constexpr int RES_STAGES = RES_STAGES_ > C_::STAGES ? C_::STAGES : RES_STAGES_;
+  const int res_stage_bytes = (p.sel_two ? 1 : C_::NPLANES) * C_::B_BYTES;
+  const int res_stages_ = (C_::STAGES * C_::STAGE_BYTES - RES_A_BYTES) / res_stage_bytes;
+  const int res_stages = res_stages_ > 4 ? 4 : res_stages_;
   float* tr_smem = reinterpret_cast<float*>(smem + C_::STAGES * C_::STAGE_BYTES + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -133,6 +143,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
     mbar_init(afull, 1); mbar_init(aempty, 1);
+    for (int i = 0; i < 4; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
@@ -168,16 +179,16 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           if (p.sel_pf > 0 && nb_ + p.sel_pf < nb1_ && (nb_ + p.sel_pf) % MT == m_blk) {
             for (int kb = 0; kb < KB; ++kb) {
               tma_prefetch_l2_2d(&p.b_hi[0], kb * UBK, (nb_ + p.sel_pf) * BN + p.b_row0);
-              if (NPASS == 3) tma_prefetch_l2_2d(&p.b_lo[0], kb * UBK, (nb_ + p.sel_pf) * BN + p.b_row0);
+              if (NPASS == 3 && !p.sel_two) tma_prefetch_l2_2d(&p.b_lo[0], kb * UBK, (nb_ + p.sel_pf) * BN + p.b_row0);
             }
           }
           for (int kb = 0; kb < KB; ++kb) {
-            mbar_wait(&empty[stage], phase ^ 1);
-            uint8_t* sb = smem + RES_A_BYTES + stage * RES_STAGE_BYTES;
-            mbar_arrive_expect_tx(&full[stage], RES_STAGE_BYTES);
-            tma_load_2d(&p.b_hi[0], &full[stage], sb, kb * UBK, n_blk * BN + p.b_row0);
-            if (NPASS == 3) tma_load_2d(&p.b_lo[0], &full[stage], sb + C_::B_BYTES, kb * UBK, n_blk * BN + p.b_row0);
-            if (++stage == RES_STAGES) { stage = 0; phase ^= 1; }
+            mbar_wait(&rempty[stage], phase ^ 1);
+            uint8_t* sb = smem + RES_A_BYTES + stage * res_stage_bytes;
+            mbar_arrive_expect_tx(&rfull[stage], res_stage_bytes);
+            tma_load_2d(&p.b_hi[0], &rfull[stage], sb, kb * UBK, n_blk * BN + p.b_row0);
+            if (NPASS == 3 && !p.sel_two) tma_load_2d(&p.b_lo[0], &rfull[stage], sb + C_::B_BYTES, kb * UBK, n_blk * BN + p.b_row0);
+            if (++stage == res_stages) { stage = 0; phase ^= 1; }
           }
           continue;
         }
@@ -234,13 +245,15 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         const uint32_t d_tmem = tmem_base + acc * BN;
         if (!A_MN && !B_MN && p.a_res) {
           if (nb_ == nb0_) { mbar_wait(afull, unit_n & 1); ++unit_n; }
+          const int nterms = p.sel_two ? 2 : NPASS;
           for (int kb = 0; kb < KB; ++kb) {
-            mbar_wait(&full[stage], phase);
+            mbar_wait(&rfull[stage], phase);
             tc_fence_after();
             const uint32_t sa_hi = smem_u32(smem + kb * C_::NPLANES * C_::A_BYTES), sa_lo = sa_hi + C_::A_BYTES;
-            const uint32_t sb_hi = smem_u32(smem + RES_A_BYTES + stage * RES_STAGE_BYTES), sb_lo = sb_hi + C_::B_BYTES;
+            const uint32_t sb_hi = smem_u32(smem + RES_A_BYTES + stage * res_stage_bytes), sb_lo = sb_hi + C_::B_BYTES;
 #pragma unroll
             for (int term = 0; term < NPASS; ++term) {
+              if (term >= nterms) break;
               const uint32_t sa = term == 1 ? sa_lo : sa_hi;
               const uint32_t sb = term == 2 ? sb_lo : sb_hi;
 #pragma unroll
@@ -250,8 +263,8 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
                 mma_bf16_ss(d_tmem, ad, bd, idesc, (kb > 0 || term > 0 || k > 0) ? 1u : 0u);
               }
             }
-            mma_commit(&empty[stage]);
-            if (++stage == RES_STAGES) { stage = 0; phase ^= 1; }
+            mma_commit(&rempty[stage]);
+            if (++stage == res_stages) { stage = 0; phase ^= 1; }
           }
           mma_commit(&tfull[acc]);
           if (nb_ == nb1_ - 1) mma_commit(aempty);     // the unit's A tile may be replaced once everything issued so far has read it
@@ -292,8 +305,8 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     // epi == 2 state: this thread's K2 best of (row, its half of the columns) for the current row tile, sorted
     float* lv = tr_smem + (threadIdx.x - 64);                                 // [r * kSelStride]
     int* li = reinterpret_cast<int*>(tr_smem + kSelCap * kSelStride) + (threadIdx.x - 64);
-    float tv = -INFINITY;
-    int ti = INT_MAX, cur_u = -1;
+    SelState st{-INFINITY, INT_MAX, 0};
+    int cur_u = -1;
     auto sel_flush = [&](int u_done) {                       // unit = (column range, row tile)
       if (u_done < 0) return;
       const int gmf = (u_done % MT) * UBM + row;
@@ -311,11 +324,15 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         sel_flush(cur_u);
         cur_u = u_;
         for (int r = 0; r < kSelCap; ++r) { lv[r * kSelStride] = -INFINITY; li[r * kSelStride] = INT_MAX; }
-        tv = -INFINITY; ti = INT_MAX;
+        st.tv = -INFINITY; st.ti = INT_MAX; st.wpos = 0;
       }
+      const int gm = m_blk * UBM + row;
+      // the row's shared lower bound, read once per tile (issued before the wait for the accumulator; a stale value is
+      // still a valid bound, it only filters less)
+      float gthr = -INFINITY;
+      if (epi2 && p.sel_thr && gm < p.M) gthr = __int_as_float(__ldcg(p.sel_thr + gm));
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      const int gm = m_blk * UBM + row;
       if (p.epi == 2) {
         const bool rok = gm < p.M;
         const int64_t mcol = p.sel_mask_off >= 0 ? p.sel_mask_off + gm : -1;
@@ -338,6 +355,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
           for (int j = 0; j < 4; ++j) t[j] = max3_nan(t[3 * j], t[3 * j + 1], t[3 * j + 2]);
           const float mx = max3_nan(max3_nan(t[0], t[1], t[2]), t[3], t[3]);
           const bool inmask = gn0 <= mcol && mcol < gn0 + 32;     // the masked column is judged by its mask value
+          const float tv = fmaxf(st.tv, gthr);
           const bool hit = rok && (!(mx < tv) || inmask);
           if (__any_sync(0xffffffffu, hit)) {
             uint32_t m = 0;
@@ -346,7 +364,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
               for (int j = 0; j < 32; ++j) m |= !(v[j] < tv) ? (1u << j) : 0u;      // also set for NaN
               if (inmask) m |= 1u << (int)(mcol - gn0);
             }
-            sel_insert_warp(m, taddr, gn0, p.N, mcol, mval, K2, lv, li, &tv, &ti);
+            sel_insert_warp(m, taddr, gn0, p.N, mcol, mval, K2, lv, li, &st, (rok && p.sel_thr) ? p.sel_thr + gm : nullptr);
           }
         }
         tc_fence_before();
@@ -543,6 +561,8 @@ static int g_sel_resident = 1, g_sel_prefetch = 4;
 void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; }
 void umma_set_sel_prefetch(int tiles) { g_sel_prefetch = tiles < 0 ? 0 : tiles; }
 
+bool umma_sel_two_ok(int32_t K) { return g_sel_resident && ceil_div(K, UBK) <= 2; }
+
 int umma_sel_slots(int32_t M, int64_t N) {
   const int64_t MT = ceil_div(M, UBM), BN = N <= 128 ? 128 : 256, NT = ceil_div(N, BN);
   int64_t S = sm_count() / MT < 1 ? 1 : sm_count() / MT;
@@ -604,6 +624,9 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     p.sel_k2 = g.sel_k2; p.sel_slots = g.sel_slots;
     p.a_res = (g_sel_resident && BN == 256 && KB <= 2) ? 1 : 0;
     p.sel_pf = g_sel_prefetch;
+    TT_CHECK_ARG(!g.sel_two || p.a_res, "umma_gemm: two-pass selection needs the resident-A mode (K <= 128)");
+    p.sel_two = g.sel_two ? 1 : 0;
+    p.sel_thr = g.sel_thr;
   }
   int splitk = g.splitk;
   if (splitk <= 0) {

@@ -53,14 +53,19 @@ struct UmmaGemm {
   // ---- epi == 2: fused row top-K2 selection (K-H / K-F retrieval scan).  Scores never leave the SM: each epilogue thread
   // (one accumulator row, half of the tile's columns) keeps the K2 best (score desc, column asc) of the columns it has
   // seen for the current 128-row tile; a CTA walks a contiguous range of column tiles of one row tile and writes its lists
-  // to sel_v / sel_i [M][sel_slots][32] (slot = 2 * part + column half; unused entries keep the caller's initialisation).
+  // (in no particular order) to sel_v / sel_i [M][sel_slots][32] (slot = 2 * part + column half; unused entries keep the
+  // caller's initialisation).
   // Column sel_mask_off + row (if sel_mask_off >= 0) scores -1 (times 1/sel_invx[row] when sel_invx is given: the scores
   // are cosines scaled by |x|); NaN scores become +inf so the row fails the caller's acceptance test.
   // Needs K-major operands, splitk 1, nbatch 1; umma_sel_slots() gives sel_slots for a problem shape.
   float* sel_v; int* sel_i; const float* sel_invx;
   int64_t sel_mask_off;
   int32_t sel_k2, sel_slots;
+  int* sel_thr;             // optional [M] ints, every word initialised to the bits of -inf (0xff800000) before the launch: the
+                            //   partitions of a row share a lower bound of its K2-th best score through it
+  int32_t sel_two;          // B's lo plane is not used (hi*hi + lo*hi only: |error| <= 2^-11 |a||b| more); needs umma_sel_two_ok(K)
 };
+bool umma_sel_two_ok(int32_t K);
 int umma_sel_slots(int32_t M, int64_t N);
 void umma_set_sel_prefetch(int tiles); // epi == 2, resident A: L2 prefetch distance in column tiles (0 = off)
 void umma_set_sel_resident(int on);   // epi == 2: keep the unit's A tile in shared memory (default on; off = stream it per tile)
