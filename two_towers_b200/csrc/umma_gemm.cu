@@ -47,13 +47,16 @@ constexpr int kSelCap = 16;              // list entries per thread held in shar
 // out as shared memory.  Kept out of line: inlined into the filter it made the hot loop stream its code through the
 // instruction cache.
 struct SelState { float tv; int ti; int wpos; };   // the WORST entry of the thread's list (score, column) and its position
-__device__ __noinline__ void sel_insert_warp(uint32_t m, uint32_t taddr, int gn0, int N, int64_t mcol, float mval, int K2,
-                                             float* lv, int* li, SelState* st, int* thr) {
-  // lv / li: this thread's K2 candidates in SHARED memory, entry r at [r * kSelStride], in NO particular order: a new
-  // candidate replaces the worst entry and the new worst is found by one pass over the K2 entries (independent loads;
-  // keeping the list sorted cost a chain of ~K2/2 dependent load-compare-store steps per insertion).
-  float tv = st->tv;
-  int ti = st->ti, wpos = st->wpos;
+__device__ __forceinline__ float lds_f32(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ int lds_s32(uint32_t a) { int v; asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts_s32(uint32_t a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+// lv_s / li_s: shared-space addresses of this thread's K2 candidates, entry r at + r * kSelStride * 4, in NO particular order:
+// a new candidate replaces the worst entry and the new worst is found by one pass over the entries - 2 * kSelCap independent
+// shared loads and a 4-level compare tree (keeping the list sorted cost a chain of ~K2/2 dependent load-compare-store
+// steps per insertion).  State goes in and out by value (registers): by reference it lived in local memory = L2.
+__device__ __noinline__ SelState sel_insert_warp(uint32_t m, uint32_t taddr, int gn0, int N, int64_t mcol, float mval, int K2,
+                                                 uint32_t lv_s, uint32_t li_s, SelState st, int* thr) {
   bool changed = false;
   uint32_t wm = __reduce_or_sync(0xffffffffu, m);
   while (wm) {
@@ -65,22 +68,33 @@ __device__ __noinline__ void sel_insert_warp(uint32_t m, uint32_t taddr, int gn0
     if (!((m >> j) & 1u)) continue;
     if (col == mcol) sc = mval;
     if (sc != sc) sc = INFINITY;
-    if (sel_better(sc, col, tv, ti)) {
-      lv[wpos * kSelStride] = sc; li[wpos * kSelStride] = col;
-      tv = lv[0]; ti = li[0]; wpos = 0;
-#pragma unroll 4
-      for (int r = 1; r < K2; ++r) {
-        const float pv = lv[r * kSelStride];
-        const int pi = li[r * kSelStride];
-        if (sel_better(tv, ti, pv, pi)) { tv = pv; ti = pi; wpos = r; }
+    if (sel_better(sc, col, st.tv, st.ti)) {
+      sts_f32(lv_s + st.wpos * (kSelStride * 4), sc);
+      sts_s32(li_s + st.wpos * (kSelStride * 4), col);
+      float pv[kSelCap];
+      int pi[kSelCap], pp[kSelCap];
+#pragma unroll
+      for (int r = 0; r < kSelCap; ++r) {
+        // entries past K2 count as better than anything, so they are never the worst
+        pv[r] = r < K2 ? lds_f32(lv_s + r * (kSelStride * 4)) : INFINITY;
+        pi[r] = r < K2 ? lds_s32(li_s + r * (kSelStride * 4)) : INT_MIN;
+        pp[r] = r;
       }
+#pragma unroll
+      for (int w = kSelCap / 2; w >= 1; w >>= 1) {
+#pragma unroll
+        for (int r = 0; r < w; ++r) {
+          if (sel_better(pv[r], pi[r], pv[r + w], pi[r + w])) { pv[r] = pv[r + w]; pi[r] = pi[r + w]; pp[r] = pp[r + w]; }
+        }
+      }
+      st.tv = pv[0]; st.ti = pi[0]; st.wpos = pp[0];
       changed = true;
     }
   }
-  st->tv = tv; st->ti = ti; st->wpos = wpos;
   // publish the row's K2-th best so far: every other partition of the row (the other column half in this CTA, other column
   // ranges in other CTAs) may skip scores below it.  Positive floats order like their bit patterns; the word starts at -inf.
-  if (changed && thr && tv > 0.f) atomicMax(thr, __float_as_int(tv));
+  if (changed && thr && st.tv > 0.f) atomicMax(thr, __float_as_int(st.tv));
+  return st;
 }
 
 template <int BN, int NPASS>
@@ -305,6 +319,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     // epi == 2 state: this thread's K2 best of (row, its half of the columns) for the current row tile, sorted
     float* lv = tr_smem + (threadIdx.x - 64);                                 // [r * kSelStride]
     int* li = reinterpret_cast<int*>(tr_smem + kSelCap * kSelStride) + (threadIdx.x - 64);
+    const uint32_t lv_s = smem_u32(lv), li_s = smem_u32(li);
     SelState st{-INFINITY, INT_MAX, 0};
     int cur_u = -1;
     auto sel_flush = [&](int u_done) {                       // unit = (column range, row tile)
@@ -364,7 +379,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
               for (int j = 0; j < 32; ++j) m |= !(v[j] < tv) ? (1u << j) : 0u;      // also set for NaN
               if (inmask) m |= 1u << (int)(mcol - gn0);
             }
-            sel_insert_warp(m, taddr, gn0, p.N, mcol, mval, K2, lv, li, &st, (rok && p.sel_thr) ? p.sel_thr + gm : nullptr);
+            st = sel_insert_warp(m, taddr, gn0, p.N, mcol, mval, K2, lv_s, li_s, st, (rok && p.sel_thr) ? p.sel_thr + gm : nullptr);
           }
         }
         tc_fence_before();
