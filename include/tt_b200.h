@@ -349,10 +349,16 @@ int tt_debug_bwd_segments(int32_t n);
 /* Selection epilogue of the retrieval scan (tt_rows_topk*, D <= 128): 1 (default) keeps the query tile of a work unit in
  * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile.  Results are identical. */
 int tt_debug_sel_resident(int32_t on);
-/* Tensor passes of the candidate scan: 2 (default where D <= 128: x_hi y_hi + x_lo y_hi, acceptance bound 2^-11 + 2^-13) or
+/* Tensor passes of the candidate scan: 2 (default where D <= 128: x_hi y_hi + x_lo y_hi, acceptance bound 2^-13 + the
+ * measured fp16 rounding residual of the corpus rows) or
  * 3 (adds x_hi y_lo, bound 2^-13).  The final top-k is bit-identical either way (exact re-score + acceptance test).
- * 12 / 13: the same without the per-row lower bound the partitions of a row share (measurement only). */
+ * +10: without the per-row lower bound the partitions of a row share; +20: rows that fail the acceptance test go through
+ * the tile-shaped exact scan even when they are few (both for measurement / tests only). */
 int tt_debug_sel_passes(int32_t passes);
+/* Byte offset, inside the workspace of a tt_rows_topk (indexed == 0) / tt_rows_topk_indexed (indexed != 0) call of this
+ * shape, of the int32[Q] flags "row failed the acceptance test of the tensor route and went through the exact scan";
+ * -1 when the call does not take the tensor route.  Tests use it to check that benign data never falls back. */
+int64_t tt_debug_topk_fallback_flags(int32_t Q, int64_t N, int32_t D, int32_t mode, int32_t k, int32_t indexed);
 /* Same kernel: how many corpus tiles ahead the CTAs of a column range prefetch into L2 (0 = off). */
 int tt_debug_sel_prefetch(int32_t tiles);
 

@@ -466,7 +466,7 @@ def test_rows_topk_tensor_route_equals_exact_scan(cosine):
 
 
 @pytest.mark.parametrize("cosine", [False, True])
-@pytest.mark.parametrize("passes", [2, 3])
+@pytest.mark.parametrize("passes", [2, 3, 22])
 def test_rows_topk_near_duplicates_inside_the_approximation_error(cosine, passes):
     """Clusters of documents whose scores differ by less than the error of the tensor-engine candidate scan (2 passes:
     2^-11, 3 passes: 2^-13): the approximate order inside a cluster is arbitrary, so the result is only right if the
@@ -495,6 +495,42 @@ def test_rows_topk_near_duplicates_inside_the_approximation_error(cosine, passes
         tv, ti = Fn.rows_topk(_t(x), _t(y), k, cosine=cosine)
     finally:
         lib.tt_debug_sel_passes(2)
+    assert torch.equal(ti, ei) and torch.equal(tv, ev)
+    # the rows aimed at the clusters were rejected by the acceptance test (and re-done exactly: by the sparse re-scan for
+    # passes 2 / 3, by the tile-shaped exact scan for 22); rows of plain random data were not
+    import two_towers_b200 as tt
+    index = tt.CorpusIndex(_t(y), cosine=cosine)
+    try:
+        lib.tt_debug_sel_passes(passes)
+        iv, ii, flags = Fn.rows_topk_indexed(_t(x), index.docs, index.buffer, k, cosine=cosine, return_fallback_rows=True)
+    finally:
+        lib.tt_debug_sel_passes(2)
+    assert torch.equal(ii, ei) and torch.equal(iv, ev)
+    flags = flags.cpu().numpy()
+    assert flags[:40].sum() >= 8 and flags[40:].sum() <= 2
+
+
+def test_rows_topk_many_rejected_rows_take_the_tile_scan():
+    """More rejected rows than the sparse re-scan holds (256): every query aims at a cluster of 40 near-identical
+    documents, so all 600 rows fail the acceptance test and the gated tile-shaped exact scan must produce them."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(5)
+    Q, N, D, k = 600, 8000, 64, 10
+    y = rng.standard_normal((N, D)).astype(np.float32)
+    base = y[0].copy()
+    for j in range(40):
+        y[50 + 3 * j] = base + 1e-5 * rng.standard_normal(D).astype(np.float32)
+    x = (base[None, :] + 0.02 * rng.standard_normal((Q, D))).astype(np.float32)
+    try:
+        lib.tt_set_engine(0)
+        ev, ei = Fn.rows_topk(_t(x), _t(y), k, cosine=True)
+    finally:
+        lib.tt_set_engine(2)
+    import two_towers_b200 as tt
+    index = tt.CorpusIndex(_t(y), cosine=True)
+    tv, ti, flags = Fn.rows_topk_indexed(_t(x), index.docs, index.buffer, k, cosine=True, return_fallback_rows=True)
+    assert int(flags.sum()) > 256
     assert torch.equal(ti, ei) and torch.equal(tv, ev)
 
 

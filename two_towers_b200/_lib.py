@@ -127,6 +127,7 @@ SIGNATURES = {
     "tt_debug_sel_resident": (C.c_int, [i32]),
     "tt_debug_sel_prefetch": (C.c_int, [i32]),
     "tt_debug_sel_passes": (C.c_int, [i32]),
+    "tt_debug_topk_fallback_flags": (i64, [i32, i64, i32, i32, i32, i32]),
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
     "tt_opt_step_workspace": (u64, [i32]),
     "tt_opt_step": (C.c_int, [P, P]),

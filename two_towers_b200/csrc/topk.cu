@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
                                                       const float* __restrict__ invy, int64_t mask_pos_offset,
                                                       int64_t index_base, int64_t cols_per_split,
                                                       float* __restrict__ out_val, int64_t* __restrict__ out_idx,
-                                                      const int* __restrict__ need) {
+                                                      const int* __restrict__ need, const int* __restrict__ nfail, int nfail_min) {
   __shared__ __align__(16) float As[BK][LDS];
   __shared__ __align__(16) float Bs[BK][LDS];
   __shared__ float thr_v[BM];
@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
 
   const int t = threadIdx.x, tx = t & 15, ty = t >> 4, lane = t & 31, warp = t >> 5;
   const int bm = blockIdx.x * BM;
+  if (nfail && *nfail <= nfail_min) return;            // few rejected rows: rescan_rows_kernel has them
   if (need && !__syncthreads_or(t < BM && bm + t < Q && need[bm + t] != 0)) return;   // no row of this tile was rejected
   const int64_t cbeg = (int64_t)blockIdx.y * cols_per_split;
   const int64_t cend = cbeg + cols_per_split < N ? cbeg + cols_per_split : N;
@@ -170,8 +171,10 @@ __global__ void __launch_bounds__(NT) rows_topk_kernel(const float* __restrict__
 
 // one warp per query: merge S lists of k (vals [S,Q,k], idx [S,Q,k]) by (score desc, idx asc)
 __global__ void topk_merge_kernel(const float* __restrict__ vals, const int64_t* __restrict__ idx, int S, int Q, int k,
-                                  float* __restrict__ out_val, int64_t* __restrict__ out_idx, const int* __restrict__ need) {
+                                  float* __restrict__ out_val, int64_t* __restrict__ out_idx, const int* __restrict__ need,
+                                  const int* __restrict__ nfail, int nfail_min) {
   const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (nfail && *nfail <= nfail_min) return;
   if (q >= Q || (need && need[q] == 0)) return;
   float lv = -INFINITY; long long li = LLONG_MAX;
   for (int s = 0; s < S; ++s)
@@ -206,21 +209,169 @@ __global__ void mrr_ranks_kernel(const int64_t* __restrict__ topk_idx, const int
 }
 
 
+// ------------------------------------------------------------------------------------------ sparse exact re-scan
+// The acceptance test of the tensor route rejects a row now and then (the k-th exact score closer to the last candidate
+// than the error bound: ~1 row in 10^4 on random data); the tile-shaped exact scan above would spend a 128-row tile's
+// work (tens of ms at corpus scale) on it.  Up to kRescanCap rejected rows are instead gathered and re-scanned one row
+// per warp: every CTA owns a contiguous chunk of the corpus, stages it through shared memory 64 documents at a time and
+// each warp scores them against ITS row with the same fp32 FMA chain (d ascending) and score formula as the exact scan,
+// so the result is bit-identical.  More rejected rows than kRescanCap: the tile-shaped scan takes all of them.
+constexpr int kRescanCap = 256, kRescanTile = 64, kRescanCtas = 148;   // (4 CTAs per SM measured slower: 4x the lists to merge)
+static inline uint32_t rescan_smem(int D) { return (uint32_t)((kRescanTile * (D + 1) + 8 * D) * sizeof(float)); }
+static inline int rescan_cap(int D) { return rescan_smem(D) <= 200 * 1024 ? kRescanCap : 0; }
+
+__global__ void compact_need_kernel(const int* __restrict__ need, int Q, int* __restrict__ rows, int* __restrict__ nfail) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < Q && need[q] != 0) {
+    const int slot = atomicAdd(nfail, 1);
+    if (slot < kRescanCap) rows[slot] = q;
+  }
+}
+// grid kRescanCtas x 256 threads.  part_v / part_i: [kRescanCtas][kRescanCap][k]
+__global__ void __launch_bounds__(256) rescan_rows_kernel(const float* __restrict__ X, const float* __restrict__ Y, int64_t N, int D,
+                                                          int k, int cosine, const float* __restrict__ invx,
+                                                          const float* __restrict__ invy, int64_t mask_pos_offset,
+                                                          int64_t index_base, const int* __restrict__ rows,
+                                                          const int* __restrict__ nfail, float* __restrict__ part_v,
+                                                          int64_t* __restrict__ part_i) {
+  extern __shared__ float rs_smem[];
+  const int nf = *nfail;
+  if (nf <= 0 || nf > kRescanCap) return;
+  float* ys = rs_smem;                                   // [kRescanTile][D + 1]
+  float* xs = rs_smem + kRescanTile * (D + 1);           // [8][D]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t per = (N + gridDim.x - 1) / gridDim.x;
+  const int64_t c0 = (int64_t)blockIdx.x * per, c1 = c0 + per < N ? c0 + per : N;
+  for (int f0 = 0; f0 < nf; f0 += 8) {
+    const int f = f0 + warp;
+    const bool has = f < nf;
+    const int m = has ? rows[f] : 0;
+    __syncthreads();                                     // previous pass done with xs / ys
+    if (has) for (int d = lane; d < D; d += 32) xs[warp * D + d] = X[(int64_t)m * D + d];
+    const float xinv = (cosine && has) ? invx[m] : 1.f;
+    const int64_t mcol = (mask_pos_offset >= 0 && has) ? mask_pos_offset + m : -1;
+    float lv = -INFINITY; int li = INT_MAX;              // lane r holds rank r; li = document index relative to c0
+    for (int64_t t0 = c0; t0 < c1; t0 += kRescanTile) {
+      const int nd = (int)(c1 - t0 < kRescanTile ? c1 - t0 : kRescanTile);
+      __syncthreads();
+      if ((D & 3) == 0) {                                  // a warp per document row, 16-byte loads, 8 rows in flight per CTA
+        for (int dl = warp; dl < nd; dl += 8) {
+          const float4* src = reinterpret_cast<const float4*>(Y + (t0 + dl) * D);
+          float* dst = ys + dl * (D + 1);
+          for (int d4 = lane; d4 < (D >> 2); d4 += 32) {
+            const float4 v = __ldg(src + d4);
+            dst[4 * d4] = v.x; dst[4 * d4 + 1] = v.y; dst[4 * d4 + 2] = v.z; dst[4 * d4 + 3] = v.w;
+          }
+        }
+      } else {
+        for (int e = threadIdx.x; e < nd * D; e += 256) ys[(e / D) * (D + 1) + (e % D)] = Y[t0 * D + e];
+      }
+      __syncthreads();
+      if (!has) continue;
+      const float* xr = xs + warp * D;
+      float a0 = 0.f, a1 = 0.f;
+      const float* y0 = ys + lane * (D + 1);
+      const float* y1 = ys + (lane + 32) * (D + 1);
+      for (int d = 0; d < D; ++d) { const float xv = xr[d]; a0 = fmaf(xv, y0[d], a0); a1 = fmaf(xv, y1[d], a1); }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int dl = lane + 32 * h;
+        const int64_t doc = t0 + dl;
+        float sc = h ? a1 : a0;
+        if (cosine) sc = (sc * xinv) * (dl < nd ? invy[doc] : 1.f);
+        if (doc == mcol) sc = -1.f;
+        if (dl >= nd) sc = -INFINITY;
+        const int ci = (int)(doc - c0);
+        const float tv = __shfl_sync(0xffffffffu, lv, k - 1);
+        const int ti = __shfl_sync(0xffffffffu, li, k - 1);
+        unsigned mm = __ballot_sync(0xffffffffu, sc > -INFINITY && better(sc, ci, tv, ti));
+        while (mm) {
+          const int b = __ffs(mm) - 1;
+          mm &= mm - 1;
+          const float cv = __shfl_sync(0xffffffffu, sc, b);
+          const int cc = __shfl_sync(0xffffffffu, ci, b);
+          if (better(cv, cc, __shfl_sync(0xffffffffu, lv, k - 1), __shfl_sync(0xffffffffu, li, k - 1))) list_insert(lv, li, cv, cc, lane);
+        }
+      }
+    }
+    if (has && lane < k) {
+      const int64_t o = ((int64_t)blockIdx.x * kRescanCap + f) * k + lane;
+      const bool empty = li == INT_MAX;
+      part_v[o] = empty ? -INFINITY : lv;
+      part_i[o] = empty ? -1 : index_base + c0 + li;
+    }
+  }
+}
+// one warp per rejected row: merge the per-CTA lists (score desc, index asc) into the row's output
+__global__ void rescan_merge_kernel(const float* __restrict__ part_v, const int64_t* __restrict__ part_i, int nctas, int k,
+                                    const int* __restrict__ rows, const int* __restrict__ nfail, float* __restrict__ out_val,
+                                    int64_t* __restrict__ out_idx) {
+  const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  const int nf = *nfail;
+  if (nf <= 0 || nf > kRescanCap || f >= nf) return;
+  float lv = -INFINITY; long long li = LLONG_MAX;
+  for (int c = 0; c < nctas; ++c)
+    for (int e = 0; e < k; ++e) {
+      const int64_t o = ((int64_t)c * kRescanCap + f) * k + e;
+      const float cv = part_v[o]; const long long ci = part_i[o];
+      if (ci < 0) continue;                                   // uniform across the warp
+      const unsigned ahead = __ballot_sync(0xffffffffu, lv > cv || (lv == cv && li < ci));
+      const int p = __popc(ahead);
+      const float uv = __shfl_up_sync(0xffffffffu, lv, 1);
+      const long long ui = __shfl_up_sync(0xffffffffu, li, 1);
+      if (lane == p) { lv = cv; li = ci; }
+      else if (lane > p) { lv = uv; li = ui; }
+    }
+  if (lane < k) {
+    const int m = rows[f];
+    const bool empty = li == LLONG_MAX;
+    out_val[(int64_t)m * k + lane] = empty ? -INFINITY : lv;
+    out_idx[(int64_t)m * k + lane] = empty ? -1 : li;
+  }
+}
+
 // ------------------------------------------------------------------------------------------ tensor route
 constexpr int kCandSlack = 8;                                // candidates beyond k (fewer when k + 8 would exceed the engine's 16)
 constexpr int kSelMax = 16;                                  // list entries per row the selection epilogue keeps (umma_gemm.cu)
 static inline int cand_k2(int k) { return k + kCandSlack <= kSelMax ? k + kCandSlack : kSelMax; }
 constexpr float kScoreErr = 1.220703125e-4f;                 // 2^-13: bound on |approx - exact| / (|x| |y|), 4x margin
 // two-pass scan (x_hi y_hi + x_lo y_hi: the corpus contributes its fp16 hi plane only): rounding y to fp16 moves a score by
-// at most |x| |y - y_hi| <= 2^-11 |x| |y| (Cauchy-Schwarz over the element-wise half-ulp errors) on top of the bound above
-constexpr float kScoreErr2 = 4.8828125e-4f + kScoreErr;
-static int g_sel_passes = 2, g_sel_share = 1;
+// at most |x| |y - y_hi| (Cauchy-Schwarz).  |y - y_hi| is not bounded a priori by 2^-11 |y| here but MEASURED: the index
+// build takes the maximum over the corpus rows of the residual's 2-norm (resid_norm_kernel, ~0.4 * 2^-11 for normalised
+// rows), and the acceptance test adds it to the bound above.
+static int g_sel_passes = 2, g_sel_share = 1, g_rescan = 1;
 
 // candidate lists empty; the first nthr words of thr = bits of -inf (the rows' shared lower bounds)
 __global__ void list_init_kernel(float* __restrict__ lv, int* __restrict__ li, int64_t n, int* __restrict__ thr, int nthr) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) { lv[i] = -INFINITY; li[i] = INT_MAX; }
   if (i < nthr) thr[i] = __float_as_int(-INFINITY);
+}
+// one warp per plane row: max over rows of | v - hi(v) |_2, v = y[row][d] * (row_scale ? row_scale[row] : 1) as the planes
+// were built (fp32 subtraction of a value and its own fp16 rounding is exact); scaled up by 2^-9 for the summation's rounding
+__global__ void resid_norm_kernel(const float* __restrict__ y, int64_t N, int D, const float* __restrict__ row_scale,
+                                  unsigned int* __restrict__ out_max) {
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  float s = 0.f;
+  if (row < N) {
+    const float sc = row_scale ? row_scale[row] : 1.f;
+    for (int d = lane; d < D; d += 32) {
+      float v = y[row * D + d];
+      if (row_scale) v *= sc;
+      const float r = v - __half2float(__float2half_rn(v));
+      s = fmaf(r, r, s);
+    }
+  }
+  s = warp_max(sqrtf(warp_sum(s)) * 1.001953125f);
+  __shared__ float sh[8];
+  if (lane == 0) sh[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float m = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) m = fmaxf(m, sh[i]);
+    if (m == m) atomicMax(out_max, __float_as_uint(m)); else atomicMax(out_max, 0x7f800000u);   // NaN row: +inf (every row re-scanned)
+  }
 }
 __global__ void min_pos_kernel(const float* __restrict__ v, int64_t n, unsigned int* __restrict__ out) {
   float m = INFINITY;
@@ -264,7 +415,7 @@ __global__ void merge_parts_kernel(const float* __restrict__ part_v, const int* 
 __global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const float* __restrict__ Y, int D, int k, int K2,
                                     int cosine, const float* __restrict__ invx, const float* __restrict__ invy,
                                     const unsigned int* __restrict__ min_invy, int64_t mask_pos_offset, int64_t index_base,
-                                    const float* __restrict__ list_v, const int* __restrict__ list_i, float score_err,
+                                    const float* __restrict__ list_v, const int* __restrict__ list_i, int two_pass,
                                     float* __restrict__ out_val, int64_t* __restrict__ out_idx, int* __restrict__ need) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= Q) return;
@@ -296,7 +447,9 @@ __global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const fl
   if (at_k) e_k = __shfl_sync(0xffffffffu, ev, __ffs(at_k) - 1);
   // cosine: |x| invx and |y| invy are <= 1; dot: |x| max|y|  (invx = 1/max(|x|,1e-8))
   const float scale = cosine ? 1.f : (1.f / invx[row]) * (1.f / __uint_as_float(*min_invy));
-  const bool ok = !full || (e_k - a_min > score_err * scale);               // false for NaN/inf as well
+  // two passes: plus |x| times the largest fp16 rounding residual of a corpus row (min_invy[1], see resid_norm_kernel)
+  const float extra = two_pass ? __uint_as_float(min_invy[1]) * (cosine ? 1.f : 1.f / invx[row]) : 0.f;
+  const bool ok = !full || (e_k - a_min > kScoreErr * scale + extra);               // false for NaN/inf as well
   if (lane == 0) need[row] = ok ? 0 : 1;
   if (ok && rank < k) {
     out_val[(int64_t)row * k + rank] = valid ? ev : -INFINITY;
@@ -323,7 +476,7 @@ static inline bool topk_tc(int64_t N, int k) { return engine_mode() >= 1 && umma
 static inline int topk_qt(int Q) { return Q < 8192 ? Q : 8192; }
 struct TopkWs {
   float *invx, *invy; unsigned int* ymin; float* pv; int64_t* pi;
-  __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp; int* thr;
+  __half *xh, *xl, *yh, *yl; float* part_v; int* part_i; int64_t slots; float* lv; int* li; int* need; int64_t dp; int* thr; int* nfail; int* fail_rows; float* rs_v; int64_t* rs_i;
 };
 // The per-corpus part of the scan (tt_corpus_index_build): row norms, their minimum, and the hi/lo planes of the tensor route
 struct CorpusIdx { float* invy; unsigned int* ymin; __half *yh, *yl; int64_t dp; bool planes; };
@@ -358,6 +511,8 @@ static void carve_topk(Workspace& w, int Q, int64_t N, int D, int mode, int k, T
     o->part_i = w.take<int>(rows_slots * 32);
     o->lv = w.take<float>((int64_t)Q * 32); o->li = w.take<int>((int64_t)Q * 32); o->need = w.take<int>(Q);
     o->thr = w.take<int>(Q);
+    o->nfail = w.take<int>(64); o->fail_rows = w.take<int>(kRescanCap);
+    o->rs_v = w.take<float>((int64_t)kRescanCtas * kRescanCap * 32); o->rs_i = w.take<int64_t>((int64_t)kRescanCtas * kRescanCap * 32);
   }
 }
 
@@ -388,6 +543,8 @@ static int corpus_prepare(const float* y, int64_t N, int D, int mode, const Corp
   note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, c.invy);
   TT_CUDA(cudaMemsetAsync(c.ymin, 0x7f, sizeof(unsigned int), s));
   note_launch(); min_pos_kernel<<<296, 256, 0, s>>>(c.invy, N, c.ymin);
+  TT_CUDA(cudaMemsetAsync(c.ymin + 1, 0, sizeof(unsigned int), s));
+  if (c.planes) { note_launch(); resid_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, mode == 1 ? c.invy : nullptr, c.ymin + 1); }
   // cosine: the corpus rows go into the planes already divided by their norm (the exact re-score uses the fp32 rows)
   if (c.planes) TT_TRY(split_rows_f16_scaled(y, N, D, c.dp, c.yh, c.yl, mode == 1 ? c.invy : nullptr, s));
   TT_LAUNCH_CHECK();
@@ -432,6 +589,7 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
     else { note_launch(); inv_norm_kernel<<<(unsigned)ceil_div(N, 8), 256, 0, s>>>(y, N, D, 1e-8f, invy); }
   }
   const int* need = nullptr;
+  int rs_cap = 0;
   if (tc) {
     // ---- tensor route: approximate tile scores -> candidates -> exact re-score -> acceptance
     const int K2 = cand_k2(k), QT = topk_qt(Q);
@@ -459,9 +617,24 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
     }
     note_launch();
     rescore_rows_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(x, Q, y, D, k, K2, mode, invx, invy, c.ymin, mask_pos_offset,
-                                                                index_base, t.lv, t.li, two ? kScoreErr2 : kScoreErr, out_val, out_idx, t.need);
+                                                                index_base, t.lv, t.li, two ? 1 : 0, out_val, out_idx, t.need);
     TT_LAUNCH_CHECK();
     need = t.need;
+    // rejected rows: a few -> gathered, one warp per row; many -> the tile-shaped exact scan below (gated on the count)
+    rs_cap = g_rescan ? rescan_cap(D) : 0;
+    if (rs_cap > 0) {
+      static bool attr_done = false;
+      const uint32_t smem = rescan_smem(D);
+      if (!attr_done) { TT_CUDA(cudaFuncSetAttribute(rescan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_done = true; }
+      TT_CUDA(cudaMemsetAsync(t.nfail, 0, sizeof(int), s));
+      note_launch(); compact_need_kernel<<<(unsigned)ceil_div(Q, 256), 256, 0, s>>>(t.need, Q, t.fail_rows, t.nfail);
+      note_launch();
+      rescan_rows_kernel<<<kRescanCtas, 256, smem, s>>>(x, y, N, D, k, mode, invx, invy, mask_pos_offset, index_base, t.fail_rows,
+                                                       t.nfail, t.rs_v, t.rs_i);
+      note_launch();
+      rescan_merge_kernel<<<kRescanCap / 8, 256, 0, s>>>(t.rs_v, t.rs_i, kRescanCtas, k, t.fail_rows, t.nfail, out_val, out_idx);
+      TT_LAUNCH_CHECK();
+    }
     if (mode == 0) { invx = nullptr; invy = nullptr; }      // the exact scan applies norms only for the cosine
   }
   // ---- exact scan: everything (engine 0) or only the rows the acceptance test rejected
@@ -471,8 +644,8 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
   cps = ceil_div(cps, BN) * BN;
   dim3 grid((unsigned)ceil_div(Q, BM), (unsigned)S);
   tt::note_launch(); rows_topk_kernel<<<grid, NT, 0, s>>>(x, Q, y, N, D, k, invx, invy, mask_pos_offset, index_base, cps,
-                                      S > 1 ? pv : out_val, S > 1 ? pi : out_idx, need);
-  if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx, need); }
+                                      S > 1 ? pv : out_val, S > 1 ? pi : out_idx, need, rs_cap > 0 ? t.nfail : nullptr, rs_cap);
+  if (S > 1) { note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, s>>>(pv, pi, S, Q, k, out_val, out_idx, need, rs_cap > 0 ? t.nfail : nullptr, rs_cap); }
   TT_LAUNCH_CHECK();
   return TT_OK;
 }
@@ -496,10 +669,22 @@ int tt_debug_sel_resident(int32_t on) {
   tt::umma_set_sel_resident(on);
   return TT_OK;
 }
+// byte offset, inside the workspace of a tt_rows_topk (indexed == 0) / tt_rows_topk_indexed (indexed != 0) call of this shape,
+// of the int32[Q] flags "row failed the acceptance test of the tensor route and was re-done by the exact scan";
+// -1 when the call does not take the tensor route
+int64_t tt_debug_topk_fallback_flags(int32_t Q, int64_t N, int32_t D, int32_t mode, int32_t k, int32_t indexed) {
+  if (!topk_tc(N, k)) return -1;
+  Workspace w(nullptr, 0);
+  TopkWs t;
+  carve_topk(w, Q, N, D, mode, k, &t, indexed == 0);
+  return (int64_t)(reinterpret_cast<char*>(t.need) - (char*)nullptr);
+}
 int tt_debug_sel_passes(int32_t passes) {
-  TT_CHECK_ARG(passes == 2 || passes == 3 || passes == 12 || passes == 13, "tt_debug_sel_passes: 2 or 3 (+10: no shared row bound)");
-  tt::g_sel_passes = passes % 10;
-  tt::g_sel_share = passes < 10;
+  const int p = passes % 10, f = passes / 10;
+  TT_CHECK_ARG((p == 2 || p == 3) && f >= 0 && f <= 3, "tt_debug_sel_passes: 2 or 3 (+10: no shared row bound, +20: no sparse re-scan)");
+  tt::g_sel_passes = p;
+  tt::g_sel_share = (f & 1) == 0;
+  tt::g_rescan = (f & 2) == 0;
   return TT_OK;
 }
 int tt_debug_sel_prefetch(int32_t tiles) {
@@ -511,7 +696,7 @@ int tt_debug_sel_prefetch(int32_t tiles) {
 int tt_topk_merge(const float* vals, const int64_t* idx, int32_t S, int32_t Q, int32_t k, float* out_val,
                   int64_t* out_idx, void* stream) {
   TT_CHECK_ARG(vals && idx && out_val && out_idx && S > 0 && Q > 0 && k >= 1 && k <= 32, "topk_merge: bad args");
-  tt::note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx, nullptr);
+  tt::note_launch(); topk_merge_kernel<<<(unsigned)ceil_div(Q, 8), 256, 0, (cudaStream_t)stream>>>(vals, idx, S, Q, k, out_val, out_idx, nullptr, nullptr, 0);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }

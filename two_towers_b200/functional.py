@@ -361,7 +361,7 @@ def corpus_index_build(y, cosine=True):
 
 
 @torch.no_grad()
-def rows_topk_indexed(x, y, index, k, cosine=True, mask_pos_offset=-1, index_base=0):
+def rows_topk_indexed(x, y, index, k, cosine=True, mask_pos_offset=-1, index_base=0, return_fallback_rows=False):
     """rows_topk against a corpus whose index (corpus_index_build(y, cosine)) already exists; bit-identical results."""
     lib = L.lib()
     x = L.f32c(x)
@@ -374,6 +374,10 @@ def rows_topk_indexed(x, y, index, k, cosine=True, mask_pos_offset=-1, index_bas
     L.check(lib.tt_rows_topk_indexed(L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base),
                                      L.ptr(val), L.ptr(idx), index.data_ptr(), index.numel(), ws.data_ptr(), ws.numel(),
                                      L.stream()), "tt_rows_topk_indexed")
+    if return_fallback_rows:
+        off = lib.tt_debug_topk_fallback_flags(Q, N, D, mode, k, 1)
+        flags = ws[off:off + 4 * Q].view(torch.int32).clone() if off >= 0 else torch.zeros(Q, dtype=torch.int32, device=x.device)
+        return val, idx, flags
     return val, idx
 
 
