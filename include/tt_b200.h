@@ -347,7 +347,8 @@ int tt_debug_wgrad_overlap(int32_t on);
  * steps use fewer segments. */
 int tt_debug_bwd_segments(int32_t n);
 /* Selection epilogue of the retrieval scan (tt_rows_topk*, D <= 128): 1 (default) keeps the query tile of a work unit in
- * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile.  Results are identical. */
+ * shared memory while its corpus tiles stream through; 0 reloads it with every corpus tile; 5: resident, and 128-column
+ * tiles with four accumulators in flight instead of 256-column tiles with two (measured slower).  Results are identical. */
 int tt_debug_sel_resident(int32_t on);
 /* Tensor passes of the candidate scan: 2 (default where D <= 128: x_hi y_hi + x_lo y_hi, acceptance bound 2^-13 + the
  * measured fp16 rounding residual of the corpus rows) or

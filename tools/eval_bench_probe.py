@@ -15,8 +15,9 @@ docs[rel % Nl] = noisy
 index = tt.CorpusIndex(docs, cosine=True)
 from two_towers_b200 import functional as Fn
 ref = None
-for passes in (3, 2, 22, 2):
+for passes, res in ((3, 1), (2, 1), (2, 5), (2, 1), (3, 1)):
     L.lib().tt_debug_sel_passes(passes)
+    L.lib().tt_debug_sel_resident(res)
     v, i, fl = Fn.rows_topk_indexed(q, index.docs, index.buffer, 10, cosine=True, return_fallback_rows=True)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -27,5 +28,5 @@ for passes in (3, 2, 22, 2):
     torch.cuda.synchronize()
     if ref is None:
         ref = (v.clone(), i.clone())
-    print(f"passes={passes}: {e0.elapsed_time(e1) / 3:.2f} ms per scan, fallback rows {int(fl.sum())} of {Q}, "
+    print(f"passes={passes} resident={res}: {e0.elapsed_time(e1) / 3:.2f} ms per scan, fallback rows {int(fl.sum())} of {Q}, "
           f"identical={torch.equal(i, ref[1]) and torch.equal(v, ref[0])}", flush=True)

@@ -122,13 +122,17 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C_::STAGES * C_::STAGE_BYTES);
   uint64_t* full = bars;                       // [STAGES]
   uint64_t* empty = bars + C_::STAGES;         // [STAGES]
-  uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]
-  uint64_t* tempty = tfull + 2;                // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  uint64_t* afull = bars + 26;                 // resident-A mode: A tile of the unit loaded / no longer read
-  uint64_t* aempty = bars + 27;
-  uint64_t* rfull = bars + 17;                 // resident-A mode: its own B ring barriers [4] (the ring may be deeper than STAGES)
-  uint64_t* rempty = bars + 21;                // [4]
+  uint64_t* tfull = bars + 2 * C_::STAGES;     // [4] (2 used unless nacc == 4)
+  uint64_t* tempty = tfull + 4;                // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 4);      // <= bars + 20
+  uint64_t* afull = bars + 30;                 // resident-A mode: A tile of the unit loaded / no longer read
+  uint64_t* aempty = bars + 31;
+  uint64_t* rfull = bars + 22;                 // resident-A mode: its own B ring barriers [4] (the ring may be deeper than STAGES)
+  uint64_t* rempty = bars + 26;                // [4]
+  // accumulators in flight: 2, or - selection epilogue on 128-column tiles - 4 (all 512 TMEM columns): the time the epilogue
+  // spends on a tile varies (candidate insertions), and with two accumulators every slow tile stalled the MMA issuer
+  const int nacc = (p.epi == 2 && BN == 128) ? 4 : 2;
+  const uint32_t tmem_cols = nacc == 4 ? 512 : C_::TMEM_COLS;
   // resident-A layout: [k-block][hi 16 KB | lo 16 KB] at the start of the ring area, then B stages of NPLANES * B_BYTES
   constexpr int RES_A_BYTES = 2 * C_::NPLANES * C_::A_BYTES;
   const int res_stage_bytes = (p.sel_two ? 1 : C_::NPLANES) * C_::B_BYTES;
@@ -155,12 +159,12 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
+    for (int i = 0; i < 4; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 256); }
     mbar_init(afull, 1); mbar_init(aempty, 1);
     for (int i = 0; i < 4; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], 1); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, C_::TMEM_COLS);
+  if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
       TT_WALK_BEGIN
         const int sp = (it / (NT * MT)) % p.splitk;
         const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
-        const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+        const int acc = nacc == 4 ? (tile & 3) : (tile & 1), acc_phase = (nacc == 4 ? (tile >> 2) : (tile >> 1)) & 1;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -321,6 +325,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     int* li = reinterpret_cast<int*>(tr_smem + kSelCap * kSelStride) + (threadIdx.x - 64);
     const uint32_t lv_s = smem_u32(lv), li_s = smem_u32(li);
     SelState st{-INFINITY, INT_MAX, 0};
+    float sel_mval = -1.f, gthr_next = -INFINITY;
     int cur_u = -1;
     auto sel_flush = [&](int u_done) {                       // unit = (column range, row tile)
       if (u_done < 0) return;
@@ -333,25 +338,29 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
     TT_WALK_BEGIN
       const int n_blk = it % NT, m_blk = (it / NT) % MT, sp = (it / (NT * MT)) % p.splitk, bz = it / (NT * MT * p.splitk);
       const int kb0 = sp * kb_per, kb1 = min(KB, kb0 + kb_per);
-      const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+      const int acc = nacc == 4 ? (tile & 3) : (tile & 1), acc_phase = (nacc == 4 ? (tile >> 2) : (tile >> 1)) & 1;
       ++tile;
       if (epi2 && u_ != cur_u) {
         sel_flush(cur_u);
         cur_u = u_;
         for (int r = 0; r < kSelCap; ++r) { lv[r * kSelStride] = -INFINITY; li[r * kSelStride] = INT_MAX; }
         st.tv = -INFINITY; st.ti = INT_MAX; st.wpos = 0;
+        // per unit, not per tile (both are global loads whose L2 latency - ~1 us per tile - sat on the critical path)
+        const int gmu = m_blk * UBM + row;
+        sel_mval = (p.sel_invx && gmu < p.M) ? -1.f / __ldg(p.sel_invx + gmu) : -1.f;
+        gthr_next = -INFINITY;
       }
       const int gm = m_blk * UBM + row;
-      // the row's shared lower bound, read once per tile (issued before the wait for the accumulator; a stale value is
-      // still a valid bound, it only filters less)
-      float gthr = -INFINITY;
-      if (epi2 && p.sel_thr && gm < p.M) gthr = __int_as_float(__ldcg(p.sel_thr + gm));
+      // the row's shared lower bound: the value used for this tile was loaded while the previous tile was filtered, the load
+      // issued here is consumed by the next tile (a stale value is still a valid bound, it only filters less)
+      const float gthr = gthr_next;
+      if (epi2 && p.sel_thr && gm < p.M) gthr_next = __int_as_float(__ldcg(p.sel_thr + gm));
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       if (p.epi == 2) {
         const bool rok = gm < p.M;
         const int64_t mcol = p.sel_mask_off >= 0 ? p.sel_mask_off + gm : -1;
-        const float mval = (p.sel_invx && rok) ? -1.f / __ldg(p.sel_invx + gm) : -1.f;
+        const float mval = sel_mval;
         const int K2 = p.sel_k2;
 #pragma unroll 1
         for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
@@ -490,7 +499,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, C_::TMEM_COLS);
+  if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
 
@@ -572,14 +581,15 @@ static int sm_count() {
   return n;
 }
 // slots per row of the selection epilogue's output for an [M, N] problem (must mirror umma_gemm_prepare)
-static int g_sel_resident = 1, g_sel_prefetch = 4;
-void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; }
+static int g_sel_resident = 1, g_sel_prefetch = 4, g_sel_bn128 = 0;   // 128-column tiles x 4 accumulators measured slower (7.8 vs 5.65 ms)
+void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; g_sel_bn128 = (on & 4) ? 1 : 0; }
 void umma_set_sel_prefetch(int tiles) { g_sel_prefetch = tiles < 0 ? 0 : tiles; }
 
 bool umma_sel_two_ok(int32_t K) { return g_sel_resident && ceil_div(K, UBK) <= 2; }
 
 int umma_sel_slots(int32_t M, int64_t N) {
-  const int64_t MT = ceil_div(M, UBM), BN = N <= 128 ? 128 : 256, NT = ceil_div(N, BN);
+  // sized for 128-column tiles (the most parts a row can have); with 256-column tiles the extra slots stay empty
+  const int64_t MT = ceil_div(M, UBM), BN = 128, NT = ceil_div(N, BN);
   int64_t S = sm_count() / MT < 1 ? 1 : sm_count() / MT;
   if (S > NT) S = NT;
   return (int)(2 * S);
@@ -593,6 +603,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   const int MT = (int)ceil_div(g.M, UBM), KB = (int)ceil_div(g.K, UBK);
   // BN = 128 when N is small, or when 256-wide tiles would leave most SMs idle
   int BN = g.N <= 128 ? 128 : 256;
+  if (g.epi == 2 && g_sel_bn128 && g_sel_resident && KB <= 2) BN = 128;      // 4 accumulators in flight (see the kernel)
   if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0 && g.epi != 2) BN = 128;
   UmmaParams& p = *reinterpret_cast<UmmaParams*>(out->blob);
   const int f16 = g.f16;
@@ -637,7 +648,7 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     TT_CHECK_ARG(g.sel_slots >= 2 * p.sel_S, "umma_gemm: sel_slots too small");
     p.sel_v = g.sel_v; p.sel_i = g.sel_i; p.sel_invx = g.sel_invx; p.sel_mask_off = g.sel_mask_off;
     p.sel_k2 = g.sel_k2; p.sel_slots = g.sel_slots;
-    p.a_res = (g_sel_resident && BN == 256 && KB <= 2) ? 1 : 0;
+    p.a_res = (g_sel_resident && KB <= 2) ? 1 : 0;
     p.sel_pf = g_sel_prefetch;
     TT_CHECK_ARG(!g.sel_two || p.a_res, "umma_gemm: two-pass selection needs the resident-A mode (K <= 128)");
     p.sel_two = g.sel_two ? 1 : 0;
