@@ -87,3 +87,27 @@ def test_cpu_tensors_are_rejected_loudly():
         tt.InfoNCELoss()(torch.randn(2, 4), torch.randn(2, 4))
     with pytest.raises(RuntimeError, match="CUDA"):
         tt.get_hard_negatives(torch.randn(4), torch.randn(5, 4), 0, 2)
+
+
+def test_retrieval_size_queries_are_host_only_and_consistent():
+    """tt_corpus_index_bytes / tt_rows_topk*_workspace / tt_debug_topk_fallback_flags are pure host arithmetic: callable
+    without a GPU, monotonic in the problem size, and the indexed scan (corpus part in the caller's index buffer) never
+    needs more scratch than the scan that converts the corpus on every call."""
+    lib = _lib.lib()
+    D = 128
+    sizes = [lib.tt_corpus_index_bytes(n, D) for n in (0, 1000, 100_000, 1_100_000)]
+    assert sizes == sorted(sizes) and sizes[0] >= 256
+    assert sizes[-1] >= 1_100_000 * 4                      # at least the row norms
+    for mode in (0, 1):
+        for q, n in ((1, 1000), (300, 20_000), (8192, 1_100_000)):
+            plain = lib.tt_rows_topk_workspace(q, n, D, mode)
+            indexed = lib.tt_rows_topk_indexed_workspace(q, n, D, mode)
+            assert 0 < indexed <= plain
+            for k in (1, 10):
+                for flag in (0, 1):
+                    off = lib.tt_debug_topk_fallback_flags(q, n, D, mode, k, flag)
+                    limit = indexed if flag else plain
+                    assert off == -1 or (0 <= off and off + 4 * q <= limit)
+    with pytest.raises(Exception):
+        _lib.check(lib.tt_debug_sel_passes(7), "tt_debug_sel_passes")
+    assert lib.tt_debug_sel_passes(2) == 0 and lib.tt_debug_sel_resident(1) == 0 and lib.tt_debug_sel_prefetch(4) == 0
