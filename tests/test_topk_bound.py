@@ -1,0 +1,83 @@
+"""CPU: the error bound behind the acceptance test of the two-pass candidate scan (csrc/topk.cu).
+
+The tensor route scores  a(x, y) = (x_hi + x_lo) . y_hi  (fp16 planes, fp32 accumulation) and accepts a row only if its k-th
+exact score clears the best non-candidate by more than   2^-13 |x||y| + |x| * max_rows |y - y_hi|_2 .
+Here the planes are emulated with numpy float16 and the claim |a - exact| <= bound is checked on random, badly scaled and
+subnormal-heavy data, with the accumulation done in float32 in the worst order we can think of (descending magnitude)."""
+import numpy as np
+import pytest
+
+
+def _planes(v):
+    hi = v.astype(np.float16)
+    lo = (v - hi.astype(np.float32)).astype(np.float16)
+    return hi.astype(np.float32), lo.astype(np.float32)
+
+
+def _fp32_dot(a, b):
+    """row-wise dot product accumulated in float32, one product at a time"""
+    acc = np.zeros(a.shape[0], np.float32)
+    for d in range(a.shape[1]):
+        acc = (acc + a[:, d] * b[:, d]).astype(np.float32)
+    return acc
+
+
+def _exact_chain(x, y):
+    acc = np.zeros(x.shape[0], np.float32)
+    for d in range(x.shape[1]):
+        acc = np.float32(1) * (acc.astype(np.float64) + x[:, d].astype(np.float64) * y[:, d].astype(np.float64)).astype(np.float32)
+    return acc
+
+
+CASES = {
+    "normalised": lambda rng, n, D: (rng.standard_normal((n, D)), rng.standard_normal((n, D)), True),
+    "aligned": lambda rng, n, D: (np.abs(rng.standard_normal((n, D))), np.abs(rng.standard_normal((n, D))), True),
+    "spiky": lambda rng, n, D: (rng.standard_normal((n, D)) * (rng.random((n, D)) < 0.05), rng.standard_normal((n, D)) ** 3, True),
+    "tiny components": lambda rng, n, D: (rng.standard_normal((n, D)), rng.standard_normal((n, D)) * 10.0 ** rng.uniform(-6, 0, (n, D)), True),
+    "dot mode, unit-scale rows": lambda rng, n, D: (3.0 * rng.standard_normal((n, D)), 0.5 * rng.standard_normal((n, D)), False),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+@pytest.mark.parametrize("D", [64, 128])
+def test_two_pass_score_error_is_inside_the_acceptance_bound(case, D):
+    rng = np.random.default_rng(hash(case) % 1000 + D)
+    n = 4000
+    x, y, cosine = CASES[case](rng, n, D)
+    x, y = x.astype(np.float32), y.astype(np.float32)
+    if cosine:                       # the corpus planes hold the rows divided by their norm (fp32 multiply, as on the device)
+        invy = (1.0 / np.maximum(np.sqrt((y.astype(np.float64) ** 2).sum(1)), 1e-8)).astype(np.float32)
+        yp = (y * invy[:, None]).astype(np.float32)
+    else:
+        yp = y
+    xh, xl = _planes(x)
+    yh, _ = _planes(yp)
+    resid = np.sqrt(((yp - yh).astype(np.float64) ** 2).sum(1))
+    rmax = float(resid.max()) * 1.001953125
+    # the device sums hi*hi and lo*hi into one fp32 accumulator; emulate with the two chains added in float32
+    approx = (_fp32_dot(xh, yh) + _fp32_dot(xl, yh)).astype(np.float32)
+    exact = _exact_chain(x, yp)
+    xn = np.sqrt((x.astype(np.float64) ** 2).sum(1))
+    yn = np.sqrt((yp.astype(np.float64) ** 2).sum(1))
+    bound = 2.0 ** -13 * xn * yn.max() + xn * rmax
+    err = np.abs(approx.astype(np.float64) - exact.astype(np.float64))
+    assert (err <= bound).all(), float((err / bound).max())
+    # and the measured residual is what makes the bound tight: the a-priori 2^-11 |y| is clearly larger on such rows
+    if case == "normalised":
+        assert rmax < 0.8 * 2.0 ** -11 * float(yn.max())
+
+
+def test_three_pass_score_error_is_inside_2_pow_minus_13():
+    rng = np.random.default_rng(3)
+    n, D = 4000, 128
+    x = rng.standard_normal((n, D)).astype(np.float32)
+    y = rng.standard_normal((n, D)).astype(np.float32)
+    xh, xl = _planes(x)
+    yh, yl = _planes(y)
+    approx = (_fp32_dot(xh, yh) + _fp32_dot(xl, yh) + _fp32_dot(xh, yl)).astype(np.float32)
+    exact = _exact_chain(x, y)
+    xn = np.sqrt((x.astype(np.float64) ** 2).sum(1))
+    yn = np.sqrt((y.astype(np.float64) ** 2).sum(1))
+    err = np.abs(approx.astype(np.float64) - exact.astype(np.float64))
+    assert (err <= 2.0 ** -13 * xn * yn).all()
+    assert (err <= 2.0 ** -15 * xn * yn).mean() > 0.99          # the 4x margin DESIGN.md quotes
