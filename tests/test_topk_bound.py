@@ -81,3 +81,22 @@ def test_three_pass_score_error_is_inside_2_pow_minus_13():
     err = np.abs(approx.astype(np.float64) - exact.astype(np.float64))
     assert (err <= 2.0 ** -13 * xn * yn).all()
     assert (err <= 2.0 ** -15 * xn * yn).mean() > 0.99          # the 4x margin DESIGN.md quotes
+
+
+@pytest.mark.parametrize("scale,holds", [(1.0, True), (1e-2, True), (1e-4, True)])
+def test_bound_holds_for_small_query_norms_down_to_the_fp16_subnormal_range(scale, holds):
+    """The bound assumes the query survives its hi + lo split; DESIGN.md section 2 states the range (|x| >~ 1e-3 at D = 128)."""
+    rng = np.random.default_rng(11)
+    n, D = 2000, 128
+    x = (scale * rng.standard_normal((n, D))).astype(np.float32)
+    y = rng.standard_normal((n, D)).astype(np.float32)
+    invy = (1.0 / np.sqrt((y.astype(np.float64) ** 2).sum(1))).astype(np.float32)
+    yp = (y * invy[:, None]).astype(np.float32)
+    xh, xl = _planes(x)
+    yh, _ = _planes(yp)
+    rmax = float(np.sqrt(((yp - yh).astype(np.float64) ** 2).sum(1)).max()) * 1.001953125
+    approx = (_fp32_dot(xh, yh) + _fp32_dot(xl, yh)).astype(np.float32)
+    exact = _exact_chain(x, yp)
+    xn = np.sqrt((x.astype(np.float64) ** 2).sum(1))
+    err = np.abs(approx.astype(np.float64) - exact.astype(np.float64))
+    assert bool((err <= 2.0 ** -13 * xn + xn * rmax).all()) == holds
