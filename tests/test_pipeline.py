@@ -342,3 +342,45 @@ def test_search_service_matches_oracle_and_cache_roundtrip(vocab, tmp_path):
     svc2 = tt.SearchService(model, vocab, docs, max_length=L, top_k=3, cache_path=cache)
     assert torch.equal(svc2.doc_embeddings.cpu(), cached)
     assert svc2.search("what is ai")["results"][0]["text"] == svc.search("what is ai")["results"][0]["text"]
+
+
+@pytest.mark.gpu
+def test_compute_mrr_matches_oracle_flow(vocab):
+    """validate_margin.compute_mrr through the package: margin text preprocessing -> ids -> device towers -> full ranking.
+    Oracle: the port on CPU with oracle/ref_pipeline.margin_ids + full_rank_rr (pinned to the live reference on CPU in
+    tests/test_full_rank_mrr.py).  Only (query, relevant document) pairs whose relevant score is > 1e-2 away from every other
+    candidate's are compared (11 of the 15 with these seeds): the rank cannot flip inside the encoders' 1e-3 tolerance."""
+    from oracle import ref_port as rp
+    dev = torch.device("cuda:0")
+    E, H, L = 10, 8, 30
+    torch.manual_seed(1)
+    port = rp.build_port("margin", E, H).eval()
+    model = tt.TwoTowerModel(E, H)
+    model.load_state_dict(port.state_dict())
+    table = torch.randn(max(INDEX.values()) + 1, E, generator=torch.Generator().manual_seed(7)) * 0.5
+    table[0] = 0
+    assert vocab.table_rows() == table.shape[0]
+    model.to(dev).train().attach_embeddings(table.to(dev), pad_id=0)
+    rng = random.Random(4)
+    cands = [" ".join(rng.choice(G["words"]) for _ in range(rng.randint(1, 25))) for _ in range(12)]
+    queries = [cands[3], "what is a " + cands[7], " ".join(rng.choice(G["words"]) for _ in range(6)), "zzz", cands[10] + " the"]
+    checked = 0
+    with torch.no_grad():
+        dv = port.encode_doc(table[torch.tensor([rpl.margin_ids(c, INDEX, L) for c in cands])])
+    for query in queries:
+        with torch.no_grad():
+            qv = port.encode_query(table[torch.tensor([rpl.margin_ids(query, INDEX, L)])])
+            sims = torch.nn.functional.cosine_similarity(qv.unsqueeze(1), dv.unsqueeze(0), dim=2).squeeze(0)
+        for j in (0, 6, 9):
+            relevant = {cands[j]}
+            rr, top = tt.compute_mrr(model, query, relevant, cands, vocab, max_length=L, batch_size=5)
+            assert model.training                                          # mode restored
+            assert len(top) == 3 and all(isinstance(d, str) for d, _ in top)
+            want_rr, want_top = rpl.full_rank_rr(sims.tolist(), cands, relevant)
+            others = torch.cat([sims[:j], sims[j + 1:]])
+            if (others - sims[j]).abs().min().item() > 1e-2:
+                assert rr == want_rr
+                checked += 1
+            assert abs(top[0][1] - want_top[0][1]) < 5e-3
+    assert checked >= 8
+    assert tt.compute_mrr(model, "anything", {"x"}, [], vocab) == (0.0, [])

@@ -127,6 +127,50 @@ def load_or_compute_doc_embeddings(model, doc_ids, cache_path=None, batch_size=4
     return emb
 
 
+# ------------------------------------------------------------------------------------------- a16: full-rank MRR
+@torch.no_grad()
+def first_relevant_rank(query_vecs, doc_vecs, relevant):
+    """Reciprocal rank of the first relevant candidate in the FULL ranking of the candidates
+    (validate_margin.compute_mrr :37-54: cosine similarity, stable descending sort - ties keep the candidate order -,
+    1/rank of the first hit, 0 without one).  query_vecs [Q,D]; doc_vecs [N,D] (one candidate list shared by the queries)
+    or [Q,N,D]; relevant bool [Q,N].  Returns (rr float64 [Q], top3 indices [Q,min(3,N)], top3 scores)."""
+    if query_vecs.dim() == 1:
+        query_vecs = query_vecs.unsqueeze(0)
+    docs = doc_vecs.unsqueeze(0) if doc_vecs.dim() == 2 else doc_vecs
+    sims = torch.nn.functional.cosine_similarity(query_vecs.unsqueeze(1), docs, dim=2)            # [Q,N], as :38-42
+    relevant = torch.as_tensor(relevant, dtype=torch.bool, device=sims.device).reshape(sims.shape)
+    val, order = torch.sort(sims, dim=1, descending=True, stable=True)
+    hit = torch.gather(relevant, 1, order)
+    first = torch.argmax(hit.to(torch.int8), dim=1)
+    rr = torch.where(hit.any(dim=1), 1.0 / (first.double() + 1.0), torch.zeros_like(first, dtype=torch.float64))
+    n3 = min(3, sims.shape[1])
+    return rr, order[:, :n3], val[:, :n3]
+
+
+def compute_mrr(model, query, relevant_docs, candidate_docs, vocab, max_length=30, batch_size=128):
+    """Text-level drop-in for validate_margin.compute_mrr(model, query, relevant_docs, candidate_docs, word2vec, device):
+    `vocab` replaces word2vec (the model carries the table, `attach_embeddings`), the device is the model's.  Candidates are
+    encoded in batches (the reference: 128 at a time, :21-36) with the margin model's text preprocessing.  Returns
+    (1/rank of the first candidate that is in relevant_docs or 0.0, [(doc, score)] of the three best), as :45-54."""
+    dev = next(model.parameters()).device
+    was_training = model.training
+    model.eval()
+    try:
+        with torch.no_grad():
+            qv = model.encode_query(vocab.encode_margin_batch([query], max_length).to(dev))
+            outs = []
+            for i in range(0, len(candidate_docs), batch_size):
+                outs.append(model.encode_doc(vocab.encode_margin_batch(candidate_docs[i:i + batch_size], max_length).to(dev)))
+    finally:
+        model.train(was_training)
+    if not outs:
+        return 0.0, []
+    relevant = torch.tensor([[d in relevant_docs for d in candidate_docs]], dtype=torch.bool)
+    rr, idx, val = first_relevant_rank(qv, torch.cat(outs, 0), relevant)
+    top = [(candidate_docs[i], float(v)) for i, v in zip(idx[0].tolist(), val[0].tolist())]
+    return float(rr[0].item()), top
+
+
 # ------------------------------------------------------------------------------------------- N3: serving path
 class SearchService:
     """The `/search` handler of server/python-api/app.py:85-120 without the web framework: query text -> ids ->
