@@ -82,3 +82,52 @@ def test_first_relevant_rank_equals_live_reference_compute_mrr():
             assert np.allclose(val[0].tolist(), [s for _, s in ref_top], atol=1e-5)
             compared += 1
     assert compared >= 3
+
+
+def test_compute_mrr_glue_on_cpu_with_the_port_as_model():
+    """compute_mrr's own logic (margin tokenisation, batching, relevance by text, mode restore) with the oracle port standing
+    in for the device model: must reproduce oracle margin_ids + full_rank_rr exactly (same arithmetic on both sides)."""
+    import json
+    import os
+    from conftest import GOLDEN
+    from oracle import ref_port as rp
+    G = json.load(open(os.path.join(GOLDEN, "pipeline.json")))
+    vocab = tt.Vocabulary(G["words"], pad_id=0, first_id=1)
+    index = {}
+    for i, w in enumerate(G["words"]):
+        index.setdefault(w, i + 1)                                            # duplicate words keep their first row
+    E, H, L = 10, 8, 30
+    torch.manual_seed(1)
+    port = rp.build_port("margin", E, H).train()
+    table = torch.randn(vocab.table_rows(), E, generator=torch.Generator().manual_seed(7)) * 0.5
+    table[0] = 0
+
+    class IdModel(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.port = port
+
+        def encode_query(self, ids):
+            return self.port.encode_query(table[ids])
+
+        def encode_doc(self, ids):
+            return self.port.encode_doc(table[ids])
+
+    model = IdModel().train()
+    rng = random.Random(4)
+    cands = [" ".join(rng.choice(G["words"]) for _ in range(rng.randint(1, 25))) for _ in range(12)]
+    cands[8] = cands[1]                                                       # duplicate text: tie, both relevant by text
+    for query, relevant in ((cands[3], {cands[9]}), ("what is a " + cands[7], {cands[1]}), ("zzz", {"not a candidate"})):
+        rr, top = tt.compute_mrr(model, query, relevant, cands, vocab, max_length=L, batch_size=5)
+        assert model.training
+        port.eval()
+        with torch.no_grad():
+            qv = port.encode_query(table[torch.tensor([rpl.margin_ids(query, index, L)])])
+            dv = torch.cat([port.encode_doc(table[torch.tensor([rpl.margin_ids(c, index, L) for c in cands[i:i + 5]])])
+                            for i in range(0, 12, 5)], 0)
+            sims = torch.nn.functional.cosine_similarity(qv.unsqueeze(1), dv.unsqueeze(0), dim=2).squeeze(0)
+        port.train()
+        want_rr, want_top = rpl.full_rank_rr(sims.tolist(), cands, relevant)
+        assert rr == want_rr and [d for d, _ in top] == [d for d, _ in want_top]
+        assert [s for _, s in top] == [s for _, s in want_top]
+    assert tt.compute_mrr(model, "anything", {"x"}, [], vocab) == (0.0, [])
