@@ -449,7 +449,19 @@ __global__ void rescore_rows_kernel(const float* __restrict__ X, int Q, const fl
   const float scale = cosine ? 1.f : (1.f / invx[row]) * (1.f / __uint_as_float(*min_invy));
   // two passes: plus |x| times the largest fp16 rounding residual of a corpus row (min_invy[1], see resid_norm_kernel)
   const float extra = two_pass ? __uint_as_float(min_invy[1]) * (cosine ? 1.f : 1.f / invx[row]) : 0.f;
-  const bool ok = !full || (e_k - a_min > kScoreErr * scale + extra);               // false for NaN/inf as well
+  // the query's own hi + lo split is exact to ~2^-22 |x| only while its components stay above the fp16 subnormal range:
+  // add the MEASURED |x - x_hi - x_lo|_2 times the largest corpus row norm (cosine: planes are normalised, times invx)
+  float rx = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float xv = X[(int64_t)row * D + d];
+    const float h = __half2float(__float2half_rn(xv));
+    const float l = __half2float(__float2half_rn(xv - h));
+    const float r = (xv - h) - l;
+    rx = fmaf(r, r, rx);
+  }
+  rx = sqrtf(warp_sum(rx)) * 1.001953125f;
+  const float extra_x = rx * (cosine ? invx[row] : 1.f / __uint_as_float(*min_invy));
+  const bool ok = !full || (e_k - a_min > kScoreErr * scale + extra + extra_x);     // false for NaN/inf as well
   if (lane == 0) need[row] = ok ? 0 : 1;
   if (ok && rank < k) {
     out_val[(int64_t)row * k + rank] = valid ? ev : -INFINITY;
