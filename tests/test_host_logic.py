@@ -91,6 +91,28 @@ def _dp_worker(rank, world, port, ret):
         red.finish()
         ok = abs(loss.item() - full.item()) < 1e-5 * abs(full.item()) and \
             (w.grad - wf.grad).norm() < 1e-5 * wf.grad.norm()
+        # buckets: never straddle a top-level submodule, reverse registration order, p.grad ends up as a view of the bucket
+        net = torch.nn.ModuleDict({"a": torch.nn.Linear(D, D), "b": torch.nn.Linear(D, 2)})
+        for p_ in net.parameters():
+            dist.broadcast(p_.data, 0)
+        ref_net = torch.nn.ModuleDict({"a": torch.nn.Linear(D, D), "b": torch.nn.Linear(D, 2)})
+        ref_net.load_state_dict(net.state_dict())
+        red2 = dops.GradientAllReducer(None, named_params=net.named_parameters(), bucket_bytes=1 << 20)
+        ok = ok and [len(b) for b in red2.buckets] == [2, 2] and red2.buckets[0][0] is net["b"].bias
+        xs = torch.randn(world, 2, 4, D)                       # [rank][micro-batch]
+        with red2.no_sync():
+            net["b"](net["a"](xs[rank, 0])).square().sum().backward()
+        net["b"](net["a"](xs[rank, 1])).square().sum().backward()
+        try:                                                   # a third backward without finish(): must raise, not drop data
+            net["b"](net["a"](xs[rank, 1])).square().sum().backward()
+            ok = False
+        except RuntimeError as e:
+            ok = ok and "no_sync" in str(e)
+        red2.finish()
+        ref_net["b"](ref_net["a"](xs.reshape(-1, D))).square().sum().backward()
+        for (n_, p_), q_ in zip(net.named_parameters(), ref_net.parameters()):
+            ok = ok and (p_.grad - q_.grad).norm() < 1e-5 * q_.grad.norm() + 1e-7
+            ok = ok and p_.grad.untyped_storage().data_ptr() == red2._flat[red2._bucket_of[id(p_)]].untyped_storage().data_ptr()
         lo, hi = dops.shard_bounds(11)
         ok = ok and (lo, hi) == ((0, 6) if rank == 0 else (6, 11))
         ret[rank] = (bool(ok), loss.item(), full.item(), (w.grad - wf.grad).abs().max().item(), lo, hi)

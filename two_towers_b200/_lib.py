@@ -172,8 +172,21 @@ def ptr(t):
     return t.data_ptr()
 
 
-def stream():
-    return torch.cuda.current_stream().cuda_stream
+def stream(device=None):
+    """Raw handle of torch's current stream ON `device` (None = the current device)."""
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def run(device, fn, what, *args):
+    """Call a library entry point whose last argument is the stream, with `device` made current for the call (the C side
+    launches on the current device and keeps per-device state) and torch's current stream of THAT device."""
+    if device.type != "cuda":
+        raise RuntimeError("two_towers_b200 kernels need CUDA tensors (no CPU fallback)")
+    if torch.cuda.current_device() == device.index:
+        check(fn(*args, torch.cuda.current_stream(device).cuda_stream), what)
+    else:
+        with torch.cuda.device(device):
+            check(fn(*args, torch.cuda.current_stream(device).cuda_stream), what)
 
 
 def f32c(t):

@@ -45,6 +45,16 @@ struct ProfScope {
     if (_r != TT_OK) return _r; \
   } while (0)
 
+// Per-DEVICE one-time state (cudaFuncSetAttribute applies to the current device's context; SM counts differ per device):
+// one process may drive several GPUs, so nothing device-dependent is cached in a plain static.
+struct DeviceOnce {
+  unsigned long long mask = 0;        // bit d: done on device d (guarded by the library's state mutex)
+  bool need();                        // true if the current device has not been marked yet
+  void done();
+};
+int device_sm_count();                // SMs of the current device (cached per device)
+int device_cooperative();             // cudaDevAttrCooperativeLaunch of the current device
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline uint64_t align_up(uint64_t a, uint64_t b) { return (a + b - 1) / b * b; }
 

@@ -4,6 +4,7 @@
 // Tile 128x128x16, 256 threads, 8x8 register micro-tile split in 4+4 so shared-memory float4 reads are
 // conflict free.  Each C element is ONE fp32 FMA chain over the reduction index in ascending order.
 #include <stdarg.h>
+#include <mutex>
 #include "common.cuh"
 #include "simt_tile.cuh"
 #include "gru_umma.cuh"
@@ -23,6 +24,26 @@ int g_engine = 2;
 int engine_mode() { return g_engine; }
 void note_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
 unsigned long long launches() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
+// ------------------------------------------------------------------------------ per-device one-time state
+static std::mutex g_state_mu;
+static int cur_dev() { int d = 0; if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d > 63) d = 0; return d; }
+bool DeviceOnce::need() { std::lock_guard<std::mutex> l(g_state_mu); return !((mask >> cur_dev()) & 1ull); }
+void DeviceOnce::done() { std::lock_guard<std::mutex> l(g_state_mu); mask |= 1ull << cur_dev(); }
+int device_sm_count() {
+  static int sms[64];
+  const int d = cur_dev();
+  std::lock_guard<std::mutex> l(g_state_mu);
+  if (!sms[d] && (cudaDeviceGetAttribute(&sms[d], cudaDevAttrMultiProcessorCount, d) != cudaSuccess || sms[d] <= 0)) sms[d] = 148;
+  return sms[d];
+}
+int device_cooperative() {
+  static int coop[64];            // 0 unknown, 1 no, 2 yes
+  const int d = cur_dev();
+  std::lock_guard<std::mutex> l(g_state_mu);
+  if (!coop[d]) { int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, d); coop[d] = v ? 2 : 1; }
+  return coop[d] == 2;
+}
 
 // ------------------------------------------------------------------------------ per-family event timing
 struct ProfSlot {

@@ -368,10 +368,10 @@ int gru_layer_fwd_umma(const tt_gru_layer* a, cudaStream_t s) {
       TT_CUDA(cudaMemsetAsync(hbuf[i][d].hi, 0, sizeof(bf16) * B * hbuf[i][d].pitch, s));
       TT_CUDA(cudaMemsetAsync(hbuf[i][d].lo, 0, sizeof(bf16) * B * hbuf[i][d].pitch, s));
     }
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     TT_CUDA(cudaFuncSetAttribute(gru_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM));
-    attr_done = true;
+    attr_once.done();
   }
   GruStepParams prm[2];
   for (int i = 0; i < 2; ++i) {

@@ -18,6 +18,7 @@
 #include "umma.cuh"
 #include "umma_gemm.cuh"
 #include "gru_v2.cuh"
+#include <mutex>
 
 namespace tt {
 using namespace umma;
@@ -1835,10 +1836,10 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     const uint64_t sneed = carve_saved(d, a->saved, a->saved_bytes, &sv, true);
     if (sneed > a->saved_bytes) { set_error("gru stack fwd (v2): saved buffer too small (%llu < %llu)", (unsigned long long)a->saved_bytes, (unsigned long long)sneed); return TT_ERR_WORKSPACE; }
   }
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     TT_CUDA(cudaFuncSetAttribute(gru_step2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S_SMEM));
-    attr_done = true;
+    attr_once.done();
   }
   // layer-0 operand planes
   {
@@ -1910,14 +1911,8 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     const int tiles = (H / S_UN) * MT * nd;
     if (seq_mode() != 0) {
       // persistent cooperative launch: all T steps, one CTA per SM at most
-      static int num_sms = 0, coop = -1;
-      if (!num_sms) {
-        int dev = 0;
-        TT_CUDA(cudaGetDevice(&dev));
-        TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-        TT_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
-      }
-      TT_CHECK_ARG(coop == 1, "gru stack fwd (v2): device lacks cooperative launch");
+      const int num_sms = device_sm_count();
+      TT_CHECK_ARG(device_cooperative() == 1, "gru stack fwd (v2): device lacks cooperative launch");
       const int tpc = (int)ceil_div(tiles, num_sms);
       const int ncta = (int)ceil_div(tiles, tpc);
       SeqParams sp;
@@ -1928,12 +1923,12 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
       note_launch();
       ProfScope prof(PROF_GRU_SEQ_FWD, s);
       if (seq_mode() == 2) {
-        static bool a2 = false;
-        if (!a2) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a2 = true; }
+        static DeviceOnce a2;
+        if (a2.need()) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a2.done(); }
         TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<2>, dim3(ncta), dim3(256 + 128), args, Q_SMEM, s));
       } else {
-        static bool a4 = false;
-        if (!a4) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a4 = true; }
+        static DeviceOnce a4;
+        if (a4.need()) { TT_CUDA(cudaFuncSetAttribute(gru_seq_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, Q_SMEM)); a4.done(); }
         TT_CUDA(cudaLaunchCooperativeKernel((const void*)gru_seq_kernel<4>, dim3(ncta), dim3(512 + 128), args, Q_SMEM, s));
       }
     } else {
@@ -1982,17 +1977,23 @@ uint64_t gru_stack_bwd_workspace_v2(const tt_gru_stack_grad* a) { return carve_b
 // Helper stream per caller stream: the weight-gradient GEMMs + bias sums of layer l run here, concurrently with the
 // BPTT kernel of layer l-1 on the caller's stream (that kernel occupies one CTA per (row tile, direction), the GEMMs
 // get the remaining SMs).  Forked / joined with events, so to the caller all work stays ordered on its stream.
-struct SideStream { cudaStream_t caller, side; cudaEvent_t fork, done[2]; bool used; };
+struct SideStream { int dev; cudaStream_t caller, side; cudaEvent_t fork, done[2]; };
 static SideStream* side_for(cudaStream_t caller) {
-  static SideStream table[8];
+  // keyed by (device, caller stream): stream handle 0 is the same value on every device.  Entries are never freed (a
+  // process uses a handful of streams); past 64 of them the caller simply gets no overlap.
+  static SideStream table[64];
   static int n = 0;
-  for (int i = 0; i < n; ++i) if (table[i].caller == caller) return &table[i];
-  if (n == 8) return nullptr;
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < n; ++i) if (table[i].caller == caller && table[i].dev == dev) return &table[i];
+  if (n == 64) return nullptr;
   SideStream& t = table[n];
   if (cudaStreamCreateWithFlags(&t.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
   if (cudaEventCreateWithFlags(&t.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
   for (int i = 0; i < 2; ++i) if (cudaEventCreateWithFlags(&t.done[i], cudaEventDisableTiming) != cudaSuccess) return nullptr;
-  t.caller = caller; t.used = false;
+  t.caller = caller; t.dev = dev;
   return &table[n++];
 }
 
@@ -2007,10 +2008,10 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
   V2BwdWs f;
   const uint64_t need = carve_bwd_ws(d, a->workspace, a->workspace_bytes, &f);
   if (need > a->workspace_bytes || !a->workspace) { set_error("gru stack bwd (v2): workspace too small (%llu < %llu)", (unsigned long long)a->workspace_bytes, (unsigned long long)need); return TT_ERR_WORKSPACE; }
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     TT_CUDA(cudaFuncSetAttribute(cell_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CB_SMEM));
-    attr_done = true;
+    attr_once.done();
   }
   // loss scale from the incoming gradients
   TT_CUDA(cudaMemsetAsync(f.mx, 0, 16, s));
@@ -2026,8 +2027,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     TT_LAUNCH_CHECK();
     d_above = f.dab[(L - 1) & 1];
   }
-  static int num_sms_b = 0;
-  if (!num_sms_b) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms_b, cudaDevAttrMultiProcessorCount, dev)); }
+  const int num_sms_b = device_sm_count();
   // CTA pairs halve the latency of a timestep but cost more SM-time (5.2 ms on 128 SMs vs 6.6 ms on 64 at B = 4096, where the
   // idle SMs are busy with the weight-gradient GEMMs and the other tower anyway): used when the pairs fit in half the GPU
   // (measured: 12.6 vs 13.8 ms/step at B = 2048, 9.4 vs 11.4 at B = 1024); mode 3 forces them.
@@ -2106,8 +2106,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     r.f16 = 1; r.npass = 1; r.a_rows = d.ntok; r.epi = 1; r.tl_Bp = Bp; r.tl_G = 1; r.tl_Hc = H;
     if ((H == 64 || H == 128 || H == 256) && bwd_seq_mode() != 0) {
       // fused persistent BPTT: dL/dh stays in tensor memory for the whole sequence
-      static int num_sms = 0;
-      if (!num_sms) { int dev = 0; TT_CUDA(cudaGetDevice(&dev)); TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev)); }
+      const int num_sms = num_sms_b;
       BwdSeqParams bp;
       memset(&bp, 0, sizeof(bp));
       for (int dd = 0; dd < nd; ++dd) {
@@ -2121,19 +2120,19 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       const int pair_grid = 2 * bp.tiles <= num_sms ? 2 * bp.tiles : (num_sms & ~1);
 #define TT_BWD_PAIR(DABV)                                                                                             \
   do {                                                                                                                \
-    static bool attr = false;                                                                                         \
-    if (!attr) {                                                                                                      \
+    static DeviceOnce attr;                                                                                           \
+    if (attr.need()) {                                                                                                \
       TT_CUDA(cudaFuncSetAttribute(gru_bwd_pair_kernel<DABV>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));  \
-      attr = true;                                                                                                    \
+      attr.done();                                                                                                    \
     }                                                                                                                 \
     gru_bwd_pair_kernel<DABV><<<pair_grid, R_THREADS, P_SMEM, s>>>(bp);                                               \
   } while (0)
 #define TT_BWD_SEQ(NCHV, DABV)                                                                                        \
   do {                                                                                                                \
-    static bool attr = false;                                                                                         \
-    if (!attr) {                                                                                                      \
+    static DeviceOnce attr;                                                                                           \
+    if (attr.need()) {                                                                                                \
       TT_CUDA(cudaFuncSetAttribute(gru_bwd_seq_kernel<NCHV, DABV>, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM)); \
-      attr = true;                                                                                                    \
+      attr.done();                                                                                                    \
     }                                                                                                                 \
     gru_bwd_seq_kernel<NCHV, DABV><<<grid, R_THREADS, R_SMEM, s>>>(bp);                                               \
   } while (0)

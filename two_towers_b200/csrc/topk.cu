@@ -635,9 +635,9 @@ static int rows_topk_impl(const float* x, int32_t Q, const float* y, int64_t N, 
     // rejected rows: a few -> gathered, one warp per row; many -> the tile-shaped exact scan below (gated on the count)
     rs_cap = g_rescan ? rescan_cap(D) : 0;
     if (rs_cap > 0) {
-      static bool attr_done = false;
+      static DeviceOnce attr_once;
       const uint32_t smem = rescan_smem(D);
-      if (!attr_done) { TT_CUDA(cudaFuncSetAttribute(rescan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_done = true; }
+      if (attr_once.need()) { TT_CUDA(cudaFuncSetAttribute(rescan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_once.done(); }
       TT_CUDA(cudaMemsetAsync(t.nfail, 0, sizeof(int), s));
       note_launch(); compact_need_kernel<<<(unsigned)ceil_div(Q, 256), 256, 0, s>>>(t.need, Q, t.fail_rows, t.nfail);
       note_launch();

@@ -550,17 +550,12 @@ __global__ void prescale_kernel(float* C, int64_t ldc, int M, int N, float beta)
 template <int BN, bool A_MN, bool B_MN, int NPASS>
 static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t s) {
   auto kern = umma_gemm_kernel<BN, A_MN, B_MN, NPASS>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;                  // one per template instantiation
+  if (attr_once.need()) {
     TT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, NPASS>::SMEM_BYTES));
-    attr_done = true;
+    attr_once.done();
   }
-  static int num_sms = 0;
-  if (!num_sms) {
-    int dev = 0;
-    TT_CUDA(cudaGetDevice(&dev));
-    TT_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  const int num_sms = device_sm_count();
   const int cap = (max_ctas > 0 && max_ctas < num_sms && p.epi != 2) ? max_ctas : num_sms;
   const int grid = items < cap ? items : cap;
   note_launch();
@@ -573,12 +568,7 @@ static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t
 static_assert(sizeof(UmmaParams) <= sizeof(((UmmaPrepared*)0)->blob), "UmmaPrepared blob too small");
 
 static int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-  }
-  return n;
+  return device_sm_count();
 }
 // slots per row of the selection epilogue's output for an [M, N] problem (must mirror umma_gemm_prepare)
 static int g_sel_resident = 1, g_sel_prefetch = 4, g_sel_bn128 = 0;   // 128-column tiles x 4 accumulators measured slower (7.8 vs 5.65 ms)

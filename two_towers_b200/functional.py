@@ -106,7 +106,7 @@ class GRUStackFunction(torch.autograd.Function):
             a.saved, a.saved_bytes = saved.data_ptr(), saved.numel()
         ws = L.workspace(lib.tt_gru_stack_fwd_workspace(C.byref(a)), dev)
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
-        L.check(lib.tt_gru_stack_fwd(C.byref(a), L.stream()), "tt_gru_stack_fwd")
+        L.run(dev, lib.tt_gru_stack_fwd, "tt_gru_stack_fwd", C.byref(a))
         if cfg.need_grad:
             ctx.cfg, ctx.is_ids, ctx.seed, ctx.nw = cfg, is_ids, seed, len(weights)
             ctx.save_for_backward(x, saved, *weights)
@@ -135,7 +135,7 @@ class GRUStackFunction(torch.autograd.Function):
         g.d_weights = C.cast(garr, C.POINTER(C.c_void_p))
         ws = L.workspace(lib.tt_gru_stack_bwd_workspace(C.byref(g)), dev)
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
-        L.check(lib.tt_gru_stack_bwd(C.byref(g), L.stream()), "tt_gru_stack_bwd")
+        L.run(dev, lib.tt_gru_stack_bwd, "tt_gru_stack_bwd", C.byref(g))
         return (None, d_x, *grads)
 
 
@@ -180,7 +180,7 @@ class HeadFunction(torch.autograd.Function):
         a.v_lo, a.v_hi = L.ptr(v_lo), L.ptr(v_hi)
         a.w1, a.b1, a.ln_w, a.ln_b, a.w2, a.b2 = (L.ptr(t) for t in (w1, b1, ln_w, ln_b, w2, b2))
         a.y1, a.stats, a.y2, a.y3, a.out, a.norm = (L.ptr(t) for t in (y1, stats, y2, y3, out, norm))
-        L.check(lib.tt_head_fwd(C.byref(a), L.stream()), "tt_head_fwd")
+        L.run(dev, lib.tt_head_fwd, "tt_head_fwd", C.byref(a))
         result = out if normalize else (y3 if has2 else y2)
         if need_grad:
             ctx.meta = (B, In, P1, D2, bool(normalize), float(dropout_p), int(a.seed), has2)
@@ -217,7 +217,7 @@ class HeadFunction(torch.autograd.Function):
         g.d_w1, g.d_b1, g.d_ln_w, g.d_ln_b, g.d_w2, g.d_b2 = (L.ptr(t) for t in (d_w1, d_b1, d_ln_w, d_ln_b, d_w2, d_b2))
         ws = L.workspace(lib.tt_head_bwd_workspace(C.byref(g)), dev)
         g.workspace, g.workspace_bytes = ws.data_ptr(), ws.numel()
-        L.check(lib.tt_head_bwd(C.byref(g), L.stream()), "tt_head_bwd")
+        L.run(dev, lib.tt_head_bwd, "tt_head_bwd", C.byref(g))
         return d_v_lo, d_v_hi, d_w1, d_b1, d_ln_w, d_ln_b, d_w2, d_b2, None, None, None
 
 
@@ -235,7 +235,7 @@ class L2NormFunction(torch.autograd.Function):
         x = L.f32c(x)
         B, D = x.shape
         y, norm = torch.empty_like(x), torch.empty(B, device=x.device, dtype=torch.float32)
-        L.check(lib.tt_l2norm_fwd(L.ptr(x), B, D, eps, L.ptr(y), L.ptr(norm), L.stream()), "tt_l2norm_fwd")
+        L.run(x.device, lib.tt_l2norm_fwd, "tt_l2norm_fwd", L.ptr(x), B, D, eps, L.ptr(y), L.ptr(norm))
         ctx.eps = eps
         ctx.save_for_backward(y, norm)
         return y
@@ -246,8 +246,7 @@ class L2NormFunction(torch.autograd.Function):
         y, norm = ctx.saved_tensors
         dy = L.f32c(dy)
         dx = torch.empty_like(y)
-        L.check(lib.tt_l2norm_bwd(L.ptr(y), L.ptr(norm), L.ptr(dy), y.shape[0], y.shape[1], ctx.eps, L.ptr(dx),
-                                  L.stream()), "tt_l2norm_bwd")
+        L.run(y.device, lib.tt_l2norm_bwd, "tt_l2norm_bwd", L.ptr(y), L.ptr(norm), L.ptr(dy), y.shape[0], y.shape[1], ctx.eps, L.ptr(dx))
         return dx, None
 
 
@@ -270,8 +269,8 @@ class ScoreCEFunction(torch.autograd.Function):
         row_loss = torch.empty(Bl, device=dev, dtype=torch.float32)
         row_lse = torch.empty(Bl, device=dev, dtype=torch.float32)
         ws = L.workspace(lib.tt_score_ce_workspace(Bl, Bg, D), dev)
-        L.check(lib.tt_score_ce_fwd(L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_loss),
-                                    L.ptr(row_lse), ws.data_ptr(), ws.numel(), L.stream()), "tt_score_ce_fwd")
+        L.run(dev, lib.tt_score_ce_fwd, "tt_score_ce_fwd", L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_loss),
+                                    L.ptr(row_lse), ws.data_ptr(), ws.numel())
         ctx.args = (pos_offset, inv_temp, margin)
         ctx.save_for_backward(x, y, row_lse)
         ctx.mark_non_differentiable(row_lse)
@@ -288,9 +287,8 @@ class ScoreCEFunction(torch.autograd.Function):
         ws = L.workspace(lib.tt_score_ce_workspace(Bl, Bg, D), x.device)
         # the upstream gradient stays on the device (float(g) would drain the launch queue at the start of every backward)
         g = L.f32c(g)
-        L.check(lib.tt_score_ce_bwd_dev(L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_lse),
-                                        1.0, L.ptr(g), L.ptr(dx), L.ptr(dy), ws.data_ptr(), ws.numel(), L.stream()),
-                "tt_score_ce_bwd_dev")
+        L.run(x.device, lib.tt_score_ce_bwd_dev, "tt_score_ce_bwd_dev", L.ptr(x), Bl, L.ptr(y), Bg, D, pos_offset, inv_temp, margin, L.ptr(row_lse),
+                                        1.0, L.ptr(g), L.ptr(dx), L.ptr(dy), ws.data_ptr(), ws.numel())
         return dx, dy, None, None, None
 
 
@@ -308,7 +306,7 @@ class HingeFunction(torch.autograd.Function):
         B, D = q.shape
         k = neg.shape[0] // B
         row = torch.empty(B, device=q.device, dtype=torch.float32)
-        L.check(lib.tt_hinge_fwd(L.ptr(q), L.ptr(pos), L.ptr(neg), B, k, D, margin, L.ptr(row), L.stream()), "tt_hinge_fwd")
+        L.run(q.device, lib.tt_hinge_fwd, "tt_hinge_fwd", L.ptr(q), L.ptr(pos), L.ptr(neg), B, k, D, margin, L.ptr(row))
         ctx.margin, ctx.k = margin, k
         ctx.save_for_backward(q, pos, neg)
         return row.sum()
@@ -320,8 +318,8 @@ class HingeFunction(torch.autograd.Function):
         B, D = q.shape
         dq, dpos, dneg = torch.empty_like(q), torch.empty_like(pos), torch.empty_like(neg)
         g = L.f32c(g)
-        L.check(lib.tt_hinge_bwd_dev(L.ptr(q), L.ptr(pos), L.ptr(neg), B, ctx.k, D, ctx.margin, 1.0, L.ptr(g), L.ptr(dq),
-                                     L.ptr(dpos), L.ptr(dneg), L.stream()), "tt_hinge_bwd_dev")
+        L.run(q.device, lib.tt_hinge_bwd_dev, "tt_hinge_bwd_dev", L.ptr(q), L.ptr(pos), L.ptr(neg), B, ctx.k, D, ctx.margin, 1.0, L.ptr(g), L.ptr(dq),
+                                     L.ptr(dpos), L.ptr(dneg))
         return dq, dpos, dneg, None
 
 
@@ -341,8 +339,8 @@ def rows_topk(x, y, k, cosine=True, mask_pos_offset=-1, index_base=0):
     val = torch.empty(Q, k, device=x.device, dtype=torch.float32)
     idx = torch.empty(Q, k, device=x.device, dtype=torch.int64)
     ws = L.workspace(lib.tt_rows_topk_workspace(Q, N, D, mode), x.device)
-    L.check(lib.tt_rows_topk(L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base), L.ptr(val),
-                             L.ptr(idx), ws.data_ptr(), ws.numel(), L.stream()), "tt_rows_topk")
+    L.run(x.device, lib.tt_rows_topk, "tt_rows_topk", L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base), L.ptr(val),
+                             L.ptr(idx), ws.data_ptr(), ws.numel())
     return val, idx
 
 
@@ -354,9 +352,7 @@ def corpus_index_build(y, cosine=True):
         raise RuntimeError("two_towers_b200: corpus index needs a CUDA tensor (no CPU fallback)")
     N, D = y.shape
     buf = torch.empty(lib.tt_corpus_index_bytes(N, D), dtype=torch.uint8, device=y.device)
-    with torch.cuda.device(y.device):
-        L.check(lib.tt_corpus_index_build(L.ptr(y), N, D, 1 if cosine else 0, buf.data_ptr(), buf.numel(), L.stream()),
-                "tt_corpus_index_build")
+    L.run(y.device, lib.tt_corpus_index_build, "tt_corpus_index_build", L.ptr(y), N, D, 1 if cosine else 0, buf.data_ptr(), buf.numel())
     return buf
 
 
@@ -371,9 +367,8 @@ def rows_topk_indexed(x, y, index, k, cosine=True, mask_pos_offset=-1, index_bas
     val = torch.empty(Q, k, device=x.device, dtype=torch.float32)
     idx = torch.empty(Q, k, device=x.device, dtype=torch.int64)
     ws = L.workspace(lib.tt_rows_topk_indexed_workspace(Q, N, D, mode), x.device)
-    L.check(lib.tt_rows_topk_indexed(L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base),
-                                     L.ptr(val), L.ptr(idx), index.data_ptr(), index.numel(), ws.data_ptr(), ws.numel(),
-                                     L.stream()), "tt_rows_topk_indexed")
+    L.run(x.device, lib.tt_rows_topk_indexed, "tt_rows_topk_indexed", L.ptr(x), Q, L.ptr(y), N, D, k, mode, int(mask_pos_offset), int(index_base),
+                                     L.ptr(val), L.ptr(idx), index.data_ptr(), index.numel(), ws.data_ptr(), ws.numel())
     if return_fallback_rows:
         off = lib.tt_debug_topk_fallback_flags(Q, N, D, mode, k, 1)
         flags = ws[off:off + 4 * Q].view(torch.int32).clone() if off >= 0 else torch.zeros(Q, dtype=torch.int32, device=x.device)
@@ -389,7 +384,7 @@ def topk_merge(vals, idx):
     S, Q, k = vals.shape
     ov = torch.empty(Q, k, device=vals.device, dtype=torch.float32)
     oi = torch.empty(Q, k, device=vals.device, dtype=torch.int64)
-    L.check(lib.tt_topk_merge(L.ptr(vals), L.ptr(idx), S, Q, k, L.ptr(ov), L.ptr(oi), L.stream()), "tt_topk_merge")
+    L.run(vals.device, lib.tt_topk_merge, "tt_topk_merge", L.ptr(vals), L.ptr(idx), S, Q, k, L.ptr(ov), L.ptr(oi))
     return ov, oi
 
 
@@ -401,7 +396,7 @@ def mrr_ranks(topk_idx, relevant):
     Q, k = topk_idx.shape
     fr = torch.empty(Q, device=topk_idx.device, dtype=torch.int32)
     rr = torch.empty(Q, device=topk_idx.device, dtype=torch.float32)
-    L.check(lib.tt_mrr_ranks(L.ptr(topk_idx), L.ptr(relevant), Q, k, L.ptr(fr), L.ptr(rr), L.stream()), "tt_mrr_ranks")
+    L.run(topk_idx.device, lib.tt_mrr_ranks, "tt_mrr_ranks", L.ptr(topk_idx), L.ptr(relevant), Q, k, L.ptr(fr), L.ptr(rr))
     return fr, rr
 
 
@@ -411,8 +406,8 @@ def embed_gather(ids, table, pad_id=-1):
     ids = ids.contiguous()
     table = L.f32c(table)
     out = torch.empty(*ids.shape, table.shape[1], device=table.device, dtype=torch.float32)
-    L.check(lib.tt_embed_gather(L.ptr(ids), 1 if ids.dtype == torch.int64 else 0, ids.numel(), L.ptr(table),
-                                table.shape[0], table.shape[1], int(pad_id), L.ptr(out), L.stream()), "tt_embed_gather")
+    L.run(table.device, lib.tt_embed_gather, "tt_embed_gather", L.ptr(ids), 1 if ids.dtype == torch.int64 else 0, ids.numel(), L.ptr(table),
+                                table.shape[0], table.shape[1], int(pad_id), L.ptr(out))
     return out
 
 
@@ -424,5 +419,5 @@ def gemm_nt(a, b, bias=None, alpha=1.0):
     M, K = a.shape
     N = b.shape[0]
     c = torch.empty(M, N, device=a.device, dtype=torch.float32)
-    L.check(lib.tt_gemm_nt(L.ptr(a), K, L.ptr(b), K, L.ptr(c), N, L.ptr(bias), M, N, K, alpha, 0.0, L.stream()), "tt_gemm_nt")
+    L.run(a.device, lib.tt_gemm_nt, "tt_gemm_nt", L.ptr(a), K, L.ptr(b), K, L.ptr(c), N, L.ptr(bias), M, N, K, alpha, 0.0)
     return c

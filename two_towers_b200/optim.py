@@ -141,7 +141,7 @@ class FusedAdam(torch.optim.Optimizer):
         clip = self.max_grad_norm is not None and self.max_grad_norm > 0
         if self._norm is None or self._norm.device != device:
             self._norm = torch.zeros(2, dtype=torch.float32, device=device)
-        stream = L.stream()
+        stream = L.stream(device)
         with torch.cuda.device(device):
             if clip and len(groups) > 1:           # one norm over every group first
                 every = [x for _, e in groups for x in e]
