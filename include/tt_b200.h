@@ -131,6 +131,8 @@ typedef struct tt_gru_stack {
   float* h_n;                      /* [L*ndir,B,H] */
   void* saved; uint64_t saved_bytes;             /* tt_gru_stack_saved_bytes(); needed when save_for_backward */
   void* workspace; uint64_t workspace_bytes;     /* tt_gru_stack_fwd_workspace() */
+  const uint64_t* seed_dev;        /* optional DEVICE scalar added to `seed` when the kernels run: a CUDA graph that captured
+                                      this call draws a new dropout mask on every replay by bumping it (engine 2 only) */
 } tt_gru_stack;
 uint64_t tt_gru_stack_saved_bytes(const tt_gru_stack* a);
 uint64_t tt_gru_stack_fwd_workspace(const tt_gru_stack* a);
@@ -168,6 +170,7 @@ typedef struct tt_head {
   float* y3;        /* [B,D2] pre-normalise (saved; == output when !normalize); unused if D2==0 */
   float* out;       /* [B,Dout] normalised output when normalize, else may be NULL */
   float* norm;      /* [B] when normalize */
+  const uint64_t* seed_dev;   /* optional DEVICE scalar added to `seed` at run time (CUDA-graph replay), or NULL */
 } tt_head;
 int tt_head_fwd(const tt_head* a, void* stream);
 
@@ -270,11 +273,19 @@ int tt_hinge_bwd_dev(const float* q, const float* pos, const float* neg, int32_t
  *                     min(1, max_norm / (norm + 1e-6))  (1 when max_norm <= 0); needs the workspace
  *        TT_OPT_STEP  run the update
  *        TT_OPT_CLIP  the update scales every gradient by norm_out[1] (from this or an earlier call - several
- *                     parameter groups share one norm) and stores the scaled gradient back, as clip_grad_norm_ does */
+ *                     parameter groups share one norm) and stores the scaled gradient back, as clip_grad_norm_ does
+ *        TT_OPT_SKIP_NONFINITE  (with or after a TT_OPT_NORM call) a non-finite total norm - an overflow of the fp16
+ *                     gradient planes of the single-pass BPTT, DESIGN.md section 3 - sets norm_out[3] = 1, adds 1 to
+ *                     norm_out[2] and the update leaves parameters, moments and (capturable) the step count
+ *                     untouched: what torch.cuda.amp.GradScaler does with an inf gradient
+ * step_dev != NULL ("capturable", for CUDA-graph replay): the step count lives on the device; every TT_OPT_STEP call
+ *                     that is not skipped adds 1 to *step_dev and derives both bias corrections from it in double
+ *                     on the device (bias_correction1/2_sqrt of the struct are ignored). */
 #define TT_OPT_CHUNK 65536
 #define TT_OPT_NORM 1
 #define TT_OPT_STEP 2
 #define TT_OPT_CLIP 4
+#define TT_OPT_SKIP_NONFINITE 8
 typedef struct { float* param; float* grad; float* exp_avg; float* exp_avg_sq; int64_t numel; } tt_opt_tensor;
 typedef struct { int32_t tensor; int32_t reserved; int64_t offset; } tt_opt_chunk;
 typedef struct {
@@ -283,8 +294,10 @@ typedef struct {
   /* hyper-parameters as doubles: torch derives 1-beta, lr/bc1, 1-lr*wd in double and rounds ONCE to fp32 - so does this */
   double lr, beta1, beta2, eps, weight_decay, max_norm;
   double bias_correction1, bias_correction2_sqrt;      /* 1 - beta1^t and sqrt(1 - beta2^t) for this step t >= 1 (host) */
-  float* norm_out;                                     /* device [2] */
+  float* norm_out;                                     /* device [4]: norm, clip coefficient, skipped steps, skip flag */
   void* workspace; uint64_t workspace_bytes;
+  float* step_dev;                                     /* device scalar step count or NULL */
+  float* consts_dev;                                   /* device [2] scratch for (lr / bc1, sqrt(bc2)); needed with step_dev */
 } tt_opt_args;
 uint64_t tt_opt_step_workspace(int32_t nchunks);
 int tt_opt_step(const tt_opt_args* a, void* stream);

@@ -37,7 +37,7 @@ def test_binding_covers_every_declared_symbol():
 
 def test_library_reports_version_and_engine_without_gpu():
     lib = _lib.lib()
-    assert lib.tt_abi_version() == 1
+    assert lib.tt_abi_version() == 2
     assert lib.tt_engine().decode() in ("simt-fp32", "tcgen05-bf16x3", "tcgen05-f16x3-fwd/f16-bwd")
 
 
@@ -54,6 +54,7 @@ int main(void){
   printf("%zu %zu\n", offsetof(tt_gru_layer_grad,d_out), offsetof(tt_head_grad,d_out));
   printf("%zu %zu %zu %zu %zu %zu\n", sizeof(tt_gru_stack), sizeof(tt_gru_stack_grad), offsetof(tt_gru_stack,x),
          offsetof(tt_gru_stack,seed), offsetof(tt_gru_stack,saved_bytes), offsetof(tt_gru_stack_grad,d_weights));
+  printf("%zu %zu %zu %zu\n", offsetof(tt_gru_stack,seed_dev), offsetof(tt_head,seed_dev), offsetof(tt_opt_args,step_dev), offsetof(tt_opt_args,consts_dev));
   printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(tt_opt_tensor), sizeof(tt_opt_chunk), sizeof(tt_opt_args), offsetof(tt_opt_chunk,offset),
          offsetof(tt_opt_args,lr), offsetof(tt_opt_args,bias_correction2_sqrt), offsetof(tt_opt_args,workspace_bytes));
   return 0; }
@@ -72,6 +73,7 @@ int main(void){
     S, SG = _lib.GruStack, _lib.GruStackGrad
     exp += [ctypes.sizeof(S), ctypes.sizeof(SG), S.x.offset, S.seed.offset, S.saved_bytes.offset, SG.d_weights.offset]
     from two_towers_b200 import optim as O
+    exp += [S.seed_dev.offset, H.seed_dev.offset, O.OptStep.step_dev.offset, O.OptStep.consts_dev.offset]
     exp += [ctypes.sizeof(O.OptTensor), ctypes.sizeof(O.OptChunk), ctypes.sizeof(O.OptStep), O.OptChunk.offset.offset,
             O.OptStep.lr.offset, O.OptStep.bias_correction2_sqrt.offset, O.OptStep.workspace_bytes.offset]
     assert out == exp

@@ -384,3 +384,95 @@ def test_compute_mrr_matches_oracle_flow(vocab):
             assert abs(top[0][1] - want_top[0][1]) < 5e-3
     assert checked >= 8
     assert tt.compute_mrr(model, "anything", {"x"}, [], vocab) == (0.0, [])
+
+
+@pytest.mark.gpu
+def test_fused_adam_skips_a_step_with_non_finite_gradients():
+    """An overflow of the fp16 gradient planes (inf / NaN weight gradients) must not reach the weights: the step is skipped
+    and counted, as torch.cuda.amp.GradScaler does; the next finite step continues from the untouched state."""
+    dev = torch.device("cuda:0")
+    ours_p, ref_p = _rand_params(dev, 5, SHAPES), _rand_params(dev, 5, SHAPES)
+    for capturable in (False, True):
+        ours = tt.FusedAdam(ours_p, lr=1e-3, max_grad_norm=1.0, capturable=capturable)
+        ref = torch.optim.Adam(ref_p, lr=1e-3)
+        g = torch.Generator().manual_seed(6)
+        for step in range(4):
+            bad = step == 1
+            for a, b in zip(ours_p, ref_p):
+                gr = torch.randn(a.shape, generator=g).to(dev)
+                a.grad, b.grad = gr.clone(), gr.clone()
+            if bad:
+                ours_p[2].grad[5] = float("inf")
+                before = [p.detach().clone() for p in ours_p]
+            else:
+                torch.nn.utils.clip_grad_norm_(ref_p, max_norm=1.0)
+                ref.step()
+            ours.step()
+            if bad:
+                assert all(torch.equal(a, b) for a, b in zip(ours_p, before))
+                assert float(ours.skipped_steps) == 1.0
+        if capturable:          # the device step count did not advance on the skipped step: bit-for-bit torch's trajectory
+            assert float(ours.state[ours_p[0]]["step"]) == 3.0
+            for a, b in zip(ours_p, ref_p):
+                assert torch.allclose(a, b, rtol=2e-6, atol=2e-7)
+        else:                   # host step count advanced (documented): only the bias correction differs, slightly
+            for a, b in zip(ours_p, ref_p):
+                assert torch.allclose(a, b, rtol=0.3, atol=2e-3)
+        with torch.no_grad():
+            for a, b in zip(ours_p, ref_p):
+                b.copy_(a)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["enhanced", "simple"])
+def test_graphed_train_step_equals_the_eager_loop(kind):
+    """N4: the whole step (zero_grad, both towers, loss, backward, clip + AdamW, hard-negative mining) captured in one CUDA
+    graph and replayed equals the eager loop step for step (dropout off: the masks come from different seeds)."""
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    mk = (lambda: tt.EnhancedTwoTowerModel(20, 32)) if kind == "enhanced" else (lambda: tt.SimpleTwoTower(20, 64))
+    m1, m2 = mk().to(dev).train(), mk().to(dev).train()
+    m2.load_state_dict(m1.state_dict())
+    table = (torch.randn(500, 20) * 0.3).to(dev)
+    for m in (m1, m2):
+        m.attach_embeddings(table, pad_id=0)
+        for mod in m.modules():
+            if isinstance(mod, tt.GRU):
+                mod.dropout = 0.0
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+    crit = tt.MarginRankingLoss() if kind == "enhanced" else tt.SymmetricInfoNCELoss(0.1)
+    o1 = tt.FusedAdamW(m1.parameters(), lr=1e-3, weight_decay=0.01, max_grad_norm=1.0, capturable=True)
+    o2 = tt.FusedAdamW(m2.parameters(), lr=1e-3, weight_decay=0.01, max_grad_norm=1.0)
+    step = tt.GraphedTrainStep(m1, crit, o1, mine_k=4)
+    g = torch.Generator().manual_seed(1)
+    for it in range(5):
+        B = 48 if it != 3 else 40                     # a second shape in the middle: second capture, shared state
+        q = torch.randint(0, 500, (B, 6), generator=g).to(dev)
+        d = torch.randint(0, 500, (B, 11), generator=g).to(dev)
+        loss1, hard1 = step(q, d)
+        loss1, hard1 = loss1.clone(), hard1.clone()
+        o2.zero_grad(set_to_none=True)
+        qv, dv = m2(q, d)
+        loss2 = crit(qv, dv)
+        loss2.backward()
+        o2.step()
+        hard2 = tt.get_hard_negatives_batch(qv.detach(), dv.detach(), k=4)
+        assert abs(loss1.item() - loss2.item()) <= 1e-5 * abs(loss2.item()), (it, loss1.item(), loss2.item())
+        assert torch.equal(hard1, hard2), it
+        for (k, a), (_, b) in zip(m1.state_dict().items(), m2.state_dict().items()):
+            assert rel_err(a, b) < 1e-5, (it, k)
+    assert step.replays == 5 and len(step._graphs) == 2
+    assert step.launches_per_replay(q, d) > 20
+
+
+@pytest.mark.gpu
+def test_graphed_train_step_draws_new_dropout_masks_on_every_replay():
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    m = tt.SimpleTwoTower(20, 64).to(dev).train()       # GRU inter-layer dropout 0.1 + head dropout 0.1
+    o = tt.FusedAdamW(m.parameters(), lr=0.0, weight_decay=0.0, capturable=True)     # lr 0: weights stay put
+    step = tt.GraphedTrainStep(m, tt.SymmetricInfoNCELoss(0.1), o)
+    q, d = torch.randn(32, 5, 20, device=dev), torch.randn(32, 7, 20, device=dev)
+    losses = [step(q, d)[0].item() for _ in range(4)]
+    assert len(set(losses)) == 4, losses                # same inputs, same weights: only the masks differ

@@ -43,6 +43,7 @@ class GruStack(C.Structure):
         ("dropout_p", C.c_float), ("_pad0", i32), ("seed", u64),
         ("weights", C.POINTER(C.c_void_p)), ("lengths", C.c_void_p), ("out", C.c_void_p), ("h_n", C.c_void_p),
         ("saved", C.c_void_p), ("saved_bytes", u64), ("workspace", C.c_void_p), ("workspace_bytes", u64),
+        ("seed_dev", C.c_void_p),
     ]
 
 
@@ -61,7 +62,7 @@ class Head(C.Structure):
         ("w1", C.c_void_p), ("b1", C.c_void_p), ("ln_w", C.c_void_p), ("ln_b", C.c_void_p),
         ("w2", C.c_void_p), ("b2", C.c_void_p),
         ("y1", C.c_void_p), ("stats", C.c_void_p), ("y2", C.c_void_p), ("y3", C.c_void_p),
-        ("out", C.c_void_p), ("norm", C.c_void_p),
+        ("out", C.c_void_p), ("norm", C.c_void_p), ("seed_dev", C.c_void_p),
     ]
 
 

@@ -219,7 +219,7 @@ int colsum_f32(const float* X, int64_t ld, int64_t M, int32_t N, float* out, cud
 }  // namespace tt
 
 extern "C" {
-int tt_abi_version(void) { return 1; }
+int tt_abi_version(void) { return 2; }
 uint64_t tt_kernel_launches(void) { return tt::launches(); }
 const char* tt_engine(void) {
   return tt::engine_mode() == 2 ? "tcgen05-f16x3-fwd/f16-bwd" : tt::engine_mode() == 1 ? "tcgen05-bf16x3" : "simt-fp32";

@@ -84,6 +84,7 @@ int tt_gru_stack_fwd(const tt_gru_stack* a, void* stream) {
   TT_TRY(check_stack(a));
   cudaStream_t s = (cudaStream_t)stream;
   if (v2_supported(a)) return gru_stack_fwd_v2(a, s);
+  TT_CHECK_ARG(a->seed_dev == nullptr || a->dropout_p == 0.f, "gru stack: seed_dev (graph-replay dropout) needs engine 2 and H %% 64 == 0");
   const bool save = a->save_for_backward && a->saved;
   LayerBufs lb;
   uint64_t layer_ws_off = 0;

@@ -194,6 +194,7 @@ struct alignas(64) Step2Params {
   int32_t B, Bp, T, H, ndir, step, has_next;
   float drop_p, inv_keep;
   uint64_t seed;
+  const uint64_t* seed_dev;          // optional device scalar added to seed (CUDA-graph replay draws a new mask)
   unsigned long long* dbg;           // optional phase timestamps, 8 per CTA (tools/step_phases.py)
 };
 
@@ -385,7 +386,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
           if (p.drop_p > 0.f && row_ok) {
             const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 8 * c);
             float s8[8];
-            dropout_scale8(p.seed, e >> 3, p.drop_p, p.inv_keep, s8);
+            dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), e >> 3, p.drop_p, p.inv_keep, s8);
 #pragma unroll
             for (int j = 0; j < 8; ++j) xo[j] *= s8[j];
           }
@@ -739,7 +740,7 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
               if (p.drop_p > 0.f && row_ok) {
                 const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 8 * c);
                 float s8[8];
-                dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+                dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), el >> 3, p.drop_p, p.inv_keep, s8);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) xo[j] *= s8[j];
               }
@@ -793,6 +794,7 @@ struct alignas(64) CellBwdParams {
   int32_t B, Bp, T, H, ndir, step;
   float drop_p, inv_keep;            // dropout that was applied to this layer's OUTPUT (the next layer's input)
   uint64_t seed;
+  const uint64_t* seed_dev;
 };
 constexpr int CB_SMEM = 4 * 16384 + 1024;
 
@@ -831,7 +833,7 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
       if (dab && p.drop_p > 0.f) {
         const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 4 * i);
         float s8[8];
-        dropout_scale8(p.seed, e >> 3, p.drop_p, p.inv_keep, s8);
+        dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), e >> 3, p.drop_p, p.inv_keep, s8);
         const int o8 = (i & 1) * 4;
         da.x *= s8[o8]; da.y *= s8[o8 + 1]; da.z *= s8[o8 + 2]; da.w *= s8[o8 + 3];
       }
@@ -906,6 +908,7 @@ struct alignas(64) BwdSeqParams {
   int32_t B, Bp, T, H, ndir, tiles;
   float drop_p, inv_keep;
   uint64_t seed;
+  const uint64_t* seed_dev;
   unsigned long long* dbg;
   // time segment of this launch: BPTT steps step_begin-1, step_begin-2, ..., step_end (step s is timestep s of the
   // forward direction, T-1-s of the reverse one).  A whole sequence is (T, 0).  dhs_out (may alias dhs0, may be null):
@@ -1143,10 +1146,10 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             if (p.drop_p > 0.f && live) {
               const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * c + 16 * sub);
               float s8[8];
-              dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), el >> 3, p.drop_p, p.inv_keep, s8);
               d4[0].x *= s8[0]; d4[0].y *= s8[1]; d4[0].z *= s8[2]; d4[0].w *= s8[3];
               d4[1].x *= s8[4]; d4[1].y *= s8[5]; d4[1].z *= s8[6]; d4[1].w *= s8[7];
-              dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
               d4[2].x *= s8[0]; d4[2].y *= s8[1]; d4[2].z *= s8[2]; d4[2].w *= s8[3];
               d4[3].x *= s8[4]; d4[3].y *= s8[5]; d4[3].z *= s8[6]; d4[3].w *= s8[7];
             }
@@ -1503,10 +1506,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
             if (p.drop_p > 0.f && live) {
               const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * (cg0 + c) + 16 * sub);
               float s8[8];
-              dropout_scale8(p.seed, el >> 3, p.drop_p, p.inv_keep, s8);
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), el >> 3, p.drop_p, p.inv_keep, s8);
               d4[0].x *= s8[0]; d4[0].y *= s8[1]; d4[0].z *= s8[2]; d4[0].w *= s8[3];
               d4[1].x *= s8[4]; d4[1].y *= s8[5]; d4[1].z *= s8[6]; d4[1].w *= s8[7];
-              dropout_scale8(p.seed, (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
               d4[2].x *= s8[0]; d4[2].y *= s8[1]; d4[2].z *= s8[2]; d4[2].w *= s8[3];
               d4[3].x *= s8[4]; d4[3].y *= s8[5]; d4[3].z *= s8[6]; d4[3].w *= s8[7];
             }
@@ -1907,6 +1910,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     p.drop_p = has_next ? a->dropout_p : 0.f;
     p.inv_keep = p.drop_p > 0.f ? 1.f / (1.f - p.drop_p) : 1.f;
     p.seed = a->seed + (uint64_t)(l + 1) * 0x9E3779B97F4A7C15ull;     // per-layer stream (layer l+1's input mask)
+    p.seed_dev = a->seed_dev;
     p.dbg = g_step_dbg;
     const int tiles = (H / S_UN) * MT * nd;
     if (seq_mode() != 0) {
@@ -2095,6 +2099,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     cp.drop_p = (has_next && d_above) ? fw->dropout_p : 0.f;
     cp.inv_keep = cp.drop_p > 0.f ? 1.f / (1.f - cp.drop_p) : 1.f;
     cp.seed = fw->seed + (uint64_t)(l + 1) * 0x9E3779B97F4A7C15ull;
+    cp.seed_dev = fw->seed_dev;
     // per step: dhs (tiled) += dGH_t W_hh     (A rows t*Bp.., K = 3H; B = W_hh as stored = [K][N] MN-major)
     UmmaGemm r{};
     for (int dd = 0; dd < nd; ++dd) {
@@ -2115,7 +2120,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       }
       bp.g16 = sv.g16[l]; bp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
       bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
-      bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.dbg = g_step_dbg;
+      bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.seed_dev = cp.seed_dev; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
       const int pair_grid = 2 * bp.tiles <= num_sms ? 2 * bp.tiles : (num_sms & ~1);
 #define TT_BWD_PAIR(DABV)                                                                                             \

@@ -8,9 +8,10 @@ namespace tt {
 // y2 = relu(LN(y1)) ; stats = (mean, rstd).  One warp per row.
 __global__ void ln_relu_fwd_kernel(const float* __restrict__ y1, const float* __restrict__ w, const float* __restrict__ b,
                                    float* __restrict__ y2, float* __restrict__ stats, int B, int P, float eps, float p,
-                                   float inv_keep, uint64_t seed, uint64_t offset) {
+                                   float inv_keep, uint64_t seed, uint64_t offset, const uint64_t* __restrict__ seed_dev) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= B) return;
+  if (seed_dev) seed += *seed_dev;
   const float* x = y1 + (int64_t)row * P;
   float s = 0.f;
   for (int c = lane; c < P; c += 32) s += x[c];
@@ -153,7 +154,7 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   }
   const float pdrop = a->dropout_p;
   tt::note_launch(); ln_relu_fwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(a->y1, a->ln_w, a->ln_b, a->y2, a->stats, B, P, 1e-5f, pdrop,
-                                                              pdrop > 0.f ? 1.f / (1.f - pdrop) : 1.f, a->seed, a->offset);
+                                                              pdrop > 0.f ? 1.f / (1.f - pdrop) : 1.f, a->seed, a->offset, a->seed_dev);
   TT_LAUNCH_CHECK();
   const float* last = a->y2;
   int Dl = P;

@@ -62,7 +62,20 @@ __global__ void __launch_bounds__(256) opt_finish_norm_kernel(const float* __res
     const float norm = (float)sqrt(sh[0]);
     norm_out[0] = norm;
     norm_out[1] = max_norm > 0.f ? fminf(1.f, max_norm / (norm + 1e-6f)) : 1.f;
+    const bool bad = !(fabsf(norm) <= 3.0e38f);       // inf or NaN
+    norm_out[3] = bad ? 1.f : 0.f;
+    if (bad) norm_out[2] += 1.f;
   }
+}
+
+// capturable mode: step count and bias corrections on the device (one thread), skipped when the gradients are non-finite
+__global__ void opt_prepare_kernel(float* __restrict__ step_dev, float* __restrict__ consts, const float* __restrict__ skip,
+                                   double lr, double beta1, double beta2) {
+  if (skip && skip[3] != 0.f) return;
+  const float t = step_dev[0] + 1.f;
+  step_dev[0] = t;
+  consts[0] = (float)(lr / (1.0 - pow(beta1, (double)t)));
+  consts[1] = (float)sqrt(1.0 - pow(beta2, (double)t));
 }
 
 struct AdamConsts {       // every derived constant is formed in double on the host and rounded once, as torch does
@@ -83,7 +96,10 @@ __device__ __forceinline__ void adam_one(float& p, float& g, float& m, float& v,
 
 __global__ void __launch_bounds__(256) opt_adam_kernel(const tt_opt_tensor* __restrict__ tensors,
                                                        const tt_opt_chunk* __restrict__ chunks,
-                                                       const float* __restrict__ norm, const AdamConsts c) {
+                                                       const float* __restrict__ norm, const float* __restrict__ skip,
+                                                       const float* __restrict__ consts_dev, AdamConsts c) {
+  if (skip && skip[3] != 0.f) return;                  // non-finite gradients: leave everything as it is
+  if (consts_dev) { c.step_size = consts_dev[0]; c.bc2_sqrt = consts_dev[1]; }
   const tt_opt_chunk ck = chunks[blockIdx.x];
   const tt_opt_tensor tn = tensors[ck.tensor];
   const int64_t n = min((int64_t)TT_OPT_CHUNK, tn.numel - ck.offset);
@@ -134,10 +150,11 @@ int tt_opt_step(const tt_opt_args* a, void* stream) {
   TT_CHECK_ARG(a->tensors && a->chunks, "opt_step: null tensor / chunk table");
   TT_CHECK_ARG(a->lr >= 0.0 && a->eps >= 0.0 && a->beta1 >= 0.0 && a->beta1 < 1.0 && a->beta2 >= 0.0 && a->beta2 < 1.0,
                "opt_step: lr/eps/betas out of range");
-  TT_CHECK_ARG(a->bias_correction1 > 0.0 && a->bias_correction2_sqrt > 0.0, "opt_step: bias corrections must be > 0 (step >= 1)");
+  TT_CHECK_ARG(a->step_dev || (a->bias_correction1 > 0.0 && a->bias_correction2_sqrt > 0.0), "opt_step: bias corrections must be > 0 (step >= 1)");
+  TT_CHECK_ARG(!a->step_dev || a->consts_dev, "opt_step: step_dev needs consts_dev");
   const bool do_norm = (a->flags & TT_OPT_NORM) != 0, do_step = (a->flags & TT_OPT_STEP) != 0;
-  const bool clip = (a->flags & TT_OPT_CLIP) != 0;
-  TT_CHECK_ARG(!(do_norm || clip) || a->norm_out, "opt_step: TT_OPT_NORM / TT_OPT_CLIP need norm_out");
+  const bool clip = (a->flags & TT_OPT_CLIP) != 0, skip = (a->flags & TT_OPT_SKIP_NONFINITE) != 0;
+  TT_CHECK_ARG(!(do_norm || clip || skip) || a->norm_out, "opt_step: TT_OPT_NORM / TT_OPT_CLIP / TT_OPT_SKIP_NONFINITE need norm_out");
   cudaStream_t s = (cudaStream_t)stream;
   if (do_norm) {
     TT_CHECK_ARG(a->workspace && a->workspace_bytes >= tt_opt_step_workspace(a->nchunks), "opt_step: workspace too small");
@@ -153,12 +170,18 @@ int tt_opt_step(const tt_opt_args* a, void* stream) {
   AdamConsts c;
   c.decay = (float)(1.0 - a->lr * a->weight_decay); c.wd = (float)a->weight_decay;
   c.omb1 = (float)(1.0 - a->beta1); c.beta2 = (float)a->beta2; c.omb2 = (float)(1.0 - a->beta2); c.eps = (float)a->eps;
-  c.step_size = (float)(a->lr / a->bias_correction1);
-  c.bc2_sqrt = (float)a->bias_correction2_sqrt;
+  c.step_size = a->step_dev ? 0.f : (float)(a->lr / a->bias_correction1);
+  c.bc2_sqrt = a->step_dev ? 1.f : (float)a->bias_correction2_sqrt;
+  if (a->step_dev) {
+    tt::note_launch();
+    opt_prepare_kernel<<<1, 1, 0, s>>>(a->step_dev, a->consts_dev, skip ? a->norm_out : nullptr, a->lr, a->beta1, a->beta2);
+    TT_LAUNCH_CHECK();
+  }
   c.decoupled = a->decoupled_wd != 0 && a->weight_decay != 0.0;
   c.store_grad = clip ? 1 : 0;
   tt::note_launch();
-  opt_adam_kernel<<<(unsigned)a->nchunks, 256, 0, s>>>(a->tensors, a->chunks, clip ? a->norm_out : nullptr, c);
+  opt_adam_kernel<<<(unsigned)a->nchunks, 256, 0, s>>>(a->tensors, a->chunks, clip ? a->norm_out : nullptr, skip ? a->norm_out : nullptr,
+                                                       a->step_dev ? a->consts_dev : nullptr, c);
   TT_LAUNCH_CHECK();
   return TT_OK;
 }

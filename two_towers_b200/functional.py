@@ -11,6 +11,28 @@ def _next_seed():
     return int(torch.randint(0, 2 ** 62, (1,)).item())
 
 
+# Dropout under CUDA-graph replay: a captured call would replay the SAME Philox seed forever.  Inside `device_seed(t)` every
+# dropout-bearing call also hands the kernels the device scalar `t` (int64, 1 element), which they add to the host seed when
+# they RUN - the graphed step bumps it once per replay (graph.GraphedTrainStep).
+_SEED_DEV = None
+
+
+class device_seed:
+    def __init__(self, tensor):
+        if tensor is not None and (tensor.dtype != torch.int64 or tensor.numel() != 1 or not tensor.is_cuda):
+            raise ValueError("device_seed: a 1-element int64 CUDA tensor")
+        self.tensor = tensor
+
+    def __enter__(self):
+        global _SEED_DEV
+        self.prev, _SEED_DEV = _SEED_DEV, self.tensor
+        return self.tensor
+
+    def __exit__(self, *exc):
+        global _SEED_DEV
+        _SEED_DEV = self.prev
+
+
 def _arr2(tensors):
     a = (C.c_void_p * 2)()
     for i, t in enumerate(tensors):
@@ -59,8 +81,9 @@ def _ptr_array(tensors):
     return a
 
 
-def _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, saved, B, T):
+def _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, saved, B, T, seed_dev=None):
     a = L.GruStack()
+    a.seed_dev = seed_dev.data_ptr() if seed_dev is not None else None
     a.B, a.T, a.In, a.H, a.L, a.ndir = B, T, cfg.input_size, cfg.hidden_size, cfg.num_layers, cfg.ndir
     a.save_for_backward = 1 if saved is not None else 0
     a.ids_are_i64 = 1 if (is_ids and x.dtype == torch.int64) else 0
@@ -98,7 +121,8 @@ class GRUStackFunction(torch.autograd.Function):
         out = torch.empty(B, T, nd * H, device=dev, dtype=torch.float32) if cfg.need_out else None
         seed = _next_seed() if (cfg.num_layers > 1 and cfg.dropout_p > 0) else 0
         warr = _ptr_array(weights)
-        a = _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, None, B, T)
+        seed_dev = _SEED_DEV if seed != 0 else None
+        a = _fill_stack(cfg, x, is_ids, weights, warr, out, h_n, seed, None, B, T, seed_dev)
         saved = None
         if cfg.need_grad:
             a.save_for_backward = 1
@@ -108,7 +132,7 @@ class GRUStackFunction(torch.autograd.Function):
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         L.run(dev, lib.tt_gru_stack_fwd, "tt_gru_stack_fwd", C.byref(a))
         if cfg.need_grad:
-            ctx.cfg, ctx.is_ids, ctx.seed, ctx.nw = cfg, is_ids, seed, len(weights)
+            ctx.cfg, ctx.is_ids, ctx.seed, ctx.nw, ctx.seed_dev = cfg, is_ids, seed, len(weights), seed_dev
             ctx.save_for_backward(x, saved, *weights)
         if out is None:
             out = torch.empty(0, device=dev, dtype=torch.float32)
@@ -130,7 +154,7 @@ class GRUStackFunction(torch.autograd.Function):
         warr, garr = _ptr_array(weights), _ptr_array(grads)
         g = L.GruStackGrad()
         g.fwd = _fill_stack(cfg, x, ctx.is_ids, weights, warr, None, d_h_n if d_h_n is not None else grads[0], ctx.seed,
-                            saved, B, T)
+                            saved, B, T, ctx.seed_dev)
         g.d_out, g.d_h_n, g.d_x = L.ptr(d_out), L.ptr(d_h_n), L.ptr(d_x)
         g.d_weights = C.cast(garr, C.POINTER(C.c_void_p))
         ws = L.workspace(lib.tt_gru_stack_bwd_workspace(C.byref(g)), dev)
@@ -173,6 +197,8 @@ class HeadFunction(torch.autograd.Function):
         a.B, a.In, a.P1, a.D2, a.normalize = B, In, P1, D2, 1 if normalize else 0
         a.dropout_p = float(dropout_p)
         a.seed, a.offset = (_next_seed() if dropout_p > 0 else 0), 0
+        seed_dev = _SEED_DEV if dropout_p > 0 else None
+        a.seed_dev = seed_dev.data_ptr() if seed_dev is not None else None
         e = lambda *s: torch.empty(*s, device=dev, dtype=torch.float32)
         y1, stats, y2 = e(B, P1), e(B, 2), e(B, P1)
         y3 = e(B, D2) if has2 else None
