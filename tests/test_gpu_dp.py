@@ -37,6 +37,7 @@ def test_data_parallel_step_matches_single_process_nccl_world2():
     world = 2
     ret = mp.get_context("spawn").Manager().dict()
     mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    print("[dp parity]", dict(ret))
     for r in range(world):
         assert ret.get(r), dict(ret)
         for res in ret[r]:
