@@ -301,6 +301,18 @@ typedef struct {
 } tt_opt_args;
 uint64_t tt_opt_step_workspace(int32_t nchunks);
 int tt_opt_step(const tt_opt_args* a, void* stream);
+/* Allocation-free variant of tt_opt_step.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments and results as tt_opt_step, except that a->workspace / a->workspace_bytes are IGNORED: the scratch
+ * of the gradient-norm pass (one float per chunk) lives in a file-scope `static __device__` array of
+ * TT_OPT_NOALLOC_MAX_CHUNKS floats (64 KiB on every GPU that loads the library, held until the process exits), i.e.
+ * parameter sets of up to TT_OPT_NOALLOC_MAX_CHUNKS chunks (>= 1.07 G elements when tensors fill their chunks).  More
+ * chunks -> TT_ERR_INVALID with a message naming the limit.  The call itself performs no cudaMalloc / cudaFree and calls
+ * no allocating routine; the first call on a device resolves the array's device address (cudaGetSymbolAddress) - make
+ * that first call outside stream capture.  All calls on a device share the array and it keeps the previous call's
+ * contents (none of it needs to start at zero); calls that overlap on the GPU (different streams) race on it. */
+#define TT_OPT_NOALLOC_MAX_CHUNKS 16384
+int tt_opt_step_noalloc(const tt_opt_args* a, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * N1  host input pipeline: text -> token ids.  HOST functions taking HOST pointers - the one exception to

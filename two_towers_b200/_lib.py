@@ -132,6 +132,7 @@ SIGNATURES = {
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),
     "tt_opt_step_workspace": (u64, [i32]),
     "tt_opt_step": (C.c_int, [P, P]),
+    "tt_opt_step_noalloc": (C.c_int, [P, P]),
     "tt_vocab_create": (P, [P, P, i64, P]),
     "tt_vocab_destroy": (None, [P]),
     "tt_vocab_size": (i64, [P]),

@@ -4,6 +4,7 @@
 // HBM-bound elementwise work: 16 B read + 12 B written per parameter (+4 B when the clipped gradient is stored back,
 // as clip_grad_norm_ does in place).  One CTA per (tensor, 64 Ki-element chunk); the chunk list is built once by the
 // host for a parameter set, so the 44 tensors of a two-tower model are one grid instead of 44 x 3 launches.
+#include <mutex>
 #include "common.cuh"
 
 namespace tt {
@@ -184,6 +185,44 @@ int tt_opt_step(const tt_opt_args* a, void* stream) {
                                                        a->step_dev ? a->consts_dev : nullptr, c);
   TT_LAUNCH_CHECK();
   return TT_OK;
+}
+
+// ------------------------------------------------------------------------------------------ allocation-free variant
+// tt_opt_step_noalloc: tt_opt_step with the per-chunk partial sums of the gradient norm (its only scratch memory) held in a
+// file-scope device array instead of a caller-provided workspace - for callers that cannot allocate (code under CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// TT_OPT_NOALLOC_MAX_CHUNKS floats (64 KiB) per GPU that loads the library, held until
+// the process exits.  Every call on a device shares the array: nothing in it has to start at zero (opt_sqnorm_kernel
+// writes partial[c] for every chunk c < nchunks before opt_finish_norm_kernel reads exactly those), but two calls that
+// overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) float g_opt_noalloc_scratch[TT_OPT_NOALLOC_MAX_CHUNKS];
+
+int tt_opt_step_noalloc(const tt_opt_args* a, void* stream) {
+  TT_CHECK_ARG(a != nullptr, "opt_step_noalloc: null args");
+  TT_CHECK_ARG(a->nchunks <= TT_OPT_NOALLOC_MAX_CHUNKS,
+               "opt_step_noalloc: %d chunks exceed the static scratch (TT_OPT_NOALLOC_MAX_CHUNKS = %d chunks of %d elements); "
+               "use tt_opt_step with a caller workspace", a->nchunks, TT_OPT_NOALLOC_MAX_CHUNKS, TT_OPT_CHUNK);
+  // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that
+  // device current (cudaGetSymbolAddress allocates nothing; it returns the address inside the already loaded module).
+  static float* scratch_ptr[64];
+  static std::mutex mu;
+  int dev = 0;
+  TT_CUDA(cudaGetDevice(&dev));
+  TT_CHECK_ARG(dev >= 0 && dev < 64, "opt_step_noalloc: device ordinal %d out of range", dev);
+  float* ptr = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!scratch_ptr[dev]) {
+      float* q = nullptr;
+      TT_CUDA(cudaGetSymbolAddress((void**)&q, g_opt_noalloc_scratch));
+      scratch_ptr[dev] = q;
+    }
+    ptr = scratch_ptr[dev];
+  }
+  tt_opt_args b = *a;
+  b.workspace = ptr;
+  b.workspace_bytes = sizeof(float) * (uint64_t)TT_OPT_NOALLOC_MAX_CHUNKS;
+  return tt_opt_step(&b, stream);
 }
 
 }  // extern "C"
