@@ -45,6 +45,11 @@ uint64_t tt_kernel_launches(void);
 int tt_prof_enable(int32_t on);
 int tt_prof_read(int32_t family, double* total_ms, uint64_t* launches);
 const char* tt_prof_family(int32_t family);
+/* Family 2 broken down by GEMM shape since tt_prof_enable(1): one row per (M, N, K, batched problems, tensor passes,
+ * flags); flags bit 0 A MN-major, bit 1 B MN-major, bits 4.. epilogue kind (0 row-major, 1 tiled, 2 top-k selection),
+ * bit 8 split-K.  Flops of a row = 2 M N K nbatch (x npass issued).  Returns the number of rows written (<= cap). */
+typedef struct { int32_t M, N, K, nbatch, npass, flags; double total_ms; uint64_t launches; } tt_prof_gemm_row;
+int tt_prof_gemm_rows(tt_prof_gemm_row* out, int32_t cap);
 
 /* ---------------------------------------------------------------------------------------------
  * K-A  embedding gather.  Replaces the per-word CPU lookup `self.word2vec[word]` + zero padding

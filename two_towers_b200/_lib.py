@@ -74,6 +74,11 @@ class HeadGrad(C.Structure):
     ]
 
 
+class ProfGemmRow(C.Structure):
+    _fields_ = [("M", i32), ("N", i32), ("K", i32), ("nbatch", i32), ("npass", i32), ("flags", i32),
+                ("total_ms", C.c_double), ("launches", u64)]
+
+
 P = C.c_void_p
 F = C.c_float
 # name -> (restype, argtypes).  Must list EVERY symbol include/tt_b200.h declares (tests check this).
@@ -85,6 +90,7 @@ SIGNATURES = {
     "tt_prof_enable": (C.c_int, [i32]),
     "tt_prof_read": (C.c_int, [i32, C.POINTER(C.c_double), C.POINTER(u64)]),
     "tt_prof_family": (C.c_char_p, [i32]),
+    "tt_prof_gemm_rows": (C.c_int, [C.POINTER(ProfGemmRow), i32]),
     "tt_set_engine": (C.c_int, [i32]),
     "tt_embed_gather": (C.c_int, [P, C.c_int, i64, P, i64, i32, i64, P, P]),
     "tt_gru_layer_fwd_workspace": (u64, [C.POINTER(GruLayer)]),

@@ -14,6 +14,9 @@ unsigned long long launches();
 enum ProfFamily { PROF_GRU_SEQ_FWD = 0, PROF_GRU_SEQ_BWD = 1, PROF_GEMM_TC = 2, PROF_FAMILIES = 3 };
 void prof_begin(int family, cudaStream_t s);
 void prof_end(int family, cudaStream_t s);
+// per-shape table of the GEMM engine (family PROF_GEMM_TC): launches of one (M, N, K, batches, passes, layout, epilogue)
+// share a row; read with tt_prof_gemm_rows
+void prof_begin_gemm(cudaStream_t s, int M, int N, int K, int nbatch, int npass, int flags);
 struct ProfScope {
   int f; cudaStream_t s;
   ProfScope(int family, cudaStream_t stream) : f(family), s(stream) { prof_begin(f, s); }

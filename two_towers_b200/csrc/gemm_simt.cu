@@ -49,10 +49,15 @@ int device_cooperative() {
 struct ProfSlot {
   static constexpr int CAP = 256;
   cudaEvent_t e0[CAP], e1[CAP];
+  int tag[CAP];
   int created = 0, n = 0;
   double ms = 0.0;
   unsigned long long count = 0;
 };
+struct GemmRow { int M, N, K, nbatch, npass, flags; double ms; unsigned long long count; };
+static GemmRow g_gemm_rows[64];
+static int g_gemm_nrows = 0;
+static thread_local int g_gemm_tag = -1;
 static bool g_prof_on = false;
 static ProfSlot g_prof[PROF_FAMILIES];
 static void prof_drain(ProfSlot& p) {
@@ -61,6 +66,10 @@ static void prof_drain(ProfSlot& p) {
     if (cudaEventSynchronize(p.e1[i]) == cudaSuccess && cudaEventElapsedTime(&ms, p.e0[i], p.e1[i]) == cudaSuccess) {
       p.ms += ms;
       ++p.count;
+      if (&p == &g_prof[PROF_GEMM_TC] && p.tag[i] >= 0 && p.tag[i] < g_gemm_nrows) {
+        g_gemm_rows[p.tag[i]].ms += ms;
+        ++g_gemm_rows[p.tag[i]].count;
+      }
     }
   }
   p.n = 0;
@@ -74,7 +83,22 @@ void prof_begin(int family, cudaStream_t s) {
     cudaEventCreate(&p.e1[p.created]);
     ++p.created;
   }
+  p.tag[p.n] = family == PROF_GEMM_TC ? g_gemm_tag : -1;
+  g_gemm_tag = -1;
   cudaEventRecord(p.e0[p.n], s);
+}
+void prof_begin_gemm(cudaStream_t s, int M, int N, int K, int nbatch, int npass, int flags) {
+  if (!g_prof_on) return;
+  int r = 0;
+  for (; r < g_gemm_nrows; ++r) {
+    const GemmRow& g = g_gemm_rows[r];
+    if (g.M == M && g.N == N && g.K == K && g.nbatch == nbatch && g.npass == npass && g.flags == flags) break;
+  }
+  if (r == g_gemm_nrows) {
+    if (g_gemm_nrows == 64) r = -1;
+    else g_gemm_rows[g_gemm_nrows++] = GemmRow{M, N, K, nbatch, npass, flags, 0.0, 0ull};
+  }
+  g_gemm_tag = r;                      // consumed by the prof_begin of the launch that follows on this thread
 }
 void prof_end(int family, cudaStream_t s) {
   if (!g_prof_on) return;
@@ -232,8 +256,19 @@ int tt_set_engine(int32_t mode) {
 const char* tt_last_error(void) { return tt::last_error(); }
 int tt_prof_enable(int32_t on) {
   for (int f = 0; f < tt::PROF_FAMILIES; ++f) { tt::prof_drain(tt::g_prof[f]); tt::g_prof[f].ms = 0.0; tt::g_prof[f].count = 0; }
+  tt::g_gemm_nrows = 0;
   tt::g_prof_on = on != 0;
   return TT_OK;
+}
+int tt_prof_gemm_rows(tt_prof_gemm_row* out, int32_t cap) {
+  tt::prof_drain(tt::g_prof[tt::PROF_GEMM_TC]);
+  int n = 0;
+  for (; n < tt::g_gemm_nrows && n < cap; ++n) {
+    const tt::GemmRow& g = tt::g_gemm_rows[n];
+    out[n].M = g.M; out[n].N = g.N; out[n].K = g.K; out[n].nbatch = g.nbatch; out[n].npass = g.npass; out[n].flags = g.flags;
+    out[n].total_ms = g.ms; out[n].launches = g.count;
+  }
+  return n;
 }
 const char* tt_prof_family(int32_t family) {
   static const char* names[tt::PROF_FAMILIES] = {"gru_seq_kernel (persistent forward recurrence)",

@@ -559,6 +559,7 @@ static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t
   const int cap = (max_ctas > 0 && max_ctas < num_sms && p.epi != 2) ? max_ctas : num_sms;
   const int grid = items < cap ? items : cap;
   note_launch();
+  prof_begin_gemm(s, p.M, p.N, p.K, p.nbatch, NPASS, (A_MN ? 1 : 0) | (B_MN ? 2 : 0) | (p.epi << 4) | (p.splitk > 1 ? 256 : 0));
   ProfScope prof(PROF_GEMM_TC, s);
   kern<<<grid, kThreads, Cfg<BN, NPASS>::SMEM_BYTES, s>>>(p);
   TT_LAUNCH_CHECK();
