@@ -43,7 +43,10 @@ def parse():
     p.add_argument("--optimizer", default="fused", choices=["fused", "torch"],
                    help="fused = this repo's tt_opt_step Adam kernel (FusedAdam); torch = torch.optim.Adam(fused=True)")
     p.add_argument("--serial-towers", action="store_true", help="both towers on one stream (for per-kernel launch lists)")
-    p.add_argument("--eval-queries", type=int, default=8192, help="queries of the retrieval leg (0 = skip it)")
+    p.add_argument("--eval-queries", type=int, default=100_000, help="queries of the retrieval leg (C5: 100 000; 0 = skip it)")
+    p.add_argument("--no-graph", action="store_true", help="eager steps instead of the CUDA-graph captured step")
+    p.add_argument("--no-configs", action="store_true", help="skip the secondary configurations (C1', C2, C3b)")
+    p.add_argument("--no-torch-gpu", action="store_true", help="skip the stock-torch-on-the-GPU arm folded into the line")
     p.add_argument("--eval-docs", type=int, default=1_100_000, help="corpus rows per GPU of the retrieval leg (C5 shard)")
     return p.parse_args()
 
@@ -168,7 +171,7 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------------------- stock torch on the GPU
-def run_torch_gpu(args):
+def torch_gpu_arm(args, steps, warmup):
     """Extra arm (SURVEY 8d "the real beat-it bar"), not part of the driver contract: the reference's architecture
     (enhanced_two_tower.py:14-65: nn.GRU bi x2 + Linear/LayerNorm/ReLU/Linear heads), its in-batch margin loss
     (:90-101) and cosine + topk mining (:123-133) written with STOCK torch modules and run on cuda:0 - cuDNN GRU,
@@ -176,9 +179,8 @@ def run_torch_gpu(args):
     Nothing of this repo's library and nothing under oracle/ is on this path.  One JSON line per cuDNN TF32 setting."""
     import torch.nn as nn
     import torch.nn.functional as F
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
-    dev = torch.device("cuda", 0)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rows = []
     B, V = args.batch, args.vocab
 
     class Stock(nn.Module):
@@ -220,23 +222,34 @@ def run_torch_gpu(args):
             opt.step()
             return loss, hard
 
-        for i in range(args.warmup):
+        for i in range(warmup):
             step(*ids[i % 4])
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()
-        for i in range(args.steps):
+        for i in range(steps):
             loss, _ = step(*ids[i % 4])
         e1.record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / args.steps
-        print(json.dumps({"impl": "torch-gpu", "metric": METRIC, "value": B / (ms * 1e-3), "unit": "pairs/s", "n_gpus": 1,
-                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-                          "dtype": "f32 (cuDNN GRU, allow_tf32=%s; cuBLAS matmul fp32)" % tf32, "data": "synthetic",
-                          "config": workload_config(B, 1, V), "loss": loss.item(),
-                          "note": "stock torch nn.GRU/nn.Linear/LayerNorm/cross_entropy/topk on the GPU; not this repo's kernels"}),
-              flush=True)
+        ms = e0.elapsed_time(e1) / steps
+        rows.append({"impl": "torch-gpu", "metric": METRIC, "value": B / (ms * 1e-3), "unit": "pairs/s", "n_gpus": 1,
+                     "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
+                     "dtype": "f32 (cuDNN GRU, allow_tf32=%s; cuBLAS matmul fp32)" % tf32, "data": "synthetic",
+                     "config": workload_config(B, 1, V), "loss": loss.item(),
+                     "note": "stock torch nn.GRU/nn.Linear/LayerNorm/cross_entropy/topk on the GPU; not this repo's kernels"})
         del model, opt
+    torch.backends.cudnn.allow_tf32 = True
+    del table, ids, eye
+    torch.cuda.empty_cache()
+    return rows
+
+
+def run_torch_gpu(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    torch.cuda.set_device(0)
+    for row in torch_gpu_arm(args, args.steps, args.warmup):
+        print(json.dumps(row), flush=True)
 
 
 # ----------------------------------------------------------------------------------------- this repo's arm
@@ -295,12 +308,68 @@ def kernel_rooflines(lib, steps, B, pk):
     return out, fams
 
 
+def gemm_table(lib, steps, pk):
+    """Per-shape rows of the tcgen05 GEMM engine (family 2) from the same profiled steps: the roofline of the largest family.
+    Flops of a row = 2 M N K x batched problems (algorithmic) and x passes (issued); peak = sustained bf16 (fp16 runs at the
+    same rate)."""
+    from two_towers_b200 import _lib as L
+    buf = (L.ProfGemmRow * 64)()
+    n = lib.tt_prof_gemm_rows(buf, 64)
+    rows = []
+    for r in buf[:n]:
+        if r.launches == 0 or r.total_ms <= 0:
+            continue
+        sec = r.total_ms * 1e-3
+        fl = 2.0 * r.M * r.N * r.K * r.nbatch * r.launches
+        kind = {0: "row-major", 1: "tiled", 2: "top-k selection"}.get((r.flags >> 4) & 15, "?")
+        rows.append({"M": r.M, "N": r.N, "K": r.K, "batched": r.nbatch, "passes": r.npass,
+                     "layout": ("A^T " if r.flags & 1 else "A ") + ("B MN-major" if r.flags & 2 else "B K-major"), "epilogue": kind,
+                     "split_k": bool(r.flags & 256), "launches_per_step": r.launches / steps, "ms_per_step": r.total_ms / steps,
+                     "algorithmic_tflops": fl / sec / 1e12, "issued_tflops": fl * r.npass / sec / 1e12,
+                     "frac_of_bf16_sustained": fl / sec / 1e12 / pk["bf16_sustained"],
+                     "issued_frac_of_bf16_sustained": fl * r.npass / sec / 1e12 / pk["bf16_sustained"]})
+    rows.sort(key=lambda x: -x["ms_per_step"])
+    tot_ms = sum(x["ms_per_step"] for x in rows)
+    tot_fl = sum(x["algorithmic_tflops"] * x["ms_per_step"] for x in rows)
+    tot_is = sum(x["issued_tflops"] * x["ms_per_step"] for x in rows)
+    summary = None
+    if tot_ms > 0:
+        summary = {"bound": "tensor", "kernel": "umma_gemm_kernel (tcgen05 GEMM engine), all shapes of the step",
+                   "achieved": tot_is / tot_ms, "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": tot_is / tot_ms / pk["bf16_sustained"],
+                   "algorithmic_tflops": tot_fl / tot_ms, "algorithmic_frac": tot_fl / tot_ms / pk["bf16_sustained"],
+                   "ms_per_step": tot_ms, "peak_source": f"cuBLAS bf16 sustained, {pk['src']} (MEASURED_PEAKS.json)",
+                   "note": "achieved counts the tensor passes issued (3 per forward product: fp16 hi/lo split for fp32-grade results)"}
+    return rows, summary
+
+
+def eval_cpu_baseline(q, docs, nq=1000):
+    """SURVEY 8d CPU figure for C5: the reference's retrieval semantics (validate_enhanced.py:75-76: cosine_similarity of a
+    query against every doc embedding + topk(10)) batched as q_tile @ docs.T on all host threads, nq queries x one shard."""
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    qc, dc = q[:nq].float().cpu(), docs.float().cpu()
+    t0 = time.perf_counter()
+    dn = torch.nn.functional.normalize(dc, dim=1, eps=1e-8)
+    t_norm = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    out = []
+    for i in range(0, nq, 250):
+        sim = torch.nn.functional.normalize(qc[i:i + 250], dim=1, eps=1e-8) @ dn.t()
+        out.append(sim.topk(10, dim=1).indices)
+    sec = time.perf_counter() - t0
+    return {"value": nq / sec, "unit": "queries/s", "cores": threads, "kind": "port",
+            "sample": f"{nq} queries x {dc.shape[0]} docs (one C5 shard) x {dc.shape[1]}: cosine + topk(10) with stock torch on the "
+                      f"host ({sec * 1e3:.0f} ms; corpus normalisation {t_norm * 1e3:.0f} ms outside, as the reference encodes once)"}, \
+        torch.cat(out)
+
+
 def eval_leg(args, dev, rank, world, group):
-    """SURVEY 8d metric (ii) on a bounded sample of BASELINE configs[4]: score + top-10 + shard merge + MRR@10 over
-    pre-computed embeddings.  Queries replicated, corpus sharded by contiguous global id (1.1 M rows per GPU = the C5
-    shard size); one relevant doc per query planted as normalize(q + 0.5 randn)."""
+    """SURVEY 8d metric (ii), BASELINE configs[4]: score + top-10 + shard merge + MRR@10 over pre-computed embeddings.
+    Q = 100 000 replicated queries (processed in tiles of 8192), corpus sharded by contiguous global id with 1.1 M rows per
+    GPU (the C5 shard size: 8.8 M docs on 8 GPUs); one relevant doc per query planted as normalize(q + 0.5 randn)."""
     import two_towers_b200 as tt
     Q, Nl, D = args.eval_queries, args.eval_docs, HID
+    QT = 8192
     g = torch.Generator(device=dev).manual_seed(4321)
     q = torch.nn.functional.normalize(torch.randn(Q, D, device=dev, generator=g), dim=1)
     gl = torch.Generator(device=dev).manual_seed(99 + rank)
@@ -318,32 +387,56 @@ def eval_leg(args, dev, rank, world, group):
     b0.record()
     index = tt.CorpusIndex(docs, cosine=True, index_base=rank * Nl)
     b1.record()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
 
-    def run():
-        val, idx = tt.sharded_search_topk(q, index, rank * Nl, k=10, group=group)
-        return tt.mrr_recall(idx, rel)
+    def run(timed=False):
+        vals, idxs = [], []
+        if timed:
+            ev[0].record()
+        for i in range(0, Q, QT):                      # local shard scan, query tile by query tile
+            v, ix = tt.search_topk(q[i:i + QT], index, k=10)
+            vals.append(v)
+            idxs.append(ix)
+        val, idx = torch.cat(vals), torch.cat(idxs)
+        if timed:
+            ev[1].record()
+        val, idx = tt.merge_shard_topk(val, idx, group)     # all-gather of the per-shard lists + merge (identity at N = 1)
+        if timed:
+            ev[2].record()
+        m = tt.mrr_recall(idx, rel)
+        if timed:
+            ev[3].record()
+        return m, idx
 
     run()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
-    reps = 3
-    e0.record()
-    for _ in range(reps):
-        m = run()
-    e1.record()
+    m, idx = run(timed=True)
     torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+    parts = torch.tensor([ev[0].elapsed_time(ev[3]), ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3])],
+                         device=dev)
     if world > 1:
         import torch.distributed as dist
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = ms.item()
-    return {"metric": "eval queries/sec (score + top-10 + shard merge + MRR@10)", "value": Q / (ms * 1e-3), "unit": "queries/s",
-            "queries": Q, "docs_per_gpu": Nl, "docs_total": Nl * world, "dim": D, "ms": ms, "mrr10": m["MRR"],
-            "recall10": m["R@10"], "algorithmic_tflops": 2.0 * Q * Nl * world * D / (ms * 1e-3) / 1e12,
-            "index_build_ms": b0.elapsed_time(b1),
-            "note": "bounded sample of BASELINE configs[4] (1e5 queries x 8.8 M docs): same shard size, fewer queries; "
-                    "the corpus index (norms + fp16 hi/lo planes of the shard) is built once outside the timed scans "
-                    "(index_build_ms), as the reference encodes its corpus once"}
+        dist.all_reduce(parts, op=dist.ReduceOp.MAX)
+    ms, ms_scan, ms_merge, ms_mrr = parts.tolist()
+    pk = peaks()
+    tf = 2.0 * Q * Nl * D / (ms_scan * 1e-3) / 1e12            # per GPU: every rank scans its own shard
+    out = {"metric": "eval queries/sec (score + top-10 + shard merge + MRR@10)", "value": Q / (ms * 1e-3), "unit": "queries/s",
+           "queries": Q, "docs_per_gpu": Nl, "docs_total": Nl * world, "dim": D, "ms": ms,
+           "ms_scan": ms_scan, "ms_allgather_merge": ms_merge, "ms_mrr": ms_mrr, "query_tile": QT,
+           "mrr10": m["MRR"], "recall10": m["R@10"], "index_build_ms": b0.elapsed_time(b1),
+           "roofline": {"bound": "tensor", "kernel": "umma_gemm_kernel selection epilogue (fused score + top-k candidates)",
+                        "achieved": tf * 2, "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": tf * 2 / pk["bf16_sustained"],
+                        "algorithmic_tflops": tf, "algorithmic_frac": tf / pk["bf16_sustained"], "passes": 2,
+                        "peak_source": f"cuBLAS bf16 sustained, {pk['src']}; the scan time includes the exact fp32 re-score of the "
+                                       "candidates and the list merge (the GEMM kernel alone is faster)"},
+           "note": "BASELINE configs[4] shape per GPU: 100 000 queries against a 1.1 M-doc shard (8.8 M docs on 8 GPUs); the corpus "
+                   "index (norms + fp16 hi/lo planes of the shard) is built once outside the timed scan (index_build_ms), as the "
+                   "reference encodes its corpus once"}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb, cpu_idx = eval_cpu_baseline(q, docs)
+        out["cpu_baseline"] = cb
+        out["cpu_sample_index_agreement"] = (idx[:cpu_idx.shape[0]].cpu() == cpu_idx).float().mean().item()
+    return out
 
 
 def run_ours(args):

@@ -12,6 +12,6 @@ from .models import (EnhancedTwoTower, EnhancedTwoTowerModel, SimpleTwoTower, To
 from .optim import FusedAdam, FusedAdamW, load_checkpoint, save_checkpoint  # noqa: F401
 from .pipeline import PinnedIdRing, Vocabulary, id_batches  # noqa: F401
 from .retrieval import (CorpusIndex, SearchService, compute_mrr, encode_corpus, first_relevant_rank, load_doc_embeddings, load_or_compute_doc_embeddings,  # noqa: F401
-                        mrr_recall, save_doc_embeddings, search_topk, sharded_search_topk)
+                        merge_shard_topk, mrr_recall, save_doc_embeddings, search_topk, sharded_search_topk)
 
 __version__ = "0.1.0"

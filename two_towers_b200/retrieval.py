@@ -50,12 +50,9 @@ def search_topk(query_vecs, doc_encodings, k=10, cosine=True, index_base=0):
 
 
 @torch.no_grad()
-def sharded_search_topk(query_vecs, local_docs, index_base, k=10, group=None, cosine=True):
-    """Every rank holds a contiguous corpus shard starting at global id `index_base`; queries are replicated.
-    Returns the identical global top-k on every rank."""
-    if isinstance(local_docs, CorpusIndex) and local_docs.index_base != int(index_base):
-        raise ValueError("sharded_search_topk: index_base differs from the CorpusIndex's")
-    val, idx = search_topk(query_vecs, local_docs, k, cosine, index_base)
+def merge_shard_topk(val, idx, group=None):
+    """Per-shard top-k lists (global doc ids) of every rank -> the identical global top-k on every rank: all-gather of the
+    [Q,k] lists + K-I merge (score desc, lowest global id on ties)."""
     W = dist_ops.world_size(group)
     if W == 1:
         return val, idx
@@ -64,6 +61,15 @@ def sharded_search_topk(query_vecs, local_docs, index_base, k=10, group=None, co
     dist.all_gather_into_tensor(vals, val.contiguous(), group=group)
     dist.all_gather_into_tensor(idxs, idx.contiguous(), group=group)
     return Fn.topk_merge(vals, idxs)
+
+
+def sharded_search_topk(query_vecs, local_docs, index_base, k=10, group=None, cosine=True):
+    """Every rank holds a contiguous corpus shard starting at global id `index_base`; queries are replicated.
+    Returns the identical global top-k on every rank."""
+    if isinstance(local_docs, CorpusIndex) and local_docs.index_base != int(index_base):
+        raise ValueError("sharded_search_topk: index_base differs from the CorpusIndex's")
+    val, idx = search_topk(query_vecs, local_docs, k, cosine, index_base)
+    return merge_shard_topk(val, idx, group)
 
 
 @torch.no_grad()
