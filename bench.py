@@ -439,6 +439,84 @@ def eval_leg(args, dev, rank, world, group):
     return out
 
 
+def secondary_configs(args, dev, table, graphed):
+    """The other train configurations of BASELINE.json / SURVEY section 8 as short measured lines beside the C3 headline
+    (same timing rules: resident ids, CUDA events, warm-up, 4 rotating id batches; whole step incl. the optimizer):
+      C1'  SimpleTwoTower(300,128), B = 256, Tq/Td 32/32, symmetric InfoNCE(0.1), AdamW + clip 1.0 (simple_two_tower.py:175-243)
+      C2   TwoTowerModel(300,256), B = 1024, Tq/Td 32/128, MarginRankingLoss in-batch and InfoNCELoss(0.1), Adam + clip
+           (margin_two_tower.py:9-85, train_margin.py:62-67,111-123)
+      C3b  EnhancedTwoTowerModel(300,512) - the reference default hidden_dim (train_enhanced.py:30) - B = 4096, Tq/Td 32/128"""
+    import two_towers_b200 as tt
+    from two_towers_b200 import simple_two_tower as S
+    pk = peaks()
+    small = torch.empty(13085, E, device=dev).normal_(0, 0.1, generator=torch.Generator(device=dev).manual_seed(8))
+    small[0] = 0
+    cases = [
+        ("c1_simple", lambda: tt.SimpleTwoTower(E, 128), lambda: S.InfoNCELoss(0.1), 256, 32, 32, 128, small,
+         lambda ps, c: tt.FusedAdamW(ps, lr=1e-4, weight_decay=0.01, max_grad_norm=1.0, capturable=c), 20, 0),
+        ("c2_margin_ce", lambda: tt.TwoTowerModel(E, 256), lambda: tt.MarginRankingLoss(0.2, 0.1), 1024, 32, 128, 256, table,
+         lambda ps, c: tt.FusedAdam(ps, lr=1e-4, max_grad_norm=1.0, capturable=c), 10, 0),
+        ("c2_infonce", lambda: tt.TwoTowerModel(E, 256), lambda: tt.InfoNCELoss(0.1), 1024, 32, 128, 256, table,
+         lambda ps, c: tt.FusedAdam(ps, lr=1e-4, max_grad_norm=1.0, capturable=c), 10, 0),
+        ("c3b_enhanced_h512", lambda: tt.EnhancedTwoTowerModel(E, 512), lambda: tt.MarginRankingLoss(0.2, 0.1), 4096, 32, 128, 1024, table,
+         lambda ps, c: tt.FusedAdam(ps, capturable=c), 3, TOPK),
+    ]
+    out = []
+    for name, mk, mkloss, B, Tq, Td, Hg, tab, mkopt, steps, mine_k in cases:
+        row = {"name": name, "batch": B, "query_len": Tq, "doc_len": Td, "gru_hidden": Hg, "steps": steps}
+        try:
+            torch.manual_seed(0)
+            model = mk().to(dev).train()
+            model.attach_embeddings(tab, pad_id=0)
+            crit = mkloss()
+            gen = torch.Generator().manual_seed(4321)
+            V = tab.shape[0]
+            ids = [(make_ids(B, Tq, V, gen).to(dev), make_ids(B, Td, V, gen).to(dev)) for _ in range(4)]
+            results = {}
+            for mode in (["graph", "eager"] if graphed else ["eager"]):
+                opt = mkopt(model.parameters(), mode == "graph")
+                if mode == "graph":
+                    step = tt.GraphedTrainStep(model, crit, opt, mine_k=mine_k)
+                else:
+                    def step(q, d, opt=opt):
+                        opt.zero_grad(set_to_none=True)
+                        qv, dv = model(q, d)
+                        loss = crit(qv, dv)
+                        loss.backward()
+                        opt.step()
+                        if mine_k:
+                            tt.get_hard_negatives_batch(qv.detach(), dv.detach(), k=mine_k)
+                        return loss, None
+                for i in range(3):
+                    step(*ids[i % 4])
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                th = time.perf_counter()
+                for i in range(steps):
+                    loss, _ = step(*ids[i % 4])
+                host_ms = (time.perf_counter() - th) * 1e3 / steps
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / steps
+                results[mode] = {"ms_per_step": ms, "pairs_per_s": B / (ms * 1e-3), "host_queue_ms_per_step": host_ms,
+                                 "loss": float(loss.detach())}
+                if mode == "graph":
+                    results[mode]["launches_per_replay"] = step.launches_per_replay(*ids[0])
+                del opt, step
+            best = min(results.values(), key=lambda r: r["ms_per_step"])
+            flops = 3.0 * 12 * Hg * (E + 4 * Hg) * (Tq + Td)
+            row.update({"value": best["pairs_per_s"], "unit": "pairs/s", "ms_per_step": best["ms_per_step"], "modes": results,
+                        "gflop_per_pair": flops / 1e9,
+                        "step_frac_of_bf16_sustained": flops * best["pairs_per_s"] / 1e12 / pk["bf16_sustained"]})
+            del model, crit, ids
+        except Exception as exc:                                   # e.g. out of memory for C3b: reported, not fatal
+            row["error"] = repr(exc)[:300]
+        torch.cuda.empty_cache()
+        out.append(row)
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     import two_towers_b200 as tt
@@ -470,14 +548,16 @@ def run_ours(args):
     if os.environ.get("TT_BWD_SEGMENTS"):
         lib.tt_debug_bwd_segments(int(os.environ["TT_BWD_SEGMENTS"]))
     crit = tt.MarginRankingLoss(margin=0.2, temperature=0.1, group=group)
-    opt = tt.FusedAdam(model.parameters()) if args.optimizer == "fused" else torch.optim.Adam(model.parameters(), fused=True)
-    reducer = dops.GradientAllReducer(model.parameters(), group) if world > 1 else None
+    graphed = (not args.no_graph) and args.optimizer == "fused"
+    opt = tt.FusedAdam(model.parameters(), capturable=graphed) if args.optimizer == "fused" else \
+        torch.optim.Adam(model.parameters(), fused=True)
+    reducer = dops.GradientAllReducer(None, group, named_params=model.named_parameters()) if world > 1 else None
     nb = 4
     host = [(make_ids(B, TQ, V, gen).pin_memory(), make_ids(B, TD, V, gen).pin_memory()) for _ in range(nb)]
     resident = [(q.to(dev), d.to(dev)) for q, d in host]
     resident_shape = host[0]
 
-    def step(q, d):
+    def eager_step(q, d):
         opt.zero_grad(set_to_none=True)
         qv, dv = model(q, d)
         loss = crit(qv, dv)
@@ -488,6 +568,14 @@ def run_ours(args):
             reducer.finish()
         opt.step()
         return loss, hard
+
+    # The whole step (zero_grad, both towers, loss, backward, gradient all-reduce, clip-free Adam, hard-negative mining) as ONE
+    # CUDA graph: captured on the first call, replayed afterwards (two_towers_b200/graph.py).  --no-graph keeps the eager loop.
+    gstep = None
+    if graphed:
+        gstep = tt.GraphedTrainStep(model, crit, opt, reducer=reducer, mine_k=TOPK, pos_offset=rank * B,
+                                    docs_fn=(lambda x: dops.all_gather_rows(x, group)) if world > 1 else None)
+    step = gstep if graphed else eager_step
 
     def barrier():
         if world > 1:
@@ -512,19 +600,22 @@ def run_ours(args):
     e1.record(st)
     barrier()
     launches = int(lib.tt_kernel_launches() - k0)
+    if graphed:
+        launches = int(gstep.launches_per_replay(*resident[0]) or 0) * args.steps      # replays do not pass through the host counter
     sampler.mark_end()
     clocks = sampler.stop()
     # ---- dominant-kernel timing: the same K steps again with the towers on ONE stream (kernel durations under
     # two-stream overlap would include time-slicing with the other tower), CUDA events around every launch
     model.overlap_towers = False
     lib.tt_debug_wgrad_overlap(0)
-    step(*resident[0])
+    eager_step(*resident[0])
     barrier()
     lib.tt_prof_enable(1)
     for i in range(args.steps):
-        step(*resident[i % nb])
+        eager_step(*resident[i % nb])
     barrier()
     roofs, fams = kernel_rooflines(lib, args.steps, B, peaks())
+    gemm_rows, gemm_roof = gemm_table(lib, args.steps, peaks())
     lib.tt_prof_enable(0)
     lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
     model.overlap_towers = not args.serial_towers
@@ -617,13 +708,41 @@ def run_ours(args):
             "step_frac_of_bf16_sustained": FLOPS_PER_PAIR * B / (ms_step * 1e-3) / 1e12 / pk["bf16_sustained"],
         }
         line["roofline"] = roofs[0] if roofs else None
-        line["kernels"] = roofs[1:] + [f for f in fams[2:]]
+        line["kernels"] = roofs[1:] + ([gemm_roof] if gemm_roof else [f for f in fams[2:]])
+        line["gemm_table"] = gemm_rows
+        line["graph"] = {"captured": bool(graphed), "launches_per_replay": (gstep.launches_per_replay(*resident[0]) if graphed else None),
+                         "note": "host_queue_ms_per_step is the host time to queue one step: input copies + one cudaGraphLaunch when "
+                                 "captured, every kernel launch through Python/ctypes otherwise (--no-graph)"}
+    # ---- parity self-check on this very process group (small shapes, ~1 s): the sharded step - eager and captured in a CUDA
+    # graph, NCCL included - against one process on the concatenated batch: loss, every gradient, mined indices
+    from two_towers_b200.selfcheck import dp_parity_check
+    try:
+        pc = dp_parity_check(group, dev, graphed=graphed)
+        parity = {"status": "ok" if pc["ok"] else "MISMATCH", "world": world, "loss_rel": pc["loss_rel"],
+                  "worst_grad_rel": pc["worst_grad"][1], "worst_grad": pc["worst_grad"][0], "indices_equal": pc["indices_equal"],
+                  "graphed_weight_rel": pc.get("graphed_weight_rel"),
+                  "what": "data-parallel step vs single process on the concatenated batch (two_towers_b200/selfcheck.py)"}
+    except Exception as exc:                                  # a failing check must not hide the measurement; it is reported
+        parity = {"status": "ERROR", "error": repr(exc)[:300]}
+    if rank == 0:
+        line["parity_check"] = parity
     del resident[:], host[:]
-    del model, opt, table
+    del model, opt, gstep, step, eager_step, reducer
+    torch.cuda.empty_cache()
+    if rank == 0 and world == 1 and not args.no_configs:
+        line["configs"] = secondary_configs(args, dev, table, graphed)
+    del table
     torch.cuda.empty_cache()
     ev = eval_leg(args, dev, rank, world, group) if args.eval_queries > 0 else None
     if rank == 0:
         line["eval"] = ev
+        if world == 1 and not args.no_torch_gpu:
+            try:
+                rows = torch_gpu_arm(args, 5, 3)
+                line["torch_gpu_baseline"] = [{"value": r["value"], "unit": "pairs/s", "ms_per_step": r["ms_per_step"], "dtype": r["dtype"],
+                                               "ratio_ours_over_it": value / r["value"]} for r in rows]
+            except Exception as exc:
+                line["torch_gpu_baseline"] = {"error": repr(exc)[:300]}
         if world == 1 and not args.no_cpu_baseline:
             val, ms, threads = cpu_reference(3, 1, args.cpu_batch)
             line["cpu_baseline"] = {"value": val, "unit": "pairs/s", "cores": threads, "kind": "port",
