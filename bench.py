@@ -255,16 +255,16 @@ def run_torch_gpu(args):
 # ----------------------------------------------------------------------------------------- this repo's arm
 def seq_kernel_work(B):
     """Algorithmic work of the persistent recurrence kernels per train step (both towers, 2 layers, 2 directions);
-    DESIGN.md section 5.  Per (token, direction, layer), Hg = 256:
-      forward  gru_seq_kernel     reads gi fp32 [3Hg] (12 Hg B); writes the saved gates r,z,n,q as 4 x 16 bit (8 Hg B),
-                                  hn fp32 (4 Hg B) and h_t as fp16 hi+lo planes (4 Hg B)            -> 28 Hg B
-      backward gru_bwd_seq_kernel reads the saved gates + hn (12 Hg B) [+ dL/dout fp32 4 Hg B, counted];
-                                  writes the dG fp16 planes dr|dz|dn*r|dn (8 Hg B)                  -> 24 Hg B
+    DESIGN.md section 4.  Per (token, direction, layer), Hg = 256:
+      forward  gru_seq_kernel     reads gi fp32 [3Hg] (12 Hg B); writes the five 16-bit gate-record planes z, r, A, C, B
+                                  (10 Hg B) and h_t as fp16 hi+lo planes (4 Hg B)                    -> 26 Hg B
+      backward gru_bwd_seq_kernel reads the gate records (10 Hg B) [+ dL/dout fp32 4 Hg B, counted];
+                                  writes the dG fp16 planes dr|dz|dn*r|dn (8 Hg B)                  -> 22 Hg B
       flops (either)              one [1 x Hg] x [Hg x 3Hg] recurrent product = 6 Hg^2 (one fp32-equivalent pass;
                                   the forward issues 3 fp16 tensor passes of it, the backward 1)."""
     units = B * (TQ + TD) * 2 * 2
-    return {0: dict(bytes=units * 28 * GRU_H, flops=units * 6 * GRU_H * GRU_H, passes=3),
-            1: dict(bytes=units * 24 * GRU_H, flops=units * 6 * GRU_H * GRU_H, passes=1)}
+    return {0: dict(bytes=units * 26 * GRU_H, flops=units * 6 * GRU_H * GRU_H, passes=3),
+            1: dict(bytes=units * 22 * GRU_H, flops=units * 6 * GRU_H * GRU_H, passes=1)}
 
 
 def kernel_rooflines(lib, steps, B, pk):

@@ -94,6 +94,87 @@ __device__ __forceinline__ float dq_s16(uint32_t v, float inv_scale) {
 }
 constexpr float kNScale = 32767.f, kQScale = 16383.5f;
 
+// ---- saved gate records (what the BPTT needs of a forward step), five 16-bit planes of 8 units per 16-byte word:
+//   Z = z, R = r                       u16, x 65535
+//   A = (1 - z)(1 - n^2)               u16, x 65535          dn_pre       = dh * A
+//   C = (h_t - n)(1 - z)               s16, x 65000 (|C| <= 1/2: h_t - n = z (h_prev - n))    dz_pre = dh * C
+//   B = (h W_hn + b_hn) r (1 - r)      fp16                   dr_pre       = dn_pre * B
+// Everything that does not depend on the running gradient is formed ONCE, in the forward epilogue (which has the
+// operands in registers), instead of per BPTT step from r, z, n, q and an fp32 hn plane: the BPTT kernel runs on one CTA
+// per (row tile, direction) and is bound by the instructions of its gate-gradient loop (40 -> ~25 per unit), and the
+// saved state shrinks from 12 H to 10 H bytes per (token, direction).  Padded steps / pad rows store z = 1 and zeros:
+// the gradient passes through and every gate gradient is zero without any masking in the BPTT.
+// Word index of (dir, t, row tile mt, unit group u8 = unit / 8, row): ((((dir T + t) MT + mt) H/8 + u8) 128 + row); plane
+// k starts k * g16_plane words further on.
+enum { GP_Z = 0, GP_R = 1, GP_A = 2, GP_C = 3, GP_B = 4, GP_PLANES = 5 };
+constexpr float kCScale = 65000.f;
+// quantisers without clamps (the value ranges are guaranteed by construction); the result's LOW 16 bits are the code
+__device__ __forceinline__ uint32_t qf_u16(float x) { return __float_as_uint(fmaf(x, 65535.f, 8388608.f)); }
+__device__ __forceinline__ uint32_t qf_s16(float x, float scale) { return __float_as_uint(fmaf(x, scale, 8388608.f + 32768.f)); }
+__device__ __forceinline__ uint32_t pk_lo16(uint32_t a, uint32_t b) { return __byte_perm(a, b, 0x5410); }   // a.lo16 | b.lo16 << 16
+// code in the low (HALF = 0) / high (HALF = 1) 16 bits of w -> float, one PRMT + one FFMA
+template <int HALF> __device__ __forceinline__ float dqf_u16(uint32_t w) {
+  constexpr float c = 1.f / 65535.f;
+  return fmaf(__uint_as_float(__byte_perm(w, 0x4B000000u, HALF ? 0x7632 : 0x7610)), c, -8388608.f * c);
+}
+template <int HALF> __device__ __forceinline__ float dqf_s16(uint32_t w, float inv_scale) {
+  return fmaf(__uint_as_float(__byte_perm(w, 0x4B000000u, HALF ? 0x7632 : 0x7610)), inv_scale, -(8388608.f + 32768.f) * inv_scale);
+}
+// forward: records of 8 consecutive units of one row.  dst = plane-Z word of (.., u8, row).
+__device__ __forceinline__ void store_rec8(uint4* __restrict__ dst, int64_t plane, const float (&r)[8], const float (&z)[8],
+                                           const float (&n)[8], const float (&q)[8], const float (&hn)[8]) {
+  uint32_t cz[8], cr[8], ca[8], cc[8];
+  float bv[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float omz = 1.f - z[j];
+    cz[j] = qf_u16(z[j]);
+    cr[j] = qf_u16(r[j]);
+    ca[j] = qf_u16(omz * fmaf(-n[j], n[j], 1.f));
+    cc[j] = qf_s16(q[j] * omz, kCScale);
+    const float t = fmaf(-r[j], r[j], r[j]);                       // r (1 - r)
+    bv[j] = hn[j] * t;
+  }
+  dst[GP_Z * plane] = make_uint4(pk_lo16(cz[0], cz[1]), pk_lo16(cz[2], cz[3]), pk_lo16(cz[4], cz[5]), pk_lo16(cz[6], cz[7]));
+  dst[GP_R * plane] = make_uint4(pk_lo16(cr[0], cr[1]), pk_lo16(cr[2], cr[3]), pk_lo16(cr[4], cr[5]), pk_lo16(cr[6], cr[7]));
+  dst[GP_A * plane] = make_uint4(pk_lo16(ca[0], ca[1]), pk_lo16(ca[2], ca[3]), pk_lo16(ca[4], ca[5]), pk_lo16(ca[6], ca[7]));
+  dst[GP_C * plane] = make_uint4(pk_lo16(cc[0], cc[1]), pk_lo16(cc[2], cc[3]), pk_lo16(cc[4], cc[5]), pk_lo16(cc[6], cc[7]));
+  dst[GP_B * plane] = make_uint4(pack_h2(bv[0], bv[1]), pack_h2(bv[2], bv[3]), pack_h2(bv[4], bv[5]), pack_h2(bv[6], bv[7]));
+}
+// backward: the four planes the gate gradients of 8 units need (Z is consumed separately, by the dh * z pass)
+struct GateRec8 { uint4 r, a, c, b; };
+__device__ __forceinline__ void load_rec8(GateRec8& g, const uint4* __restrict__ src, int64_t plane) {
+  g.r = __ldg(src + GP_R * plane);
+  g.a = __ldg(src + GP_A * plane);
+  g.c = __ldg(src + GP_C * plane);
+  g.b = __ldg(src + GP_B * plane);
+}
+// gate gradients of 8 units from dL/dh: packed fp16 (dr | dz | dn*r | dn), 16 bytes each
+__device__ __forceinline__ void grad_rec8(const GateRec8& g, const float (&dh)[8], uint4& o_dr, uint4& o_dz, uint4& o_dnr, uint4& o_dn) {
+  const uint32_t rw[4] = {g.r.x, g.r.y, g.r.z, g.r.w}, aw[4] = {g.a.x, g.a.y, g.a.z, g.a.w};
+  const uint32_t cw[4] = {g.c.x, g.c.y, g.c.z, g.c.w}, bw[4] = {g.b.x, g.b.y, g.b.z, g.b.w};
+  uint32_t pr[4], pz[4], pnr[4], pn[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 bb = __half22float2(*reinterpret_cast<const __half2*>(&bw[i]));
+    const float dn0 = dh[2 * i] * dqf_u16<0>(aw[i]), dn1 = dh[2 * i + 1] * dqf_u16<1>(aw[i]);
+    pn[i] = pack_h2(dn0, dn1);
+    pnr[i] = pack_h2(dn0 * dqf_u16<0>(rw[i]), dn1 * dqf_u16<1>(rw[i]));
+    pr[i] = pack_h2(dn0 * bb.x, dn1 * bb.y);
+    pz[i] = pack_h2(dh[2 * i] * dqf_s16<0>(cw[i], 1.f / kCScale), dh[2 * i + 1] * dqf_s16<1>(cw[i], 1.f / kCScale));
+  }
+  o_dr = make_uint4(pr[0], pr[1], pr[2], pr[3]);
+  o_dz = make_uint4(pz[0], pz[1], pz[2], pz[3]);
+  o_dnr = make_uint4(pnr[0], pnr[1], pnr[2], pnr[3]);
+  o_dn = make_uint4(pn[0], pn[1], pn[2], pn[3]);
+}
+// dh[0..7] *= z of 8 units (one Z word)
+__device__ __forceinline__ void mul_z8(float* dh, const uint4& zw) {
+  const uint32_t w[4] = {zw.x, zw.y, zw.z, zw.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { dh[2 * i] *= dqf_u16<0>(w[i]); dh[2 * i + 1] *= dqf_u16<1>(w[i]); }
+}
+
 // ------------------------------------------------------------------------------------------ operand producers
 // x fp32 [B,T,In] (batch-first) -> fp16 hi/lo planes [T][Bp][Kp] (time-major); pad rows / pad columns are zero.
 __global__ void x_planes_kernel(const float* __restrict__ x, int B, int Bp, int T, int In, int Kp, f16* __restrict__ hi,
@@ -185,9 +266,9 @@ struct alignas(64) Step2Params {
   CUtensorMap x_hi, x_lo;            // next layer's input planes [T*Bp][ndir*H], box 64 x 128 (store)
   const float* gi;                   // tiled [ndir][T][MT][3][H/4][128][4], biases folded
   const float* b_hh[2];              // only the n-gate third is read
-  uint4* g16;                        // saved gates or null: plane A [ndir][T][MT][H/4][128] x (r0..3, z0..3 as u16), then
-  int64_t g16_plane;                 // plane B (n0..3, q0..3 as s16) g16_plane uint4 further on (each plane contiguous per row)
-  float* hn;                         // saved h W_hn^T + b_hn, tiled [ndir][T][MT][H/4][128][4] or null
+  uint4* g16;                        // saved gate records or null: GP_PLANES planes [ndir][T][MT][H/8][128] of 16-byte words
+  int64_t g16_plane;                 // words per plane (see store_rec8)
+  float* hn;                         // unused (the records carry hn r (1 - r))
   float* out;                        // fp32 [B,T,ndir*H] or null
   float* h_n;                        // fp32 [ndir][B][H] (written at the last step)
   const int32_t* lengths;
@@ -305,7 +386,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
       const int e = threadIdx.x - 64;
       if (e < S_UN) bhn_s[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
     }
-    const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
+    const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + (uh >> 3)) * 128 + row;
     // 4 x 16 KB staging tiles in the operand stage that does NOT hold the own A tile (free once tfull has fired)
     uint8_t* stg = smem + (own_stage == 0 ? S_STAGE : 0);
     const uint8_t* own_hi = smem + own_stage * S_STAGE, *own_lo = own_hi + S_A_BYTES;
@@ -360,22 +441,7 @@ __global__ void __launch_bounds__(S_THREADS, 1) gru_step2_kernel(const __grid_co
           xo[j] = 0.f;
         }
       }
-      if (p.g16) {
-#pragma unroll
-        for (int g4 = 0; g4 < 2; ++g4) {
-          const int o = 4 * g4;
-          uint4 a, bq;
-          a.x = q_u16(r[o]) | (q_u16(r[o + 1]) << 16); a.y = q_u16(r[o + 2]) | (q_u16(r[o + 3]) << 16);
-          a.z = q_u16(z[o]) | (q_u16(z[o + 1]) << 16); a.w = q_u16(z[o + 2]) | (q_u16(z[o + 3]) << 16);
-          bq.x = q_s16(n[o], kNScale) | (q_s16(n[o + 1], kNScale) << 16);
-          bq.y = q_s16(n[o + 2], kNScale) | (q_s16(n[o + 3], kNScale) << 16);
-          bq.z = q_s16(q[o], kQScale) | (q_s16(q[o + 1], kQScale) << 16);
-          bq.w = q_s16(q[o + 2], kQScale) | (q_s16(q[o + 3], kQScale) << 16);
-          const int64_t gidx = gbase + (int64_t)(2 * c + g4) * 128;
-          p.g16[gidx] = a; p.g16[p.g16_plane + gidx] = bq;
-          reinterpret_cast<float4*>(p.hn)[gbase + (int64_t)(2 * c + g4) * 128] = make_float4(hn[o], hn[o + 1], hn[o + 2], hn[o + 3]);
-        }
-      }
+      if (p.g16) store_rec8(p.g16 + gbase + (int64_t)c * 128, p.g16_plane, r, z, n, q, hn);
       // operand planes of h_t (next step's A tile, backward's h_prev) -> swizzled staging tiles
       {
         uint4 hi, lo;
@@ -650,7 +716,7 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
         }
         float* bh = bhn_s + (item & 1) * S_UN;
         if (!bhn_once && e < S_UN) bh[e] = __ldg(p.b_hh[dir] + 2 * H + u0 + e);
-        const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
+        const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + (uh >> 3)) * 128 + row;
         // ring position of the own A tile (last k-block of this item)
         const int own_pos = (item + 1) * KB - 1, own_stage = own_pos % S_STAGES;
         const uint8_t* own_hi = smem + own_stage * S_STAGE, *own_lo = own_hi + S_A_BYTES;
@@ -714,22 +780,7 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
               xo[j] = 0.f;
             }
           }
-          if (p.g16) {
-#pragma unroll
-            for (int g4 = 0; g4 < 2; ++g4) {
-              const int o = 4 * g4;
-              uint4 a, bq;
-              a.x = q_u16(r[o]) | (q_u16(r[o + 1]) << 16); a.y = q_u16(r[o + 2]) | (q_u16(r[o + 3]) << 16);
-              a.z = q_u16(z[o]) | (q_u16(z[o + 1]) << 16); a.w = q_u16(z[o + 2]) | (q_u16(z[o + 3]) << 16);
-              bq.x = q_s16(n[o], kNScale) | (q_s16(n[o + 1], kNScale) << 16);
-              bq.y = q_s16(n[o + 2], kNScale) | (q_s16(n[o + 3], kNScale) << 16);
-              bq.z = q_s16(q[o], kQScale) | (q_s16(q[o + 1], kQScale) << 16);
-              bq.w = q_s16(q[o + 2], kQScale) | (q_s16(q[o + 3], kQScale) << 16);
-              const int64_t gidx = gbase + (int64_t)(2 * c + g4) * 128;
-              p.g16[gidx] = a; p.g16[p.g16_plane + gidx] = bq;
-              reinterpret_cast<float4*>(p.hn)[gbase + (int64_t)(2 * c + g4) * 128] = make_float4(hn[o], hn[o + 1], hn[o + 2], hn[o + 3]);
-            }
-          }
+          if (p.g16) store_rec8(p.g16 + gbase + (int64_t)c * 128, p.g16_plane, r, z, n, q, hn);
           {
             const uint32_t off = sw128_off(row, NCH * sub + c);
             uint4 hi, lo;
@@ -808,27 +859,32 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
   const int uh = u0 + 16 * qtr;
   const bool row_ok = b < p.B;
   const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
-  const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * h4 + (uh >> 2)) * 128 + row;
+  const int64_t gbase = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + (uh >> 3)) * 128 + row;
   float4* dhs = reinterpret_cast<float4*>(p.dhs) + (((int64_t)dir * MT + mt) * h4 + (uh >> 2)) * 128 + row;
   const float4* dab = p.d_above ? reinterpret_cast<const float4*>(p.d_above) +
                                       (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H + uh) >> 2)) * 128 + row
                                 : nullptr;
-  float dr[16], dz[16], dnr[16], dn[16];
-  if (live) {
-    // all loads of the 4 unit groups first (independent addresses -> one memory round trip)
-    uint4 ga[4], gb[4];
-    float4 hn4[4], dh4[4], da4[4];
+  // records of padded steps / pad rows hold z = 1 and zeros (store_rec8): no masking needed, except that the upstream
+  // gradient of a padded step's (all-zero) output must not enter dh
+  GateRec8 g[2];
+  uint4 zw[2];
+  float4 dh4[4], da4[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      ga[i] = __ldg(p.g16 + gbase + (int64_t)i * 128);
-      gb[i] = __ldg(p.g16 + p.g16_plane + gbase + (int64_t)i * 128);
-      hn4[i] = __ldg(reinterpret_cast<const float4*>(p.hn) + gbase + (int64_t)i * 128);
-      dh4[i] = dhs[i * 128];
-      da4[i] = dab ? __ldg(dab + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+  for (int hf = 0; hf < 2; ++hf) {
+    load_rec8(g[hf], p.g16 + gbase + (int64_t)hf * 128, p.g16_plane);
+    zw[hf] = __ldg(p.g16 + GP_Z * p.g16_plane + gbase + (int64_t)hf * 128);
+  }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int o = 4 * i;
+  for (int i = 0; i < 4; ++i) {
+    dh4[i] = dhs[i * 128];
+    da4[i] = (dab && live) ? __ldg(dab + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int hf = 0; hf < 2; ++hf) {
+    float dh[8];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int i = 2 * hf + k;
       float4 da = da4[i];
       if (dab && p.drop_p > 0.f) {
         const uint64_t e = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + uh + 4 * i);
@@ -837,36 +893,18 @@ __global__ void __launch_bounds__(512) cell_bwd2_kernel(const __grid_constant__ 
         const int o8 = (i & 1) * 4;
         da.x *= s8[o8]; da.y *= s8[o8 + 1]; da.z *= s8[o8 + 2]; da.w *= s8[o8 + 3];
       }
-      const float dh[4] = {dh4[i].x + da.x, dh4[i].y + da.y, dh4[i].z + da.z, dh4[i].w + da.w};
-      const float hnv[4] = {hn4[i].x, hn4[i].y, hn4[i].z, hn4[i].w};
-      const uint32_t rw[2] = {ga[i].x, ga[i].y}, zw[2] = {ga[i].z, ga[i].w}, nw[2] = {gb[i].x, gb[i].y}, qw[2] = {gb[i].z, gb[i].w};
-      float nd[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int sh = (j & 1) * 16;
-        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw[j >> 1] >> sh);
-        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);
-        const float dn_pre = dh[j] * (1.f - z) * (1.f - n * n);
-        dn[o + j] = dn_pre;
-        dnr[o + j] = dn_pre * r;
-        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);
-        dz[o + j] = dh[j] * q * (1.f - z);            // == dh (h_prev - n) z (1 - z) with q = h_t - n = z (h_prev - n)
-        nd[j] = dh[j] * z;
-      }
-      dhs[i * 128] = make_float4(nd[0], nd[1], nd[2], nd[3]);
+      dh[4 * k] = dh4[i].x + da.x; dh[4 * k + 1] = dh4[i].y + da.y; dh[4 * k + 2] = dh4[i].z + da.z; dh[4 * k + 3] = dh4[i].w + da.w;
     }
-  } else {
-#pragma unroll
-    for (int j = 0; j < 16; ++j) { dr[j] = 0.f; dz[j] = 0.f; dnr[j] = 0.f; dn[j] = 0.f; }
-  }
-#pragma unroll
-  for (int cc = 0; cc < 2; ++cc) {
-    const int o = 8 * cc;
-    const uint32_t off = sw128_off(row, 2 * qtr + cc);
-    *reinterpret_cast<uint4*>(stg + off) = make_uint4(pack_h2(dr[o], dr[o + 1]), pack_h2(dr[o + 2], dr[o + 3]), pack_h2(dr[o + 4], dr[o + 5]), pack_h2(dr[o + 6], dr[o + 7]));
-    *reinterpret_cast<uint4*>(stg + 16384 + off) = make_uint4(pack_h2(dz[o], dz[o + 1]), pack_h2(dz[o + 2], dz[o + 3]), pack_h2(dz[o + 4], dz[o + 5]), pack_h2(dz[o + 6], dz[o + 7]));
-    *reinterpret_cast<uint4*>(stg + 32768 + off) = make_uint4(pack_h2(dnr[o], dnr[o + 1]), pack_h2(dnr[o + 2], dnr[o + 3]), pack_h2(dnr[o + 4], dnr[o + 5]), pack_h2(dnr[o + 6], dnr[o + 7]));
-    *reinterpret_cast<uint4*>(stg + 49152 + off) = make_uint4(pack_h2(dn[o], dn[o + 1]), pack_h2(dn[o + 2], dn[o + 3]), pack_h2(dn[o + 4], dn[o + 5]), pack_h2(dn[o + 6], dn[o + 7]));
+    uint4 o_dr, o_dz, o_dnr, o_dn;
+    grad_rec8(g[hf], dh, o_dr, o_dz, o_dnr, o_dn);
+    const uint32_t off = sw128_off(row, 2 * qtr + hf);
+    *reinterpret_cast<uint4*>(stg + off) = o_dr;
+    *reinterpret_cast<uint4*>(stg + 16384 + off) = o_dz;
+    *reinterpret_cast<uint4*>(stg + 32768 + off) = o_dnr;
+    *reinterpret_cast<uint4*>(stg + 49152 + off) = o_dn;
+    mul_z8(dh, zw[hf]);                                           // dh_prev (before the recurrent product) = dh * z
+    dhs[(2 * hf) * 128] = make_float4(dh[0], dh[1], dh[2], dh[3]);
+    dhs[(2 * hf + 1) * 128] = make_float4(dh[4], dh[5], dh[6], dh[7]);
   }
   fence_proxy_async();
   __syncthreads();
@@ -1052,17 +1090,11 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             // pull the NEXT step's saved-gate records (contiguous per (dir, t, row tile)) into L2 one whole step ahead:
             // the cell threads' loads then see L2 latency instead of HBM latency
             const int tn = dir == 0 ? step - 1 : T - step;
-            const int64_t grp = (((int64_t)dir * T + tn) * MT + mt) * h4;
-            const char* ga = reinterpret_cast<const char*>(p.g16 + grp * 128);
-            const char* gb = reinterpret_cast<const char*>(p.g16 + p.g16_plane + grp * 128);
-            const char* hnp = reinterpret_cast<const char*>(p.hn) + grp * 128 * 16;
+            // each plane's words of (dir, tn, mt) are contiguous: H/8 groups x 128 rows x 16 B = NCH x 16 KB
+            const int64_t w0 = (((int64_t)dir * T + tn) * MT + mt) * (H >> 3) * 128;
 #pragma unroll 1
-            for (int i = 0; i < (NCH + 1) / 2; ++i) {             // each region: H/4 groups x 128 rows x 16 B = NCH x 32 KB
-              constexpr uint32_t PF = NCH == 1 ? 32768 : 65536;
-              prefetch_l2_bulk(ga + i * 65536, PF);
-              prefetch_l2_bulk(gb + i * 65536, PF);
-              prefetch_l2_bulk(hnp + i * 65536, PF);
-            }
+            for (int k = 0; k < GP_PLANES; ++k)
+              prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + k * p.g16_plane + w0), NCH * 16384);
             if (HAS_DAB) {
               const char* dp = reinterpret_cast<const char*>(p.d_above) +
                                (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2)) * 128 * 16;
@@ -1116,17 +1148,16 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         const int t = dir == 0 ? step : T - 1 - step;
         const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
         const uint32_t cur = lane_base + (it & 1) * 256, nxt = lane_base + ((it & 1) ^ 1) * 256;
-        // record (4-unit group) index of this thread's first group; group (c, i) is at rec0 + (16 c + i) * 128
-        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * h4 + 4 * sub) * 128 + row;
+        // word index (plane Z) of this thread's first 8-unit group; group (chunk c, half hf) is at rec0 + (8 c + hf) * 128
+        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + 2 * sub) * 128 + row;
         const float4* dab0 = HAS_DAB ? reinterpret_cast<const float4*>(p.d_above) +
                                            (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 4 * sub) * 128 + row
                                      : nullptr;
         // ---------------- all z words of the step: in flight while the previous step's MMAs finish
-        uint2 zw[NCH * 4];
+        uint4 zw[NCH * 2];                        // (padded steps / pad rows hold z = 1: the gradient passes through)
 #pragma unroll
-        for (int g = 0; g < NCH * 4; ++g)
-          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) + 1)
-                       : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);                             // z = 1: gradient passes through
+        for (int g = 0; g < NCH * 2; ++g)
+          zw[g] = __ldg(p.g16 + GP_Z * p.g16_plane + rec0 + (int64_t)((g >> 1) * 8 + (g & 1)) * 128);
         float4 da[4];
         if (HAS_DAB) {
 #pragma unroll
@@ -1162,56 +1193,27 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
             }
             tmem_st16(cur + 64 * c + 16 * sub, dh);
           }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint2 z2 = zw[4 * c + i];
-            dh[4 * i] *= dq_u16(z2.x);
-            dh[4 * i + 1] *= dq_u16(z2.x >> 16);
-            dh[4 * i + 2] *= dq_u16(z2.y);
-            dh[4 * i + 3] *= dq_u16(z2.y >> 16);
-          }
+          mul_z8(dh, zw[2 * c]);
+          mul_z8(dh + 8, zw[2 * c + 1]);
           tmem_st16(nxt + 64 * c + 16 * sub, dh);
         }
         // first half-chunk of gate records for pass 2 (in flight across the barrier)
-        uint4 ga0[2], gb0[2], ga1[2], gb1[2];
-        float4 hn0[2], hn1[2];
-#define TT_LOAD_HALF(GA, GB, HN, HCV)                                                                          \
-  _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                              \
-    const int64_t rec = rec0 + (int64_t)(((HCV) >> 1) * 16 + ((HCV) & 1) * 2 + i) * 128;                       \
-    GA[i] = live ? __ldg(p.g16 + rec) : make_uint4(0u, 0u, 0u, 0u);                                            \
-    GB[i] = live ? __ldg(p.g16 + p.g16_plane + rec) : make_uint4(0u, 0u, 0u, 0u);                              \
-    HN[i] = live ? __ldg(reinterpret_cast<const float4*>(p.hn) + rec) : make_float4(0.f, 0.f, 0.f, 0.f);       \
-  }
-#define TT_GRAD_HALF(GA, GB, HN, CV, CCV, SBUF)                                                                \
+        GateRec8 g0, g1;
+#define TT_LOAD_HALF(G, HCV) load_rec8(G, p.g16 + rec0 + (int64_t)(((HCV) >> 1) * 8 + ((HCV) & 1)) * 128, p.g16_plane);
+#define TT_GRAD_HALF(G, CV, CCV, SBUF)                                                                         \
   {                                                                                                            \
     float dh[8];                                                                                               \
     tmem_ld8(cur + 64 * (CV) + 16 * sub + 8 * (CCV), dh);                                                      \
     tmem_wait_ld();                                                                                            \
-    float dr[8], dzv[8], dnr[8], dn[8];                                                                        \
-    _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                            \
-      const int o = 4 * i;                                                                                     \
-      const float hnv[4] = {HN[i].x, HN[i].y, HN[i].z, HN[i].w};                                               \
-      const uint32_t rw[2] = {GA[i].x, GA[i].y}, zw2[2] = {GA[i].z, GA[i].w};                                  \
-      const uint32_t nw[2] = {GB[i].x, GB[i].y}, qw[2] = {GB[i].z, GB[i].w};                                   \
-      _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                          \
-        const int sh = (j & 1) * 16;                                                                           \
-        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw2[j >> 1] >> sh);                               \
-        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);  \
-        const float d = live ? dh[o + j] : 0.f;                                                                \
-        const float dn_pre = d * (1.f - z) * (1.f - n * n);                                                    \
-        dn[o + j] = dn_pre;                                                                                    \
-        dnr[o + j] = dn_pre * r;                                                                               \
-        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);                                                           \
-        dzv[o + j] = d * q * (1.f - z); /* == dh (h_prev - n) z (1 - z), q = h_t - n = z (h_prev - n) */       \
-      }                                                                                                        \
-    }                                                                                                          \
+    uint4 o_dr, o_dz, o_dnr, o_dn;                                                                             \
+    grad_rec8(G, dh, o_dr, o_dz, o_dnr, o_dn);                                                                 \
     const uint32_t off = sw128_off(row, 2 * sub + (CCV));                                                      \
-    *reinterpret_cast<uint4*>(SBUF + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7])); \
+    *reinterpret_cast<uint4*>(SBUF + off) = o_dr;                                                              \
+    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = o_dz;                                                      \
+    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = o_dnr;                                                     \
+    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = o_dn;                                                      \
   }
-        TT_LOAD_HALF(ga0, gb0, hn0, 0)
+        TT_LOAD_HALF(g0, 0)
         tmem_wait_st();
         tc_fence_before();
         named_bar_sync(1, 512);
@@ -1224,16 +1226,16 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         for (int c = 0; c < NCH; ++c) {
           const int sb = (use + c) & 1;
           uint8_t* sbuf = stg + sb * R_STG;
-          TT_LOAD_HALF(ga1, gb1, hn1, 2 * c + 1)
+          TT_LOAD_HALF(g1, 2 * c + 1)
           if (e == 0 && use + c >= 2) {                          // staging buffer free: MMAs and the TMA store of its last use are done
             mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);
             mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1);
           }
           named_bar_sync(2, 512);
           if (e == 0) BWD_MARK(it, 3 + 3 * c);
-          TT_GRAD_HALF(ga0, gb0, hn0, c, 0, sbuf)
-          if (c + 1 < NCH) { TT_LOAD_HALF(ga0, gb0, hn0, 2 * c + 2) }
-          TT_GRAD_HALF(ga1, gb1, hn1, c, 1, sbuf)
+          TT_GRAD_HALF(g0, c, 0, sbuf)
+          if (c + 1 < NCH) { TT_LOAD_HALF(g0, 2 * c + 2) }
+          TT_GRAD_HALF(g1, c, 1, sbuf)
           fence_proxy_async();
           named_bar_sync(3, 512);
           if (e == 0) {
@@ -1417,12 +1419,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
         for (int step = p.step_begin - 1; step >= p.step_end; --step) {
           const int t = dir == 0 ? step : T - 1 - step;
           if (step > p.step_end) {
-            // next step's saved-gate records of THIS CTA's units (32 contiguous groups = 64 KB per array) into L2
+            // next step's saved-gate records of THIS CTA's units (16 contiguous 8-unit groups = 32 KB per plane) into L2
             const int tn = dir == 0 ? step - 1 : T - step;
-            const int64_t grp = (((int64_t)dir * T + tn) * MT + mt) * h4 + 32 * (int)rank;
-            prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + grp * 128), 65536);
-            prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + p.g16_plane + grp * 128), 65536);
-            prefetch_l2_bulk(reinterpret_cast<const char*>(p.hn) + grp * 128 * 16, 65536);
+            const int64_t w0 = ((((int64_t)dir * T + tn) * MT + mt) * (H >> 3) + 16 * (int)rank) * 128;
+#pragma unroll 1
+            for (int k = 0; k < GP_PLANES; ++k)
+              prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + k * p.g16_plane + w0), 32768);
             if (HAS_DAB) {
               const char* dp = reinterpret_cast<const char*>(p.d_above) +
                                (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 32 * (int)rank) * 128 * 16;
@@ -1480,16 +1482,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
         const int t = dir == 0 ? step : T - 1 - step;
         const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
         const uint32_t cur = lane_base + (it & 1) * 128, nxt = lane_base + ((it & 1) ^ 1) * 128;
-        // record (4-unit group) index of this thread's first group; LOCAL chunk c, group i is at rec0 + (16 c + i) * 128
-        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * h4 + 16 * cg0 + 4 * sub) * 128 + row;
+        // word index (plane Z) of this thread's first 8-unit group; LOCAL chunk c, half hf is at rec0 + (8 c + hf) * 128
+        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + 8 * cg0 + 2 * sub) * 128 + row;
         const float4* dab0 = HAS_DAB ? reinterpret_cast<const float4*>(p.d_above) +
                                            (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 16 * cg0 + 4 * sub) * 128 + row
                                      : nullptr;
-        uint2 zw[NCL * 4];
+        uint4 zw[NCL * 2];
 #pragma unroll
-        for (int g = 0; g < NCL * 4; ++g)
-          zw[g] = live ? __ldg(reinterpret_cast<const uint2*>(p.g16 + rec0 + (int64_t)((g >> 2) * 16 + (g & 3)) * 128) + 1)
-                       : make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+        for (int g = 0; g < NCL * 2; ++g)
+          zw[g] = __ldg(p.g16 + GP_Z * p.g16_plane + rec0 + (int64_t)((g >> 1) * 8 + (g & 1)) * 128);
         float4 da[4];
         if (HAS_DAB) {
 #pragma unroll
@@ -1522,55 +1523,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
             }
             tmem_st16(cur + 64 * c + 16 * sub, dh);
           }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint2 z2 = zw[4 * c + i];
-            dh[4 * i] *= dq_u16(z2.x);
-            dh[4 * i + 1] *= dq_u16(z2.x >> 16);
-            dh[4 * i + 2] *= dq_u16(z2.y);
-            dh[4 * i + 3] *= dq_u16(z2.y >> 16);
-          }
+          mul_z8(dh, zw[2 * c]);
+          mul_z8(dh + 8, zw[2 * c + 1]);
           tmem_st16(nxt + 64 * c + 16 * sub, dh);
         }
-        uint4 ga0[2], gb0[2], ga1[2], gb1[2];
-        float4 hn0[2], hn1[2];
-#define TT_LOAD_HALF(GA, GB, HN, HCV)                                                                          \
-  _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                              \
-    const int64_t rec = rec0 + (int64_t)(((HCV) >> 1) * 16 + ((HCV) & 1) * 2 + i) * 128;                       \
-    GA[i] = live ? __ldg(p.g16 + rec) : make_uint4(0u, 0u, 0u, 0u);                                            \
-    GB[i] = live ? __ldg(p.g16 + p.g16_plane + rec) : make_uint4(0u, 0u, 0u, 0u);                              \
-    HN[i] = live ? __ldg(reinterpret_cast<const float4*>(p.hn) + rec) : make_float4(0.f, 0.f, 0.f, 0.f);       \
-  }
-#define TT_GRAD_HALF(GA, GB, HN, CV, CCV, SBUF)                                                                \
+        GateRec8 g0, g1;
+#define TT_LOAD_HALF(G, HCV) load_rec8(G, p.g16 + rec0 + (int64_t)(((HCV) >> 1) * 8 + ((HCV) & 1)) * 128, p.g16_plane);
+#define TT_GRAD_HALF(G, CV, CCV, SBUF)                                                                         \
   {                                                                                                            \
     float dh[8];                                                                                               \
     tmem_ld8(cur + 64 * (CV) + 16 * sub + 8 * (CCV), dh);                                                      \
     tmem_wait_ld();                                                                                            \
-    float dr[8], dzv[8], dnr[8], dn[8];                                                                        \
-    _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                                            \
-      const int o = 4 * i;                                                                                     \
-      const float hnv[4] = {HN[i].x, HN[i].y, HN[i].z, HN[i].w};                                               \
-      const uint32_t rw[2] = {GA[i].x, GA[i].y}, zw2[2] = {GA[i].z, GA[i].w};                                  \
-      const uint32_t nw[2] = {GB[i].x, GB[i].y}, qw[2] = {GB[i].z, GB[i].w};                                   \
-      _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                                          \
-        const int sh = (j & 1) * 16;                                                                           \
-        const float r = dq_u16(rw[j >> 1] >> sh), z = dq_u16(zw2[j >> 1] >> sh);                               \
-        const float n = dq_s16(nw[j >> 1] >> sh, 1.f / kNScale), q = dq_s16(qw[j >> 1] >> sh, 1.f / kQScale);  \
-        const float d = live ? dh[o + j] : 0.f;                                                                \
-        const float dn_pre = d * (1.f - z) * (1.f - n * n);                                                    \
-        dn[o + j] = dn_pre;                                                                                    \
-        dnr[o + j] = dn_pre * r;                                                                               \
-        dr[o + j] = dn_pre * hnv[j] * r * (1.f - r);                                                           \
-        dzv[o + j] = d * q * (1.f - z);                                                                        \
-      }                                                                                                        \
-    }                                                                                                          \
+    uint4 o_dr, o_dz, o_dnr, o_dn;                                                                             \
+    grad_rec8(G, dh, o_dr, o_dz, o_dnr, o_dn);                                                                 \
     const uint32_t off = sw128_off(row, 2 * sub + (CCV));                                                      \
-    *reinterpret_cast<uint4*>(SBUF + off) = make_uint4(pack_h2(dr[0], dr[1]), pack_h2(dr[2], dr[3]), pack_h2(dr[4], dr[5]), pack_h2(dr[6], dr[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = make_uint4(pack_h2(dzv[0], dzv[1]), pack_h2(dzv[2], dzv[3]), pack_h2(dzv[4], dzv[5]), pack_h2(dzv[6], dzv[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = make_uint4(pack_h2(dnr[0], dnr[1]), pack_h2(dnr[2], dnr[3]), pack_h2(dnr[4], dnr[5]), pack_h2(dnr[6], dnr[7])); \
-    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = make_uint4(pack_h2(dn[0], dn[1]), pack_h2(dn[2], dn[3]), pack_h2(dn[4], dn[5]), pack_h2(dn[6], dn[7])); \
+    *reinterpret_cast<uint4*>(SBUF + off) = o_dr;                                                              \
+    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = o_dz;                                                      \
+    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = o_dnr;                                                     \
+    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = o_dn;                                                      \
   }
-        TT_LOAD_HALF(ga0, gb0, hn0, 0)
+        TT_LOAD_HALF(g0, 0)
         tmem_wait_st();
         tc_fence_before();
         named_bar_sync(1, 512);
@@ -1580,15 +1552,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
         for (int c = 0; c < NCL; ++c) {
           const int sb = (use + c) & 1;
           uint8_t* sbuf = stg + sb * R_STG;
-          TT_LOAD_HALF(ga1, gb1, hn1, 2 * c + 1)
+          TT_LOAD_HALF(g1, 2 * c + 1)
           if (e == 0 && use + c >= 2) {                          // staging buffer free: local MMAs, TMA store and the peer are done with it
             mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);
             mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1);
           }
           named_bar_sync(2, 512);
-          TT_GRAD_HALF(ga0, gb0, hn0, c, 0, sbuf)
-          if (c + 1 < NCL) { TT_LOAD_HALF(ga0, gb0, hn0, 2 * c + 2) }
-          TT_GRAD_HALF(ga1, gb1, hn1, c, 1, sbuf)
+          TT_GRAD_HALF(g0, c, 0, sbuf)
+          if (c + 1 < NCL) { TT_LOAD_HALF(g0, 2 * c + 2) }
+          TT_GRAD_HALF(g1, c, 1, sbuf)
           fence_proxy_async();
           named_bar_sync(3, 512);
           if (e == 0) mbar_arrive(&sfull[sb]);
@@ -1776,8 +1748,7 @@ static uint64_t carve_saved(const V2Dims& d, void* base, uint64_t size, V2Saved*
     f16* h1 = d.nd > 1 ? w.take<f16>((int64_t)(d.T + 1) * d.Bp * d.H) : nullptr;
     uint4* g = nullptr; float* hn = nullptr;
     if (with_gates) {
-      g = w.take<uint4>((int64_t)d.nd * d.ntok * (d.H >> 2) * 2);
-      hn = w.take<float>((int64_t)d.nd * d.ntok * d.H);
+      g = w.take<uint4>((int64_t)d.nd * d.ntok * (d.H >> 3) * GP_PLANES);       // 10 H bytes per (token, direction)
     }
     if (out) { out->xhi[l] = x; out->hhi[l][0] = h0; out->hhi[l][1] = h1; out->g16[l] = g; out->hn[l] = hn; }
   }
@@ -1902,7 +1873,7 @@ int gru_stack_fwd_v2(const tt_gru_stack* a, cudaStream_t s) {
     }
     p.gi = f.gi;
     p.g16 = save ? sv.g16[l] : nullptr; p.hn = save ? sv.hn[l] : nullptr;
-    p.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128;
+    p.g16_plane = (int64_t)nd * T * MT * (H >> 3) * 128;
     p.out = (a->out && !has_next) ? a->out : nullptr;
     p.h_n = a->h_n + (int64_t)l * nd * B * H;
     p.lengths = a->lengths;
@@ -2094,7 +2065,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
       }
       return TT_OK;
     };
-    cp.g16 = sv.g16[l]; cp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
+    cp.g16 = sv.g16[l]; cp.g16_plane = (int64_t)nd * T * MT * (H >> 3) * 128; cp.hn = sv.hn[l]; cp.dhs = f.dhs; cp.d_above = d_above; cp.lengths = fw->lengths;
     cp.B = B; cp.Bp = Bp; cp.T = T; cp.H = H; cp.ndir = nd;
     cp.drop_p = (has_next && d_above) ? fw->dropout_p : 0.f;
     cp.inv_keep = cp.drop_p > 0.f ? 1.f / (1.f - cp.drop_p) : 1.f;
@@ -2118,7 +2089,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
         bp.dg[dd] = cp.dg[dd];
         TT_TRY(make_plane_map(&bp.w[dd], f.whh_hi[dd], 3 * H, H, H, 64, 1));
       }
-      bp.g16 = sv.g16[l]; bp.g16_plane = (int64_t)nd * T * MT * (H >> 2) * 128; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
+      bp.g16 = sv.g16[l]; bp.g16_plane = (int64_t)nd * T * MT * (H >> 3) * 128; bp.hn = sv.hn[l]; bp.dhs0 = f.dhs; bp.d_above = d_above; bp.lengths = fw->lengths;
       bp.B = B; bp.Bp = Bp; bp.T = T; bp.H = H; bp.ndir = nd; bp.tiles = MT * nd;
       bp.drop_p = cp.drop_p; bp.inv_keep = cp.inv_keep; bp.seed = cp.seed; bp.seed_dev = cp.seed_dev; bp.dbg = g_step_dbg;
       const int grid = bp.tiles < num_sms ? bp.tiles : num_sms;
