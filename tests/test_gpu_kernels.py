@@ -203,7 +203,8 @@ def test_gru_backward_time_segments(B, T, In, H, NL, nseg, use_len):
 
 
 @pytest.mark.parametrize("B,T,In,NL,use_len,drop", [(70, 9, 40, 2, True, 0.0), (300, 17, 300, 2, False, 0.0),
-                                                     (131, 33, 24, 1, True, 0.0), (200, 12, 64, 3, False, 0.25)])
+                                                     (131, 33, 24, 1, True, 0.0), (200, 12, 64, 3, False, 0.25),
+                                                     (500, 11, 32, 2, True, 0.0), (1024, 40, 48, 1, False, 0.0)])
 def test_gru_backward_cta_pairs(B, T, In, NL, use_len, drop):
     """H = 256: the BPTT on 2-CTA clusters (hidden units split over the pair, gate-gradient tiles exchanged through
     distributed shared memory; mode 3) gives the gradients of nn.GRU in float64 and - same saved state, same dropout
@@ -227,7 +228,7 @@ def test_gru_backward_cta_pairs(B, T, In, NL, use_len, drop):
         (o * go).sum().add((hn * gh).sum()).backward()
     grads = {}
     try:
-        for mode in (3, 1):
+        for mode in (3, 4, 1):
             lib.tt_debug_bwd_seq_mode(mode)
             ws = [p.detach().float().to(DEV).requires_grad_(True) for p in ref.parameters()]
             xg = x.detach().float().to(DEV).requires_grad_(True)
@@ -242,8 +243,9 @@ def test_gru_backward_cta_pairs(B, T, In, NL, use_len, drop):
                     assert rel_err(w.grad, p.grad) < 1e-3, (mode, n, rel_err(w.grad, p.grad))
     finally:
         lib.tt_debug_bwd_seq_mode(2)
-    for a, b in zip(grads[3], grads[1]):
-        assert rel_err(a, b) < 2e-4, rel_err(a, b)
+    for mode in (3, 4):
+        for a, b in zip(grads[mode], grads[1]):
+            assert rel_err(a, b) < 2e-4, (mode, rel_err(a, b))
 
 
 def test_gru_token_ids_equal_pregathered_floats(engine):

@@ -11,6 +11,8 @@ gru = tt.GRU(In, H, num_layers=1, bidirectional=True).to(dev)
 x = torch.randn(B, T, In, device=dev) * 0.1
 buf = torch.zeros(64 * 16, dtype=torch.int64, device=dev)
 lib = L.lib()
+import os
+if os.environ.get("TT_BWD_SEQ_MODE"): lib.tt_debug_bwd_seq_mode(int(os.environ["TT_BWD_SEQ_MODE"]))
 def run():
     o, hn = gru(x, need_output=False)
     hn.square().sum().backward()

@@ -247,9 +247,10 @@ unsigned long long* g_step_dbg = nullptr;
 static int g_seq_mode = 4;                    // 0: one launch per timestep; 2 / 4: persistent kernel, epilogue warps per quarter
 static int seq_mode() { return g_seq_mode; }
 static int g_wgrad_overlap = 1;               // 1: weight-gradient GEMMs of layer l overlap the BPTT of layer l-1 (helper stream)
-static int g_bwd_seq_mode = 2;                // 2: fused persistent BPTT, on CTA pairs when H == 256 and the pairs fit in half the SMs;
-                                              // 3: CTA pairs whenever H == 256; 1: always one CTA per (row tile, direction) (H <= 256);
-                                              // 0: two launches per timestep
+static int g_bwd_seq_mode = 2;                // 2: fused persistent BPTT, on unit-split CTA pairs when H == 256 and the pairs fit in half the SMs;
+                                              // 3: unit-split CTA pairs whenever H == 256; 4: tcgen05 CTA pairs (cta_group::2, two row tiles of one
+                                              //    direction per cluster) whenever H == 256 and the row tiles pair up;
+                                              // 1: always one independent CTA per (row tile, direction) (H <= 256); 0: two launches per timestep
 static int g_bwd_segments = 1;                // time segments per fused BPTT (weight gradients of a finished segment overlap the next one)
 static int bwd_seq_mode() { return g_bwd_seq_mode; }    // tt_debug_step_buffer(): phase timestamps of the LAST launched step
 constexpr int S_BM = 128, S_BK = 64, S_UN = 64, S_BN = 3 * S_UN;
@@ -1015,8 +1016,10 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < R_WSTAGES; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 1); mbar_init(&sempty[i], 1); mbar_init(&sstored[i], 1); }
-    mbar_init(init_done, 1);
+    // sfull / init_done: one arrival per gate-gradient WARP (16) - no block-wide barrier in the per-chunk loop, so a warp
+    // that is ahead goes on into the other staging buffer instead of waiting for the slowest one at every hand-over
+    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 16); mbar_init(&sempty[i], 1); mbar_init(&sstored[i], 1); }
+    mbar_init(init_done, 16);
     mbar_init(acc_full, 1);
     fence_barrier_init();
   }
@@ -1216,8 +1219,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
         TT_LOAD_HALF(g0, 0)
         tmem_wait_st();
         tc_fence_before();
-        named_bar_sync(1, 512);
-        if (e == 0) mbar_arrive(init_done);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(init_done);
         if (e == 0) BWD_MARK(it, 2);
         // ---------------- pass 2: gate gradients, half-chunk (8 units) at a time, loads one half-chunk ahead.
         // NOT unrolled over chunks: the loop body must stay inside the instruction cache (the unrolled version spent
@@ -1227,21 +1230,18 @@ __global__ void __launch_bounds__(R_THREADS, 1) gru_bwd_seq_kernel(const __grid_
           const int sb = (use + c) & 1;
           uint8_t* sbuf = stg + sb * R_STG;
           TT_LOAD_HALF(g1, 2 * c + 1)
-          if (e == 0 && use + c >= 2) {                          // staging buffer free: MMAs and the TMA store of its last use are done
-            mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);
-            mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1);
+          if (use + c >= 2) {                                    // staging buffer free: MMAs and the TMA store of its last use are done
+            mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);  // (every thread waits itself: the phase cannot advance twice before
+            mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1); //  this warp has arrived on sfull for the use in between)
           }
-          named_bar_sync(2, 512);
           if (e == 0) BWD_MARK(it, 3 + 3 * c);
           TT_GRAD_HALF(g0, c, 0, sbuf)
           if (c + 1 < NCH) { TT_LOAD_HALF(g0, 2 * c + 2) }
           TT_GRAD_HALF(g1, c, 1, sbuf)
           fence_proxy_async();
-          named_bar_sync(3, 512);
-          if (e == 0) {
-            BWD_MARK(it, 4 + 3 * c);
-            mbar_arrive(&sfull[sb]);
-          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sfull[sb]);
+          if (e == 0) BWD_MARK(it, 4 + 3 * c);
         }
 #undef TT_LOAD_HALF
 #undef TT_GRAD_HALF
@@ -1589,6 +1589,300 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bw
   cluster_sync_all();                     // nobody leaves while the peer may still copy into / read from this CTA's shared memory
   if (warp == R_WARP_MMA) tmem_dealloc(tmem_base, 256);
 }
+
+// ------------------------------------------------------------------------------------------ fused BPTT, tcgen05 CTA pairs
+// H = 256.  Two row tiles of the SAME direction run as a 2-CTA cluster whose recurrent product dh_prev += dG W_hh is ONE
+// tcgen05.mma.cta_group::2 per k-step: M = 256 (each CTA's 128 rows, accumulators in each CTA's own tensor memory),
+// N = 256 with the W_hh k-block split by output column over the two CTAs' shared memory.  Each CTA therefore streams
+// HALF of W_hh per timestep (196 KB instead of 393 KB) through a ring of twice as many stages: the single-CTA kernel's
+// timestep was bound by that stream (latency x bytes in flight: 96 KB per ~1.2 us against 393 KB per step; in-kernel
+// marks: the MMAs of a step trailed the gate-gradient threads by 3.3 us).  Everything else - gate gradients, dG stores,
+// tensor-memory-resident dh - is the single-CTA kernel's, per CTA; the pair only shares the MMA issue (leader CTA) and
+// its barriers: the peer's warps arrive on the leader's `init_done` / `sfull` (mbarrier.arrive.release.cluster), and
+// every tcgen05.commit is multicast to both CTAs.  Same SM count as the single-CTA kernel (one CTA per (row tile, dir)).
+constexpr int D_WSTAGE = 64 * 128 * 2;             // this CTA's half of a k-block: [64 k][128 n] fp16 = 16 KB
+constexpr int D_WSTAGES = 6;
+static_assert(D_WSTAGES * D_WSTAGE == R_WSTAGES * R_WSTAGE, "same shared-memory budget as the single-CTA kernel");
+
+template <bool HAS_DAB>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(R_THREADS, 1) gru_bwd_duo_kernel(const __grid_constant__ BwdSeqParams p) {
+  constexpr int NCH = 4;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* wring = smem;
+  uint8_t* stg = smem + D_WSTAGES * D_WSTAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + 2 * R_STG);
+  uint64_t* wfull = bars;                 // [6] LEADER's: both CTAs' halves of a W k-block have landed (tx bytes of both)
+  uint64_t* wempty = bars + 6;            // [6] per CTA, arrived by the leader's multicast commit
+  uint64_t* sfull = bars + 12;            // [2] LEADER's: both CTAs' staging written (32 warp arrivals) -> MMA
+  uint64_t* sfull_l = bars + 14;          // [2] this CTA's staging written (16 warps) -> its dG store warp
+  uint64_t* sempty = bars + 16;           // [2] staging consumed (multicast commit -> both CTAs' cell threads)
+  uint64_t* init_done = bars + 18;        // LEADER's: buf[nxt] holds dht * z in both CTAs (32 warp arrivals)
+  uint64_t* acc_full = bars + 19;         // all MMAs of the step complete (multicast commit)
+  uint64_t* sstored = bars + 20;          // [2] TMA store has read the staging buffer (store warp -> cell threads)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int H = 64 * NCH, h4 = H >> 2;
+  const int T = p.T, MT = p.Bp >> 7;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < D_WSTAGES; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sfull[i], 32); mbar_init(&sfull_l[i], 16); mbar_init(&sempty[i], 1); mbar_init(&sstored[i], 1); }
+    mbar_init(init_done, 32);
+    mbar_init(acc_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == R_WARP_MMA) tmem_alloc_pair(tmem_slot, 512);      // the same warp of BOTH CTAs
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                     // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // register budget: the 16 gate-gradient warps (warpgroups 0-3) take what the control warpgroup gives up
+  if (warp >= 16) {
+    setmaxnreg_dec<32>();   // 512 * 112 + 128 * 32 == 640 * 96 registers: exactly what the launch allocated
+  if (warp == R_WARP_TMA) {
+    // ================================================================= W_hh producer: THIS CTA's half (128 of the 256 output
+    // columns) of every k-block; the bytes of both halves are counted on the leader's barrier
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        const int dir = tile / MT;
+        for (int step = p.step_end; step < p.step_begin; ++step)
+          for (int c = 0; c < NCH; ++c)
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wempty[stage], phase ^ 1);
+              uint8_t* sb = wring + stage * D_WSTAGE;
+              if (leader) mbar_arrive_expect_tx(&wfull[stage], 2 * D_WSTAGE);
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh)
+                tma_load_2d_pair(&p.w[dir], &wfull[stage], sb + hh * 8192, (2 * (int)rank + hh) * 64, g * H + c * 64);
+              if (++stage == D_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+      }
+    }
+  } else if (warp == R_WARP_MMA) {
+    // ================================================================= MMA issuer
+    if (lane == 0 && leader) {           // one thread of the pair issues the M = 256 MMAs of both row tiles
+      constexpr uint32_t idesc = make_idesc_f16(256, H, 0, 1);
+      int stage = 0, phase = 0, it = 0, use = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        for (int step = p.step_end; step < p.step_begin; ++step, ++it) {
+          const uint32_t d_tmem = tmem_base + ((it & 1) ^ 1) * 256;        // buf[nxt]
+          mbar_wait_cluster(init_done, it & 1);
+          tc_fence_after();
+          for (int c = 0; c < NCH; ++c, ++use) {
+            const int sb = use & 1;
+            mbar_wait_cluster(&sfull[sb], (use >> 1) & 1);
+            tc_fence_after();
+            for (int g = 0; g < 3; ++g) {
+              mbar_wait(&wfull[stage], phase);
+              tc_fence_after();
+              const uint32_t sa = smem_u32(stg + sb * R_STG + g * 16384), sw = smem_u32(wring + stage * D_WSTAGE);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                mma_f16_ss_pair(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sw + k * 2048, 8192, 1024), idesc, 1u);
+              mma_commit_pair(&wempty[stage], 3);
+              if (++stage == D_WSTAGES) { stage = 0; phase ^= 1; }
+            }
+            mma_commit_pair(&sempty[sb], 3);
+          }
+          mma_commit_pair(acc_full, 3);
+          BWD_MARK(it, 15);
+        }
+      }
+    }
+  } else if (warp == R_WARP_STORE) {
+    // ================================================================= dG plane writer (off the cell threads' critical path)
+    if (lane == 0) {
+      int use = 0;
+      for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+        const int mt = tile % MT, dir = tile / MT, m0 = mt * 128;
+        for (int step = p.step_begin - 1; step >= p.step_end; --step) {
+          const int t = dir == 0 ? step : T - 1 - step;
+          if (step > p.step_end) {
+            // pull the NEXT step's saved-gate records (contiguous per (dir, t, row tile)) into L2 one whole step ahead:
+            // the cell threads' loads then see L2 latency instead of HBM latency
+            const int tn = dir == 0 ? step - 1 : T - step;
+            // each plane's words of (dir, tn, mt) are contiguous: H/8 groups x 128 rows x 16 B = NCH x 16 KB
+            const int64_t w0 = (((int64_t)dir * T + tn) * MT + mt) * (H >> 3) * 128;
+#pragma unroll 1
+            for (int k = 0; k < GP_PLANES; ++k)
+              prefetch_l2_bulk(reinterpret_cast<const char*>(p.g16 + k * p.g16_plane + w0), NCH * 16384);
+            if (HAS_DAB) {
+              const char* dp = reinterpret_cast<const char*>(p.d_above) +
+                               (((int64_t)tn * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2)) * 128 * 16;
+#pragma unroll 1
+              for (int i = 0; i < (NCH + 1) / 2; ++i) prefetch_l2_bulk(dp + i * 65536, NCH == 1 ? 32768 : 65536);
+            }
+          }
+          for (int c = 0; c < NCH; ++c, ++use) {
+            const int sb = use & 1;
+            mbar_wait(&sfull_l[sb], (use >> 1) & 1);
+            const uint8_t* sbuf = stg + sb * R_STG;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) tma_store_2d(&p.dg[dir], sbuf + g * 16384, g * H + 64 * c, t * p.Bp + m0);
+            bulk_commit();
+            bulk_wait_read0();
+            mbar_arrive(&sstored[sb]);
+          }
+        }
+      }
+    }
+  }
+  } else {
+    setmaxnreg_inc<112>();
+    // ================================================================= gate gradients: thread = (batch row, 16 units per chunk)
+    const int e = threadIdx.x;
+    const int quarter = warp & 3, sub = warp >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    int it = 0, use = 0;
+    for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+      const int mt = tile % MT, dir = tile / MT, m0 = mt * 128, b = m0 + row;
+      const bool row_ok = b < p.B;
+      // ---- dL/dh at the end of the sequence -> buf[cur of this tile's first step]
+      if (it > 0) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+      {
+        const float4* src = reinterpret_cast<const float4*>(p.dhs0) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 x = __ldg(src + (int64_t)(16 * c + 4 * sub + i) * 128);
+            v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+          }
+          tmem_st16(lane_base + (it & 1) * 256 + 64 * c + 16 * sub, v);
+        }
+        tmem_wait_st();
+      }
+      for (int step = p.step_begin - 1; step >= p.step_end; --step, ++it) {
+        if (e == 0) BWD_MARK(it, 14);
+        const int t = dir == 0 ? step : T - 1 - step;
+        const bool live = row_ok && !(p.lengths && t >= p.lengths[row_ok ? b : 0]);
+        const uint32_t cur = lane_base + (it & 1) * 256, nxt = lane_base + ((it & 1) ^ 1) * 256;
+        // word index (plane Z) of this thread's first 8-unit group; group (chunk c, half hf) is at rec0 + (8 c + hf) * 128
+        const int64_t rec0 = ((((int64_t)dir * T + t) * MT + mt) * (H >> 3) + 2 * sub) * 128 + row;
+        const float4* dab0 = HAS_DAB ? reinterpret_cast<const float4*>(p.d_above) +
+                                           (((int64_t)t * MT + mt) * (p.ndir * h4) + ((dir * H) >> 2) + 4 * sub) * 128 + row
+                                     : nullptr;
+        // ---------------- all z words of the step: in flight while the previous step's MMAs finish
+        uint4 zw[NCH * 2];                        // (padded steps / pad rows hold z = 1: the gradient passes through)
+#pragma unroll
+        for (int g = 0; g < NCH * 2; ++g)
+          zw[g] = __ldg(p.g16 + GP_Z * p.g16_plane + rec0 + (int64_t)((g >> 1) * 8 + (g & 1)) * 128);
+        float4 da[4];
+        if (HAS_DAB) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) da[i] = live ? __ldg(dab0 + (int64_t)i * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (e == 0) BWD_MARK(it, 0);
+        if (step != p.step_begin - 1) { mbar_wait(acc_full, (it - 1) & 1); tc_fence_after(); }
+        if (e == 0) BWD_MARK(it, 1);
+        // ---------------- pass 1: dht = dh (+ d_above); buf[cur] <- dht; buf[nxt] <- dht * z
+        // (tcgen05.ld / .st are warp-collective: every lane executes them; only the VALUES depend on `live`)
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float dh[16];
+          tmem_ld16v(cur + 64 * c + 16 * sub, dh);
+          if (HAS_DAB) {
+            float4* d4 = da;
+            if (p.drop_p > 0.f && live) {
+              const uint64_t el = ((uint64_t)b * T + t) * (uint64_t)(p.ndir * H) + (uint64_t)(dir * H + 64 * c + 16 * sub);
+              float s8[8];
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), el >> 3, p.drop_p, p.inv_keep, s8);
+              d4[0].x *= s8[0]; d4[0].y *= s8[1]; d4[0].z *= s8[2]; d4[0].w *= s8[3];
+              d4[1].x *= s8[4]; d4[1].y *= s8[5]; d4[1].z *= s8[6]; d4[1].w *= s8[7];
+              dropout_scale8(p.seed + (p.seed_dev ? __ldg(p.seed_dev) : 0ull), (el >> 3) + 1, p.drop_p, p.inv_keep, s8);
+              d4[2].x *= s8[0]; d4[2].y *= s8[1]; d4[2].z *= s8[2]; d4[2].w *= s8[3];
+              d4[3].x *= s8[4]; d4[3].y *= s8[5]; d4[3].z *= s8[6]; d4[3].w *= s8[7];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { dh[4 * i] += d4[i].x; dh[4 * i + 1] += d4[i].y; dh[4 * i + 2] += d4[i].z; dh[4 * i + 3] += d4[i].w; }
+            if (c + 1 < NCH) {                                   // next chunk's d_above (L2-resident: prefetched a step ahead)
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                da[i] = live ? __ldg(dab0 + (int64_t)(16 * (c + 1) + i) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            tmem_st16(cur + 64 * c + 16 * sub, dh);
+          }
+          mul_z8(dh, zw[2 * c]);
+          mul_z8(dh + 8, zw[2 * c + 1]);
+          tmem_st16(nxt + 64 * c + 16 * sub, dh);
+        }
+        // first half-chunk of gate records for pass 2 (in flight across the barrier)
+        GateRec8 g0, g1;
+#define TT_LOAD_HALF(G, HCV) load_rec8(G, p.g16 + rec0 + (int64_t)(((HCV) >> 1) * 8 + ((HCV) & 1)) * 128, p.g16_plane);
+#define TT_GRAD_HALF(G, CV, CCV, SBUF)                                                                         \
+  {                                                                                                            \
+    float dh[8];                                                                                               \
+    tmem_ld8(cur + 64 * (CV) + 16 * sub + 8 * (CCV), dh);                                                      \
+    tmem_wait_ld();                                                                                            \
+    uint4 o_dr, o_dz, o_dnr, o_dn;                                                                             \
+    grad_rec8(G, dh, o_dr, o_dz, o_dnr, o_dn);                                                                 \
+    const uint32_t off = sw128_off(row, 2 * sub + (CCV));                                                      \
+    *reinterpret_cast<uint4*>(SBUF + off) = o_dr;                                                              \
+    *reinterpret_cast<uint4*>(SBUF + 16384 + off) = o_dz;                                                      \
+    *reinterpret_cast<uint4*>(SBUF + 32768 + off) = o_dnr;                                                     \
+    *reinterpret_cast<uint4*>(SBUF + 49152 + off) = o_dn;                                                      \
+  }
+        TT_LOAD_HALF(g0, 0)
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(init_done);
+        if (e == 0) BWD_MARK(it, 2);
+        // ---------------- pass 2: gate gradients, half-chunk (8 units) at a time, loads one half-chunk ahead.
+        // NOT unrolled over chunks: the loop body must stay inside the instruction cache (the unrolled version spent
+        // ~6 us per timestep refetching 65 KB of straight-line code)
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          const int sb = (use + c) & 1;
+          uint8_t* sbuf = stg + sb * R_STG;
+          TT_LOAD_HALF(g1, 2 * c + 1)
+          if (use + c >= 2) {                                    // staging buffer free: MMAs and the TMA store of its last use are done
+            mbar_wait(&sempty[sb], (((use + c) >> 1) - 1) & 1);  // (every thread waits itself: the phase cannot advance twice before
+            mbar_wait(&sstored[sb], (((use + c) >> 1) - 1) & 1); //  this warp has arrived on sfull for the use in between)
+          }
+          if (e == 0) BWD_MARK(it, 3 + 3 * c);
+          TT_GRAD_HALF(g0, c, 0, sbuf)
+          if (c + 1 < NCH) { TT_LOAD_HALF(g0, 2 * c + 2) }
+          TT_GRAD_HALF(g1, c, 1, sbuf)
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) { mbar_arrive(&sfull_l[sb]); mbar_arrive_leader(&sfull[sb]); }
+          if (e == 0) BWD_MARK(it, 4 + 3 * c);
+        }
+#undef TT_LOAD_HALF
+#undef TT_GRAD_HALF
+        use += NCH;
+      }
+      // ---- hand dL/dh to the next time segment: after the last step it lives in buf[it & 1] (that step's buf[nxt])
+      if (p.dhs_out && p.step_begin > p.step_end) {
+        mbar_wait(acc_full, (it - 1) & 1);
+        tc_fence_after();
+        float4* dst = reinterpret_cast<float4*>(p.dhs_out) + (((int64_t)dir * MT + mt) * h4) * 128 + row;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          float v[16];
+          tmem_ld16v(lane_base + (it & 1) * 256 + 64 * c + 16 * sub, v);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            dst[(int64_t)(16 * c + 4 * sub + i) * 128] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                     // nobody leaves (or frees tensor memory) while the pair's MMAs / commits may still touch it
+  if (warp == R_WARP_MMA) tmem_dealloc_pair(tmem_base, 512);
+}
+
 
 // ------------------------------------------------------------------------------------------ backward helpers
 // loss scale: s = 2^k with max|g| * s ~ 4  (fp16 planes of the gate gradients then keep >= 11 bits for everything
@@ -2007,6 +2301,11 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
   // idle SMs are busy with the weight-gradient GEMMs and the other tower anyway): used when the pairs fit in half the GPU
   // (measured: 12.6 vs 13.8 ms/step at B = 2048, 9.4 vs 11.4 at B = 1024); mode 3 forces them.
   const bool pair_bptt = H == 256 && (bwd_seq_mode() == 3 || (bwd_seq_mode() == 2 && 4 * MT * nd <= num_sms_b));
+  // tcgen05 CTA pairs: two row tiles of one direction per cluster (MT even), every cluster resident (MT * nd CTAs <= SMs)
+  // Opt-in (mode 4): measured at B = 4096 it halves the wait for the previous step's MMAs (2.5 -> 0.8 us per timestep) but the gate
+  // threads slow down by as much once the MMAs really overlap them (shared-memory bandwidth: 12.5 vs 11.8 us per timestep,
+  // profiles/r2_summary.md), so the independent one-CTA kernel stays the default.
+  const bool duo_bptt = !pair_bptt && H == 256 && (MT % 2) == 0 && MT * nd <= (num_sms_b & ~1) && bwd_seq_mode() == 4;
   const int bptt_want = MT * nd * (pair_bptt ? 2 : 1);
   const int bptt_ctas = bptt_want < num_sms_b ? bptt_want : num_sms_b;
   const int free_ctas = num_sms_b - bptt_ctas;           // SMs the BPTT kernel of the next layer leaves idle
@@ -2103,6 +2402,15 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
     }                                                                                                                 \
     gru_bwd_pair_kernel<DABV><<<pair_grid, R_THREADS, P_SMEM, s>>>(bp);                                               \
   } while (0)
+#define TT_BWD_DUO(DABV)                                                                                              \
+  do {                                                                                                                \
+    static DeviceOnce attr;                                                                                           \
+    if (attr.need()) {                                                                                                \
+      TT_CUDA(cudaFuncSetAttribute(gru_bwd_duo_kernel<DABV>, cudaFuncAttributeMaxDynamicSharedMemorySize, R_SMEM));   \
+      attr.done();                                                                                                    \
+    }                                                                                                                 \
+    gru_bwd_duo_kernel<DABV><<<bp.tiles, R_THREADS, R_SMEM, s>>>(bp);                                                 \
+  } while (0)
 #define TT_BWD_SEQ(NCHV, DABV)                                                                                        \
   do {                                                                                                                \
     static DeviceOnce attr;                                                                                           \
@@ -2121,6 +2429,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
           note_launch();
           ProfScope prof(PROF_GRU_SEQ_BWD, s);
           if (pair_bptt) { if (dab) TT_BWD_PAIR(true); else TT_BWD_PAIR(false); }
+          else if (duo_bptt) { if (dab) TT_BWD_DUO(true); else TT_BWD_DUO(false); }
           else if (H == 256) { if (dab) TT_BWD_SEQ(4, true); else TT_BWD_SEQ(4, false); }
           else if (H == 128) { if (dab) TT_BWD_SEQ(2, true); else TT_BWD_SEQ(2, false); }
           else { if (dab) TT_BWD_SEQ(1, true); else TT_BWD_SEQ(1, false); }
@@ -2135,6 +2444,7 @@ int gru_stack_bwd_v2(const tt_gru_stack_grad* a, cudaStream_t s) {
         }
       }
 #undef TT_BWD_SEQ
+#undef TT_BWD_DUO
 #undef TT_BWD_PAIR
     } else {
     UmmaPrepared prep;
@@ -2222,7 +2532,7 @@ extern "C" int tt_debug_bwd_segments(int32_t n) {
   return TT_OK;
 }
 extern "C" int tt_debug_bwd_seq_mode(int32_t mode) {
-  if (mode < 0 || mode > 3) { tt::set_error("tt_debug_bwd_seq_mode: 0..3"); return TT_ERR_INVALID; }
+  if (mode < 0 || mode > 4) { tt::set_error("tt_debug_bwd_seq_mode: 0..4"); return TT_ERR_INVALID; }
   tt::g_bwd_seq_mode = mode;
   return TT_OK;
 }
