@@ -176,7 +176,10 @@ typedef struct tt_head {
   float* out;       /* [B,Dout] normalised output when normalize, else may be NULL */
   float* norm;      /* [B] when normalize */
   const uint64_t* seed_dev;   /* optional DEVICE scalar added to `seed` at run time (CUDA-graph replay), or NULL */
+  void* workspace; uint64_t workspace_bytes;   /* tt_head_fwd_workspace(): operand planes of the tensor route; NULL -> the
+                                                  exact-fp32 SIMT GEMMs run instead (as under tt_set_engine(0)) */
 } tt_head;
+uint64_t tt_head_fwd_workspace(const tt_head* a);
 int tt_head_fwd(const tt_head* a, void* stream);
 
 typedef struct tt_head_grad {

@@ -63,6 +63,7 @@ class Head(C.Structure):
         ("w2", C.c_void_p), ("b2", C.c_void_p),
         ("y1", C.c_void_p), ("stats", C.c_void_p), ("y2", C.c_void_p), ("y3", C.c_void_p),
         ("out", C.c_void_p), ("norm", C.c_void_p), ("seed_dev", C.c_void_p),
+        ("workspace", C.c_void_p), ("workspace_bytes", u64),
     ]
 
 
@@ -102,6 +103,7 @@ SIGNATURES = {
     "tt_gru_stack_fwd": (C.c_int, [C.POINTER(GruStack), P]),
     "tt_gru_stack_bwd_workspace": (u64, [C.POINTER(GruStackGrad)]),
     "tt_gru_stack_bwd": (C.c_int, [C.POINTER(GruStackGrad), P]),
+    "tt_head_fwd_workspace": (u64, [C.POINTER(Head)]),
     "tt_head_fwd": (C.c_int, [C.POINTER(Head), P]),
     "tt_head_bwd_workspace": (u64, [C.POINTER(HeadGrad)]),
     "tt_head_bwd": (C.c_int, [C.POINTER(HeadGrad), P]),

@@ -1,7 +1,13 @@
 // K-D projection head: Linear -> LayerNorm -> ReLU [-> Linear] [-> L2 normalise], forward and backward.
-// The two Linear layers are tiny ([B,512]x[512,256] at the headline config, <0.1 % of a step) and run on the
-// exact-fp32 GEMM; LayerNorm+ReLU and the normalisation are one-warp-per-row kernels.
+// Engine 2 (default): the Linear layers and all their gradients run on the tcgen05 GEMM engine - forward products as 3
+// passes over fp16 hi/lo planes (the precision of the GRU forward), gradient products as 3 passes over bf16 hi/lo planes
+// (gradients live in fp16's subnormal range; bf16 x3 carries 16 mantissa bits at fp32's exponent range).  The pooled
+// state cat(h_n[-2], h_n[-1]) is formed once, as operand planes (never as an fp32 tensor).  Engine 0: the exact-fp32
+// SIMT GEMM.  LayerNorm + ReLU and the normalisation are one-warp-per-row kernels.
 #include "common.cuh"
+#include "umma.cuh"
+#include "umma_gemm.cuh"
+#include "gru_v2.cuh"
 
 namespace tt {
 
@@ -112,6 +118,64 @@ static inline void pair_with(GemmArgs& g, const float* A, const float* Bm, float
   g.A[1] = A; g.B[1] = Bm; g.C[1] = C; g.bias[1] = nullptr; g.nbatch = 2;
 }
 
+// ---- tensor-engine route
+// (operand planes need 16-byte rows: every dimension a multiple of 8 - otherwise the exact SIMT GEMMs run)
+static bool head_dims_tc(const tt_head* a) { return (a->In % 16) == 0 && (a->P1 % 8) == 0 && (a->D2 % 8) == 0; }
+static bool head_tc(const tt_head* a) { return engine_mode() == 2 && umma_available() && a->workspace != nullptr && head_dims_tc(a); }
+// fp32 [rows, cols] (row stride ld_in) -> fp16 hi/lo planes at row stride ld_out (no padding written: the caller owns the
+// columns outside [0, cols) - used to lay the two halves of the pooled state side by side)
+__global__ void split_f16_ld_kernel(const float* __restrict__ x, int64_t ld_in, int64_t rows, int cols, __half* __restrict__ hi,
+                                    __half* __restrict__ lo, int64_t ld_out) {
+  const int64_t total = rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / cols;
+    const int c = (int)(i - r * cols);
+    __half a, b;
+    tt::umma::split_f16(x[r * ld_in + c], a, b);
+    hi[r * ld_out + c] = a; lo[r * ld_out + c] = b;
+  }
+}
+__global__ void split_bf16_ld_kernel(const float* __restrict__ x, int64_t ld_in, int64_t rows, int cols, bf16* __restrict__ hi,
+                                     bf16* __restrict__ lo, int64_t ld_out) {
+  const int64_t total = rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / cols;
+    const int c = (int)(i - r * cols);
+    bf16 a, b;
+    tt::umma::split_bf16(x[r * ld_in + c], a, b);
+    hi[r * ld_out + c] = a; lo[r * ld_out + c] = b;
+  }
+}
+struct HeadPlanes { bf16* hi; bf16* lo; int64_t pitch; };
+static HeadPlanes take_planes(Workspace& w, int64_t rows, int64_t cols) {
+  HeadPlanes p;
+  p.pitch = plane_pitch(cols);
+  p.hi = w.take<bf16>(rows * p.pitch);
+  p.lo = w.take<bf16>(rows * p.pitch);
+  return p;
+}
+static int to_planes(const float* x, int64_t ld_in, int64_t rows, int cols, const HeadPlanes& p, int col0, bool f16, cudaStream_t s) {
+  const unsigned blocks = (unsigned)(ceil_div(rows * cols, 256) < 592 ? (ceil_div(rows * cols, 256) < 1 ? 1 : ceil_div(rows * cols, 256)) : 592);
+  note_launch();
+  if (f16) split_f16_ld_kernel<<<blocks, 256, 0, s>>>(x, ld_in, rows, cols, (__half*)p.hi + col0, (__half*)p.lo + col0, p.pitch);
+  else split_bf16_ld_kernel<<<blocks, 256, 0, s>>>(x, ld_in, rows, cols, p.hi + col0, p.lo + col0, p.pitch);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+// C[M,N] = A B^T (+ bias) with A / B K-major ([M][K], [N][K]) or MN-major ([K][M], [K][N]) plane pairs, 3 passes
+static int tc_gemm(const HeadPlanes& A, int a_col0, bool a_mn, const HeadPlanes& B, int b_col0, bool b_mn, float* C, int64_t ldc,
+                   const float* bias, int M, int N, int K, bool f16, cudaStream_t s) {
+  UmmaGemm g{};
+  g.A[0] = Planes{A.hi + a_col0, A.lo + a_col0, A.pitch};
+  g.B[0] = Planes{B.hi + b_col0, B.lo + b_col0, B.pitch};
+  g.C[0] = C; g.bias[0] = bias; g.ldc = ldc;
+  g.M = M; g.N = N; g.K = K; g.nbatch = 1; g.a_mn = a_mn; g.b_mn = b_mn; g.alpha = 1.f; g.beta = 0.f;
+  g.splitk = (a_mn && b_mn) ? 0 : 1;              // reductions over the batch rows: split-K to fill the machine
+  g.f16 = f16 ? 1 : 0; g.npass = 3;
+  return umma_gemm(g, s);
+}
+static uint64_t planes_bytes(int64_t rows, int64_t cols) { return 2 * (align_up((uint64_t)rows * plane_pitch(cols) * 2, 256) + 256); }
+
 static int check_head(const tt_head* a) {
   TT_CHECK_ARG(a && a->B > 0 && a->In > 0 && (a->In % 2) == 0 && a->P1 > 0 && a->D2 >= 0, "head: bad dims");
   TT_CHECK_ARG(a->v_lo && a->v_hi && a->w1 && a->b1 && a->ln_w && a->ln_b && a->y1 && a->stats && a->y2, "head: null buffer");
@@ -146,7 +210,19 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   TT_TRY(check_head(a));
   cudaStream_t s = (cudaStream_t)stream;
   const int B = a->B, In = a->In, P = a->P1, D2 = a->D2, Hh = In / 2;
-  {
+  const bool tc = head_tc(a);
+  Workspace w(a->workspace, a->workspace_bytes);
+  HeadPlanes vcat{}, w1p{}, y2p{}, w2p{};
+  if (tc) {
+    vcat = take_planes(w, B, In); w1p = take_planes(w, P, In);
+    if (D2 > 0) { y2p = take_planes(w, B, P); w2p = take_planes(w, D2, P); }
+    if (!w.ok()) { set_error("head fwd: workspace too small (%llu < %llu)", (unsigned long long)a->workspace_bytes, (unsigned long long)w.used); return TT_ERR_WORKSPACE; }
+    // y1 = cat(v_lo, v_hi) W1^T + b1: the pooled state goes side by side into ONE operand plane pair
+    TT_TRY(to_planes(a->v_lo, Hh, B, Hh, vcat, 0, true, s));
+    TT_TRY(to_planes(a->v_hi, Hh, B, Hh, vcat, Hh, true, s));
+    TT_TRY(to_planes(a->w1, In, P, In, w1p, 0, true, s));
+    TT_TRY(tc_gemm(vcat, 0, false, w1p, 0, false, a->y1, P, a->b1, B, P, In, true, s));
+  } else {
     // y1 = v_lo W1[:, :Hh]^T + v_hi W1[:, Hh:]^T + b1: the two halves of the concatenated input as one launch
     GemmArgs g = nt_gemm(a->v_lo, Hh, a->w1, In, a->y1, P, a->b1, B, P, Hh, 0.f);
     pair_with(g, a->v_hi, a->w1 + Hh, a->y1);
@@ -159,7 +235,13 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   const float* last = a->y2;
   int Dl = P;
   if (D2 > 0) {
-    TT_TRY(gemm_f32(nt_gemm(a->y2, P, a->w2, P, a->y3, D2, a->b2, B, D2, P, 0.f), s));
+    if (tc) {
+      TT_TRY(to_planes(a->y2, P, B, P, y2p, 0, true, s));
+      TT_TRY(to_planes(a->w2, P, D2, P, w2p, 0, true, s));
+      TT_TRY(tc_gemm(y2p, 0, false, w2p, 0, false, a->y3, D2, a->b2, B, D2, P, true, s));
+    } else {
+      TT_TRY(gemm_f32(nt_gemm(a->y2, P, a->w2, P, a->y3, D2, a->b2, B, D2, P, 0.f), s));
+    }
     last = a->y3; Dl = D2;
   }
   if (a->normalize) {
@@ -169,6 +251,13 @@ int tt_head_fwd(const tt_head* a, void* stream) {
   return TT_OK;
 }
 
+uint64_t tt_head_fwd_workspace(const tt_head* a) {
+  if (!a) return 0;
+  uint64_t n = planes_bytes(a->B, a->In) + planes_bytes(a->P1, a->In);
+  if (a->D2 > 0) n += planes_bytes(a->B, a->P1) + planes_bytes(a->D2, a->P1);
+  return n + 1024;
+}
+
 uint64_t tt_head_bwd_workspace(const tt_head_grad* a) {
   if (!a) return 0;
   const tt_head* f = &a->fwd;
@@ -176,7 +265,10 @@ uint64_t tt_head_bwd_workspace(const tt_head_grad* a) {
   const int Dl = f->D2 > 0 ? f->D2 : f->P1;
   w.take<float>((int64_t)f->B * Dl);
   for (int i = 0; i < 4; ++i) w.take<float>((int64_t)f->B * f->P1);
-  return w.used + 256;
+  // tensor route: bf16 hi/lo planes of dlast, y2, W2, d_y1, cat(v), W1
+  uint64_t n = w.used + 256 + planes_bytes(f->B, f->P1) + planes_bytes(f->B, f->In) + planes_bytes(f->P1, f->In);
+  if (f->D2 > 0) n += planes_bytes(f->B, f->D2) + planes_bytes(f->B, f->P1) + planes_bytes(f->D2, f->P1);
+  return n + 1024;
 }
 
 int tt_head_bwd(const tt_head_grad* a, void* stream) {
@@ -195,6 +287,13 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
   float* gm = w.take<float>((int64_t)B * P);
   float* gx = w.take<float>((int64_t)B * P);
   if (!w.ok()) { set_error("head bwd: workspace too small"); return TT_ERR_WORKSPACE; }
+  const bool tc = engine_mode() == 2 && umma_available() && head_dims_tc(f);
+  HeadPlanes dlp{}, y2p{}, w2p{}, dy1p{}, vcat{}, w1p{};
+  if (tc) {
+    if (D2 > 0) { dlp = take_planes(w, B, D2); y2p = take_planes(w, B, P); w2p = take_planes(w, D2, P); }
+    dy1p = take_planes(w, B, P); vcat = take_planes(w, B, In); w1p = take_planes(w, P, In);
+    if (!w.ok()) { set_error("head bwd: workspace too small (%llu < %llu)", (unsigned long long)a->workspace_bytes, (unsigned long long)w.used); return TT_ERR_WORKSPACE; }
+  }
 
   const float* dlast = a->d_out;
   if (f->normalize) {
@@ -204,9 +303,18 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
   }
   const float* dy2 = dlast;
   if (D2 > 0) {
-    TT_TRY(gemm_f32(tn_gemm(dlast, D2, f->y2, P, a->d_w2, P, D2, P, B), s));
+    if (tc) {
+      TT_TRY(to_planes(dlast, D2, B, D2, dlp, 0, false, s));
+      TT_TRY(to_planes(f->y2, P, B, P, y2p, 0, false, s));
+      TT_TRY(to_planes(f->w2, P, D2, P, w2p, 0, false, s));
+      // d_w2[D2,P] = dlast^T y2 (reduction over the batch rows: both operands MN-major); d_y2[B,P] = dlast W2
+      TT_TRY(tc_gemm(dlp, 0, true, y2p, 0, true, a->d_w2, P, nullptr, D2, P, B, false, s));
+      TT_TRY(tc_gemm(dlp, 0, false, w2p, 0, true, d_y2, P, nullptr, B, P, D2, false, s));
+    } else {
+      TT_TRY(gemm_f32(tn_gemm(dlast, D2, f->y2, P, a->d_w2, P, D2, P, B), s));
+      TT_TRY(gemm_f32(nn_gemm(dlast, D2, f->w2, P, d_y2, P, B, P, D2, 0.f), s));
+    }
     TT_TRY(colsum_f32(dlast, D2, B, D2, a->d_b2, s));
-    TT_TRY(gemm_f32(nn_gemm(dlast, D2, f->w2, P, d_y2, P, B, P, D2, 0.f), s));
     dy2 = d_y2;
   }
   tt::note_launch(); ln_relu_bwd_kernel<<<(unsigned)ceil_div(B, 8), 256, 0, s>>>(f->y1, f->y2, f->stats, f->ln_w, dy2, d_y1, gm, gx, B, P,
@@ -215,7 +323,16 @@ int tt_head_bwd(const tt_head_grad* a, void* stream) {
   TT_TRY(colsum_f32(gm, P, B, P, a->d_ln_b, s));
   TT_TRY(colsum_f32(gx, P, B, P, a->d_ln_w, s));
   TT_TRY(colsum_f32(d_y1, P, B, P, a->d_b1, s));
-  {
+  if (tc) {
+    TT_TRY(to_planes(d_y1, P, B, P, dy1p, 0, false, s));
+    TT_TRY(to_planes(f->v_lo, Hh, B, Hh, vcat, 0, false, s));
+    TT_TRY(to_planes(f->v_hi, Hh, B, Hh, vcat, Hh, false, s));
+    TT_TRY(to_planes(f->w1, In, P, In, w1p, 0, false, s));
+    // d_w1[P,In] = d_y1^T cat(v) ; d_v_lo / d_v_hi [B,Hh] = d_y1 W1[:, :Hh] / W1[:, Hh:]
+    TT_TRY(tc_gemm(dy1p, 0, true, vcat, 0, true, a->d_w1, In, nullptr, P, In, B, false, s));
+    TT_TRY(tc_gemm(dy1p, 0, false, w1p, 0, true, a->d_v_lo, Hh, nullptr, B, Hh, P, false, s));
+    TT_TRY(tc_gemm(dy1p, 0, false, w1p, Hh, true, a->d_v_hi, Hh, nullptr, B, Hh, P, false, s));
+  } else {
     // the two column halves of d_w1, and the two halves of d_v, as one launch each (disjoint outputs)
     GemmArgs g = tn_gemm(d_y1, P, f->v_lo, Hh, a->d_w1, In, P, Hh, B);
     pair_with(g, d_y1, f->v_hi, a->d_w1 + Hh);

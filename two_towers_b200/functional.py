@@ -206,6 +206,8 @@ class HeadFunction(torch.autograd.Function):
         a.v_lo, a.v_hi = L.ptr(v_lo), L.ptr(v_hi)
         a.w1, a.b1, a.ln_w, a.ln_b, a.w2, a.b2 = (L.ptr(t) for t in (w1, b1, ln_w, ln_b, w2, b2))
         a.y1, a.stats, a.y2, a.y3, a.out, a.norm = (L.ptr(t) for t in (y1, stats, y2, y3, out, norm))
+        ws = L.workspace(lib.tt_head_fwd_workspace(C.byref(a)), dev)
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         L.run(dev, lib.tt_head_fwd, "tt_head_fwd", C.byref(a))
         result = out if normalize else (y3 if has2 else y2)
         if need_grad:
