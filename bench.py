@@ -569,13 +569,28 @@ def run_ours(args):
         opt.step()
         return loss, hard
 
-    # The whole step (zero_grad, both towers, loss, backward, gradient all-reduce, clip-free Adam, hard-negative mining) as ONE
-    # CUDA graph: captured on the first call, replayed afterwards (two_towers_b200/graph.py).  --no-graph keeps the eager loop.
-    gstep = None
-    if graphed:
-        gstep = tt.GraphedTrainStep(model, crit, opt, reducer=reducer, mine_k=TOPK, pos_offset=rank * B,
-                                    docs_fn=(lambda x: dops.all_gather_rows(x, group)) if world > 1 else None)
-    step = gstep if graphed else eager_step
+    # N = 1: the whole step (zero_grad, both towers, loss, backward, clip-free Adam, hard-negative mining) as ONE CUDA graph,
+    # captured on the first call, replayed afterwards (two_towers_b200/graph.py GraphedTrainStep).
+    # N > 1: only the towers are graphed (GraphedTowers: forward and backward of both towers as two graphs); the loss with its
+    # all-gather / reduce-scatter, the gradient all-reduce and the optimizer stay eager - NCCL calls captured inside a graph
+    # cost ~2.5 ms per step at 8 GPUs (profiles/r2_summary.md).  --no-graph keeps the fully eager loop.
+    gstep = towers = None
+    if graphed and world == 1:
+        gstep = tt.GraphedTrainStep(model, crit, opt, reducer=reducer, mine_k=TOPK, pos_offset=rank * B)
+    elif graphed:
+        towers = tt.GraphedTowers(model)
+
+    def towers_step(q, d):
+        opt.zero_grad(set_to_none=True)
+        qv, dv = towers(q, d)
+        loss = crit(qv, dv)
+        hard = tt.get_hard_negatives_batch(qv.detach(), dops.all_gather_rows(dv.detach(), group), k=TOPK, pos_offset=rank * B)
+        loss.backward()
+        reducer.finish()
+        opt.step()
+        return loss, hard
+
+    step = gstep if gstep is not None else (towers_step if towers is not None else eager_step)
 
     def barrier():
         if world > 1:
@@ -600,8 +615,10 @@ def run_ours(args):
     e1.record(st)
     barrier()
     launches = int(lib.tt_kernel_launches() - k0)
-    if graphed:
+    if gstep is not None:
         launches = int(gstep.launches_per_replay(*resident[0]) or 0) * args.steps      # replays do not pass through the host counter
+    elif towers is not None:
+        launches += int(towers.launches_per_replay(*resident[0]) or 0) * args.steps     # eager part counted above + the two replays
     sampler.mark_end()
     clocks = sampler.stop()
     # ---- dominant-kernel timing: the same K steps again with the towers on ONE stream (kernel durations under
@@ -710,7 +727,10 @@ def run_ours(args):
         line["roofline"] = roofs[0] if roofs else None
         line["kernels"] = roofs[1:] + ([gemm_roof] if gemm_roof else [f for f in fams[2:]])
         line["gemm_table"] = gemm_rows
-        line["graph"] = {"captured": bool(graphed), "launches_per_replay": (gstep.launches_per_replay(*resident[0]) if graphed else None),
+        line["graph"] = {"captured": ("whole step" if gstep is not None else "towers (forward + backward); loss, NCCL, optimizer eager"
+                                      if towers is not None else False),
+                         "launches_per_replay": (gstep.launches_per_replay(*resident[0]) if gstep is not None else
+                                                 towers.launches_per_replay(*resident[0]) if towers is not None else None),
                          "note": "host_queue_ms_per_step is the host time to queue one step: input copies + one cudaGraphLaunch when "
                                  "captured, every kernel launch through Python/ctypes otherwise (--no-graph)"}
     # ---- parity self-check on this very process group (small shapes, ~1 s): the sharded step - eager and captured in a CUDA
@@ -720,14 +740,14 @@ def run_ours(args):
         pc = dp_parity_check(group, dev, graphed=graphed)
         parity = {"status": "ok" if pc["ok"] else "MISMATCH", "world": world, "loss_rel": pc["loss_rel"],
                   "worst_grad_rel": pc["worst_grad"][1], "worst_grad": pc["worst_grad"][0], "indices_equal": pc["indices_equal"],
-                  "graphed_weight_rel": pc.get("graphed_weight_rel"),
+                  "graphed_weight_rel": pc.get("graphed_weight_rel"), "failed": pc.get("failed"),
                   "what": "data-parallel step vs single process on the concatenated batch (two_towers_b200/selfcheck.py)"}
     except Exception as exc:                                  # a failing check must not hide the measurement; it is reported
         parity = {"status": "ERROR", "error": repr(exc)[:300]}
     if rank == 0:
         line["parity_check"] = parity
     del resident[:], host[:]
-    del model, opt, gstep, step, eager_step, reducer
+    del model, opt, gstep, towers, towers_step, step, eager_step, reducer
     torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_configs:
         line["configs"] = secondary_configs(args, dev, table, graphed)

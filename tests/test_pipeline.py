@@ -476,3 +476,69 @@ def test_graphed_train_step_draws_new_dropout_masks_on_every_replay():
     q, d = torch.randn(32, 5, 20, device=dev), torch.randn(32, 7, 20, device=dev)
     losses = [step(q, d)[0].item() for _ in range(4)]
     assert len(set(losses)) == 4, losses                # same inputs, same weights: only the masks differ
+
+
+@pytest.mark.gpu
+def test_graphed_towers_equal_the_eager_step_and_fire_grad_hooks():
+    """The data-parallel form of the graphed step: tower forward / backward replayed from two CUDA graphs, loss / optimizer
+    eager.  Equal to the eager loop step for step (two shapes), and post-accumulate-grad hooks (the all-reducer's) fire."""
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    m1, m2 = tt.EnhancedTwoTowerModel(20, 32).to(dev).train(), tt.EnhancedTwoTowerModel(20, 32).to(dev).train()
+    m2.load_state_dict(m1.state_dict())
+    table = (torch.randn(500, 20) * 0.3).to(dev)
+    for m in (m1, m2):
+        m.attach_embeddings(table, pad_id=0)
+        for mod in m.modules():
+            if isinstance(mod, tt.GRU):
+                mod.dropout = 0.0
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+    crit = tt.MarginRankingLoss()
+    o1 = tt.FusedAdamW(m1.parameters(), lr=1e-3, weight_decay=0.01, max_grad_norm=1.0)
+    o2 = tt.FusedAdamW(m2.parameters(), lr=1e-3, weight_decay=0.01, max_grad_norm=1.0)
+    towers = tt.GraphedTowers(m1)
+    fired = []
+    hooks = [p.register_post_accumulate_grad_hook(lambda p: fired.append(1)) for p in m1.parameters()]
+    g = torch.Generator().manual_seed(1)
+    for it in range(5):
+        B = 48 if it != 3 else 40
+        q = torch.randint(0, 500, (B, 6), generator=g).to(dev)
+        d = torch.randint(0, 500, (B, 11), generator=g).to(dev)
+        fired.clear()
+        o1.zero_grad(set_to_none=True)
+        qv1, dv1 = towers(q, d)
+        loss1 = crit(qv1, dv1)
+        loss1.backward()
+        o1.step()
+        assert len(fired) == len(list(m1.parameters())), it
+        o2.zero_grad(set_to_none=True)
+        qv2, dv2 = m2(q, d)
+        loss2 = crit(qv2, dv2)
+        loss2.backward()
+        o2.step()
+        assert abs(loss1.item() - loss2.item()) <= 1e-5 * abs(loss2.item()), (it, loss1.item(), loss2.item())
+        for (k, a), (_, b) in zip(m1.state_dict().items(), m2.state_dict().items()):
+            assert rel_err(a, b) < 1e-5, (it, k)
+    for h in hooks:
+        h.remove()
+    assert len(towers._runs) == 2 and towers.launches_per_replay(q, d) > 20
+
+
+@pytest.mark.gpu
+def test_graphed_towers_draw_new_dropout_masks_on_every_call():
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    m = tt.SimpleTwoTower(20, 64).to(dev).train()
+    towers = tt.GraphedTowers(m)
+    q, d = torch.randn(32, 5, 20, device=dev), torch.randn(32, 7, 20, device=dev)
+    crit = tt.SymmetricInfoNCELoss(0.1)
+    losses = []
+    for _ in range(4):
+        qv, dv = towers(q, d)
+        loss = crit(qv, dv)
+        loss.backward()                                  # backward of the same call sees the same masks: finite gradients
+        assert all(torch.isfinite(p.grad).all() for p in m.parameters())
+        m.zero_grad(set_to_none=True)
+        losses.append(loss.item())
+    assert len(set(losses)) == 4, losses

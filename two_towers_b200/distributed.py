@@ -12,6 +12,8 @@ is sharded and there is exactly one exchange step:
 Each rank's loss is  sum(local rows) / B_global ; the sum over ranks is the reference's mean over the global
 batch, hence SUM (not mean) for the gradient all-reduce.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -93,7 +95,11 @@ class GradientAllReducer:
       do nothing and `finish()` reduces whatever has accumulated.
     """
 
-    def __init__(self, params, group=None, bucket_bytes=4 << 20, named_params=None):
+    def __init__(self, params, group=None, bucket_bytes=None, named_params=None, overlap=None):
+        # TT_DP_BUCKET_MB / TT_DP_OVERLAP: measurement knobs (bench.py); overlap=False launches every bucket from finish()
+        if bucket_bytes is None:
+            bucket_bytes = int(float(os.environ.get("TT_DP_BUCKET_MB", "4")) * (1 << 20))
+        self.overlap = (os.environ.get("TT_DP_OVERLAP", "1") != "0") if overlap is None else bool(overlap)
         self.group = group
         if named_params is not None:
             named = [(n, p) for n, p in named_params if p.requires_grad]
@@ -172,7 +178,7 @@ class GradientAllReducer:
             e.record(torch.cuda.current_stream(p.grad.device))
             self._events[i].append(e)
         self._pending[i] -= 1
-        if self._pending[i] == 0:
+        if self._pending[i] == 0 and self.overlap:
             self._launch(i)
 
     class _NoSync:

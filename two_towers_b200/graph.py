@@ -135,3 +135,89 @@ class GraphedTrainStep:
         key = (tuple(q.shape), q.dtype, tuple(d.shape), d.dtype, q.device)
         c = self._graphs.get(key)
         return c.launches if c is not None else None
+
+
+class _TowersFn(torch.autograd.Function):
+    """Autograd node of GraphedTowers: forward / backward = replay of the two captured graphs.  The parameters are inputs of
+    the node, so their gradients flow through autograd's AccumulateGrad like any others (post-accumulate hooks - the
+    gradient all-reducer's - fire as in the eager step)."""
+
+    @staticmethod
+    def forward(ctx, run, q, d, *params):
+        run.q.copy_(q, non_blocking=True)
+        run.d.copy_(d, non_blocking=True)
+        run.fwd.replay()
+        ctx.run = run
+        return run.qv.detach(), run.dv.detach()
+
+    @staticmethod
+    def backward(ctx, gq, gd):
+        run = ctx.run
+        run.gq.copy_(gq)
+        run.gd.copy_(gd)
+        run.bwd.replay()
+        return (None, None, None) + tuple(g.detach() for g in run.grads)
+
+
+class _TowersRun:
+    __slots__ = ("fwd", "bwd", "q", "d", "qv", "dv", "gq", "gd", "grads", "launches")
+
+
+class GraphedTowers:
+    """towers = GraphedTowers(model);  query_vec, doc_vec = towers(q, d)   - a drop-in for `model(q, d)` in a train step.
+
+    Forward and backward of BOTH towers (embedding gather, GRU stacks, projection heads: ~150 of the ~180 kernel launches of
+    a step) are captured as two CUDA graphs per input shape; the loss, the collectives, the gradient all-reduce and the
+    optimizer stay eager.  This is the data-parallel form of GraphedTrainStep: NCCL collectives captured INSIDE a CUDA graph
+    cost ~2.5 ms per step at 8 GPUs (measured: 25.4 vs 22.8 ms, profiles/r2_summary.md), so under data parallelism only the
+    collective-free part of the step is graphed.  Dropout draws fresh masks on every call (device seed, bumped here).
+    Train mode only; the model must keep returning a (query_vec, doc_vec) tuple."""
+
+    def __init__(self, model, warmup=2):
+        self.model, self.warmup = model, max(1, int(warmup))
+        self._runs = {}
+        self._seed = None
+        self._stream = None
+
+    def _capture(self, q, d):
+        dev = q.device
+        if self._seed is None:
+            self._seed = torch.zeros(1, dtype=torch.int64, device=dev)
+            self._stream = torch.cuda.Stream(dev)
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        r = _TowersRun()
+        r.q, r.d = q.clone(), d.clone()
+        cur = torch.cuda.current_stream(dev)
+        self._stream.wait_stream(cur)
+        with torch.cuda.stream(self._stream), Fn.device_seed(self._seed):
+            for _ in range(self.warmup):                       # allocator + library one-time state, outside any capture
+                qv, dv = self.model(r.q, r.d)
+                torch.autograd.grad((qv, dv), params, (torch.ones_like(qv), torch.ones_like(dv)))
+        cur.wait_stream(self._stream)
+        torch.cuda.synchronize(dev)
+        lib = L.lib()
+        n0 = lib.tt_kernel_launches()
+        r.fwd, r.bwd = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with Fn.device_seed(self._seed):
+            with torch.cuda.graph(r.fwd, stream=self._stream):
+                r.qv, r.dv = self.model(r.q, r.d)
+            r.gq, r.gd = torch.zeros_like(r.qv), torch.zeros_like(r.dv)
+            with torch.cuda.graph(r.bwd, pool=r.fwd.pool(), stream=self._stream):
+                r.grads = torch.autograd.grad((r.qv, r.dv), params, (r.gq, r.gd))
+        r.launches = int(lib.tt_kernel_launches() - n0)
+        return r, params
+
+    def __call__(self, q, d):
+        if not self.model.training:
+            raise RuntimeError("GraphedTowers captures the training step; use the model directly for inference")
+        key = (tuple(q.shape), q.dtype, tuple(d.shape), d.dtype, q.device)
+        ent = self._runs.get(key)
+        if ent is None:
+            ent = self._runs[key] = self._capture(q, d)
+        run, params = ent
+        self._seed.add_(1)
+        return _TowersFn.apply(run, q, d, *params)
+
+    def launches_per_replay(self, q, d):
+        ent = self._runs.get((tuple(q.shape), q.dtype, tuple(d.shape), d.dtype, q.device))
+        return ent[0].launches if ent is not None else None
