@@ -39,7 +39,11 @@ class CorpusIndex:
 @torch.no_grad()
 def search_topk(query_vecs, doc_encodings, k=10, cosine=True, index_base=0):
     """query_vecs [Q,D] (or [D]) vs doc_encodings [N,D] (tensor or CorpusIndex) -> (scores [Q,k], indices int64 [Q,k]),
-    best first; ties go to the lowest index.  Same per-query result as cosine_similarity + topk in the reference."""
+    best first; ties go to the lowest index.  Scores are the exact fp32 FMA chain in ascending d (the arithmetic of the
+    oracle's restatement); indices equal what a stable descending sort of those scores gives - which is cosine_similarity +
+    topk of the reference up to torch's unspecified tie order and cuBLAS summation order.  The tensor-engine candidate
+    selection in front of the exact re-score accepts a row only when its k-th score clears every non-candidate by more than
+    the measured error bound (corpus AND query rounding residuals included); other rows are re-scanned exactly."""
     if isinstance(doc_encodings, CorpusIndex):
         if doc_encodings.cosine != bool(cosine):
             raise ValueError("search_topk: the CorpusIndex was built for the other score mode")
@@ -139,7 +143,9 @@ def first_relevant_rank(query_vecs, doc_vecs, relevant):
     """Reciprocal rank of the first relevant candidate in the FULL ranking of the candidates
     (validate_margin.compute_mrr :37-54: cosine similarity, stable descending sort - ties keep the candidate order -,
     1/rank of the first hit, 0 without one).  query_vecs [Q,D]; doc_vecs [N,D] (one candidate list shared by the queries)
-    or [Q,N,D]; relevant bool [Q,N].  Returns (rr float64 [Q], top3 indices [Q,min(3,N)], top3 scores)."""
+    or [Q,N,D]; relevant bool [Q,N].  Returns (rr float64 [Q], top3 indices [Q,min(3,N)], top3 scores).
+    A helper on stock torch ops (cosine_similarity + stable sort over a few hundred candidates), not one of the library's
+    kernels and not a hot path: the reference ranks ~1000 candidates per query here."""
     if query_vecs.dim() == 1:
         query_vecs = query_vecs.unsqueeze(0)
     docs = doc_vecs.unsqueeze(0) if doc_vecs.dim() == 2 else doc_vecs
