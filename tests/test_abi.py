@@ -1,4 +1,5 @@
-"""CPU: the C-ABI library loads and exports every symbol include/tt_b200.h declares; struct layouts seen by
+"""CPU: the C-ABI library loads and exports every symbol include/*.h declares (tt_b200.h: the boundary; tt_b200_debug.h:
+test / measurement hooks); struct layouts seen by
 ctypes equal the C compiler's.  No compute calls (no GPU here)."""
 import ctypes
 import os
@@ -12,12 +13,21 @@ from conftest import ROOT
 from two_towers_b200 import _lib
 
 HEADER = os.path.join(ROOT, "include", "tt_b200.h")
+HEADERS = [HEADER, os.path.join(ROOT, "include", "tt_b200_debug.h")]
 
 
-def _declared_symbols():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(tt_[a-z0-9_]+)\s*\(", src)))
+def _declared_symbols(headers=HEADERS):
+    out = set()
+    for h in headers:
+        src = open(h).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        out |= set(re.findall(r"\b(tt_[a-z0-9_]+)\s*\(", src))
+    return sorted(out)
+
+
+def test_debug_hooks_are_not_in_the_boundary_header():
+    public = _declared_symbols([HEADER])
+    assert not [s for s in public if s.startswith("tt_debug_") or s.startswith("tt_gemm_")], public
 
 
 def test_header_declares_functions():
@@ -28,7 +38,7 @@ def test_header_declares_functions():
 def test_library_exports_every_declared_symbol():
     handle = ctypes.CDLL(_lib.LIB_PATH)
     for s in _declared_symbols():
-        assert hasattr(handle, s), f"{s} declared in tt_b200.h but not exported"
+        assert hasattr(handle, s), f"{s} declared in include/*.h but not exported"
 
 
 def test_binding_covers_every_declared_symbol():

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include "../../include/tt_b200.h"
+#include "../../include/tt_b200_debug.h"
 
 namespace tt {
 
