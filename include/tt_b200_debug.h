@@ -64,6 +64,10 @@ int tt_debug_sel_passes(int32_t passes);
  * shape, of the int32[Q] flags "row failed the acceptance test of the tensor route and went through the exact scan";
  * -1 when the call does not take the tensor route.  Tests use it to check that benign data never falls back. */
 int64_t tt_debug_topk_fallback_flags(int32_t Q, int64_t N, int32_t D, int32_t mode, int32_t k, int32_t indexed);
+/* GEMM engine: 1 (default) = large K-major problems (the 3-pass input-projection GEMMs) run on 2-CTA clusters with
+ * tcgen05.mma.cta_group::2 (256 x 256 tiles, each CTA stages half of B); 0 = always one CTA per 128 x 256 tile.  Same
+ * products in the same order per output element: results are bit-identical. */
+int tt_debug_gemm_pairs(int32_t on);
 /* Same kernel: how many corpus tiles ahead the CTAs of a column range prefetch into L2 (0 = off). */
 int tt_debug_sel_prefetch(int32_t tiles);
 

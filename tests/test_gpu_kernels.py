@@ -682,3 +682,33 @@ def test_gemm_operand_formats(M, N, K, flags):
     tol = 2e-3 if flags & 2 else 5e-5          # single fp16 pass: 2^-11 per operand; 3 passes: ~fp32
     assert flags & 1 or not flags & 2          # (bf16 single pass is not a supported mode of the pipeline)
     assert rel_err(c, ref) < tol, rel_err(c, ref)
+
+
+@pytest.mark.parametrize("flags", [0, 1, 1 | 2])
+@pytest.mark.parametrize("M,N,K", [(128 * 76, 1024, 300), (128 * 80, 1000, 128), (128 * 150, 768, 520)])
+def test_gemm_cta_pairs_bit_identical_to_single_cta(M, N, K, flags):
+    """Large K-major problems run on 2-CTA clusters (tcgen05.mma.cta_group::2, 256 x 256 tiles, each CTA stages half of B):
+    vs float64 within the operand-format tolerance, and bit-identical to the one-CTA-per-tile kernel (same products, same
+    order per output element).  Ragged N (1000) and K (300, 520) tails included."""
+    from two_towers_b200 import _lib as L
+    lib = L.lib()
+    rng = np.random.default_rng(M + N + K + flags)
+    a = rng.standard_normal((M, K)).astype(np.float32)
+    b = rng.standard_normal((N, K)).astype(np.float32)
+    ad, bd = _t(a), _t(b)
+    ws = L.workspace(lib.tt_gemm_x3_workspace(M, N, K), DEV)
+    out = []
+    try:
+        for pairs in (1, 0):
+            lib.tt_debug_gemm_pairs(pairs)
+            c = torch.zeros(M, N, device=DEV)
+            L.check(lib.tt_gemm_test(L.ptr(ad), L.ptr(bd), L.ptr(c), M, N, K, 1.0, 0.0, flags, ws.data_ptr(), ws.numel(),
+                                     L.stream()), "tt_gemm_test")
+            torch.cuda.synchronize()
+            out.append(c)
+    finally:
+        lib.tt_debug_gemm_pairs(1)
+    ref = torch.from_numpy(a.astype(np.float64) @ b.astype(np.float64).T)
+    tol = 2e-3 if flags & 2 else 5e-5
+    assert rel_err(out[0], ref) < tol, rel_err(out[0], ref)
+    assert torch.equal(out[0], out[1])

@@ -135,6 +135,7 @@ SIGNATURES = {
     "tt_debug_bwd_segments": (C.c_int, [i32]),
     "tt_debug_sel_resident": (C.c_int, [i32]),
     "tt_debug_sel_prefetch": (C.c_int, [i32]),
+    "tt_debug_gemm_pairs": (C.c_int, [i32]),
     "tt_debug_sel_passes": (C.c_int, [i32]),
     "tt_debug_topk_fallback_flags": (i64, [i32, i64, i32, i32, i32, i32]),
     "tt_gemm_test": (C.c_int, [P, P, P, i32, i32, i32, F, F, i32, P, u64, P]),

@@ -1282,10 +1282,6 @@ constexpr int P_WSTAGES = 3;
 constexpr int P_LAND = 3 * 16384;                  // landing slot: the peer's dr | dz | dn*r tiles of one chunk
 constexpr int P_SMEM = P_WSTAGES * P_WSTAGE + 2 * R_STG + P_LAND + 1024 + 512;
 
-__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));

@@ -699,6 +699,10 @@ int tt_debug_sel_passes(int32_t passes) {
   tt::g_rescan = (f & 2) == 0;
   return TT_OK;
 }
+int tt_debug_gemm_pairs(int32_t on) {
+  tt::umma_set_pairs(on);
+  return TT_OK;
+}
 int tt_debug_sel_prefetch(int32_t tiles) {
   TT_CHECK_ARG(tiles >= 0 && tiles <= 64, "tt_debug_sel_prefetch: 0..64 column tiles");
   tt::umma_set_sel_prefetch(tiles);

@@ -117,6 +117,11 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // ------------------------------------------------------------------------------------------ CTA pairs (cta_group::2)
 // A 2-CTA cluster sharing one tcgen05.mma: M = 256 (each CTA's 128 rows of A and of the accumulator, in its own shared /
 // tensor memory), B split by N over the two CTAs' shared memory.  Forms as in the PTX ISA / CUTLASS cute/arch

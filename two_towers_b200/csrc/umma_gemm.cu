@@ -114,6 +114,112 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + TAIL_BYTES;
 };
 
+// Drain one accumulator tile (this thread: row `row` of the 128, columns [chalf*BN/2, (chalf+1)*BN/2)) to C: plain row-major
+// (transposed through shared memory where a full 32-column block allows), time-major -> batch-first remap, tiled gi layout,
+// split-K atomics.  Shared by the single-CTA and the CTA-pair kernels.
+template <int BN>
+__device__ __forceinline__ void epi_store_tile(const UmmaParams& p, uint32_t tmem_acc, float* tr_smem, int warp, int lane, int quarter,
+                                               int chalf, int gm, int m_blk, int n_blk, int sp, int bz, bool has_k, float alpha) {
+  const int kb0 = 0, kb1 = has_k ? 1 : 0;
+  const float* bias = p.bias[bz];
+  bool row_ok = gm < p.M;
+  float* crow;
+  int64_t tl_base = 0;
+  if (p.epi == 1) {                        // tiled: 128-row tile == one batch tile of one timestep
+    const int t = gm / p.tl_Bp, mt = (gm % p.tl_Bp) >> 7;
+    tl_base = ((int64_t)t * (p.tl_Bp >> 7) + mt) * p.tl_G;
+    crow = p.C[bz] + (gm & 127) * 4;
+  } else if (p.rm_Bp > 0) {                // time-major rows -> batch-first C rows
+    const int t = gm / p.rm_Bp, b = gm % p.rm_Bp;
+    row_ok = row_ok && b < p.rm_B;
+    crow = p.C[bz] + ((int64_t)b * p.rm_T + t) * p.ldc;
+  } else {
+    crow = p.C[bz] + (int64_t)gm * p.ldc;
+  }
+  const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C[bz]) & 15) == 0);
+#pragma unroll 1
+  for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
+    float v[32];
+    tmem_ld32(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+    const int gn0 = n_blk * BN + c0;
+    // plain row-major store of a full 32-column block: transpose the warp's 32x32 block through shared memory so
+    // that 8 lanes write one 128-byte row segment (a TMEM lane is a row: direct stores would put 32 rows, 16 bytes
+    // each, into every instruction).  All conditions are warp-uniform.
+    if (p.epi == 0 && p.splitk == 1 && p.beta == 0.f && p.rm_Bp == 0 && vec_ok && gn0 + 32 <= p.N && kb0 < kb1) {
+      float* T = tr_smem + (warp - 2) * 1024;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 o = make_float4(alpha * v[4 * j], alpha * v[4 * j + 1], alpha * v[4 * j + 2], alpha * v[4 * j + 3]);
+        if (bias) { o.x += bias[gn0 + 4 * j]; o.y += bias[gn0 + 4 * j + 1]; o.z += bias[gn0 + 4 * j + 2]; o.w += bias[gn0 + 4 * j + 3]; }
+        *reinterpret_cast<float4*>(T + lane * 32 + ((j ^ (lane & 7)) << 2)) = o;
+      }
+      __syncwarp();
+      const int c4 = lane & 7, rsub = lane >> 3;
+      float* cbase = p.C[bz] + (int64_t)(m_blk * UBM + quarter * 32) * p.ldc + gn0 + 4 * c4;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int rr = 4 * i + rsub;
+        const float4 o = *reinterpret_cast<const float4*>(T + rr * 32 + ((c4 ^ (rr & 7)) << 2));
+        if (m_blk * UBM + quarter * 32 + rr < p.M) *reinterpret_cast<float4*>(cbase + (int64_t)rr * p.ldc) = o;
+      }
+      __syncwarp();
+      continue;
+    }
+    if (row_ok && gn0 < p.N && kb0 < kb1) {
+      if (p.epi == 1) {
+        const int hc4 = p.tl_Hc >> 2;
+        float4* dst[8];
+        float4 cv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {          // all read-modify-write loads first: one L2 round trip, not eight
+          const int n = gn0 + 4 * j;
+          const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
+          dst[j] = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
+          cv[j] = (p.beta != 0.f && n < p.N) ? *dst[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int n = gn0 + 4 * j;
+          if (n < p.N) {
+            float4 o = make_float4(alpha * v[4 * j] + p.beta * cv[j].x, alpha * v[4 * j + 1] + p.beta * cv[j].y,
+                                   alpha * v[4 * j + 2] + p.beta * cv[j].z, alpha * v[4 * j + 3] + p.beta * cv[j].w);
+            if (bias) { o.x += bias[n]; o.y += bias[n + 1]; o.z += bias[n + 2]; o.w += bias[n + 3]; }
+            *dst[j] = o;
+          }
+        }
+      } else if (p.splitk > 1) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (gn0 + j < p.N) {
+            float x = alpha * v[j];
+            if (sp == 0 && bias) x += bias[gn0 + j];
+            atomicAdd(crow + gn0 + j, x);
+          }
+      } else if (vec_ok && gn0 + 32 <= p.N) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 o = make_float4(alpha * v[j], alpha * v[j + 1], alpha * v[j + 2], alpha * v[j + 3]);
+          if (p.beta != 0.f) {
+            const float4 c = *reinterpret_cast<const float4*>(crow + gn0 + j);
+            o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
+          }
+          if (bias) { o.x += bias[gn0 + j]; o.y += bias[gn0 + j + 1]; o.z += bias[gn0 + j + 2]; o.w += bias[gn0 + j + 3]; }
+          *reinterpret_cast<float4*>(crow + gn0 + j) = o;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (gn0 + j < p.N) {
+            float x = alpha * v[j];
+            if (p.beta != 0.f) x += p.beta * crow[gn0 + j];
+            if (bias) x += bias[gn0 + j];
+            crow[gn0 + j] = x;
+          }
+      }
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN, int NPASS>
 __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   using C_ = Cfg<BN, NPASS>;
@@ -395,103 +501,7 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
         mbar_arrive(&tempty[acc]);
         continue;
       }
-      const float* bias = p.bias[bz];
-      bool row_ok = gm < p.M;
-      float* crow;
-      int64_t tl_base = 0;
-      if (p.epi == 1) {                        // tiled: 128-row tile == one batch tile of one timestep
-        const int t = gm / p.tl_Bp, mt = (gm % p.tl_Bp) >> 7;
-        tl_base = ((int64_t)t * (p.tl_Bp >> 7) + mt) * p.tl_G;
-        crow = p.C[bz] + (gm & 127) * 4;
-      } else if (p.rm_Bp > 0) {                // time-major rows -> batch-first C rows
-        const int t = gm / p.rm_Bp, b = gm % p.rm_Bp;
-        row_ok = row_ok && b < p.rm_B;
-        crow = p.C[bz] + ((int64_t)b * p.rm_T + t) * p.ldc;
-      } else {
-        crow = p.C[bz] + (int64_t)gm * p.ldc;
-      }
-      const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C[bz]) & 15) == 0);
-#pragma unroll 1
-      for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c0), v);
-        const int gn0 = n_blk * BN + c0;
-        // plain row-major store of a full 32-column block: transpose the warp's 32x32 block through shared memory so
-        // that 8 lanes write one 128-byte row segment (a TMEM lane is a row: direct stores would put 32 rows, 16 bytes
-        // each, into every instruction).  All conditions are warp-uniform.
-        if (p.epi == 0 && p.splitk == 1 && p.beta == 0.f && p.rm_Bp == 0 && vec_ok && gn0 + 32 <= p.N && kb0 < kb1) {
-          float* T = tr_smem + (warp - 2) * 1024;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float4 o = make_float4(alpha * v[4 * j], alpha * v[4 * j + 1], alpha * v[4 * j + 2], alpha * v[4 * j + 3]);
-            if (bias) { o.x += bias[gn0 + 4 * j]; o.y += bias[gn0 + 4 * j + 1]; o.z += bias[gn0 + 4 * j + 2]; o.w += bias[gn0 + 4 * j + 3]; }
-            *reinterpret_cast<float4*>(T + lane * 32 + ((j ^ (lane & 7)) << 2)) = o;
-          }
-          __syncwarp();
-          const int c4 = lane & 7, rsub = lane >> 3;
-          float* cbase = p.C[bz] + (int64_t)(m_blk * UBM + quarter * 32) * p.ldc + gn0 + 4 * c4;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rr = 4 * i + rsub;
-            const float4 o = *reinterpret_cast<const float4*>(T + rr * 32 + ((c4 ^ (rr & 7)) << 2));
-            if (m_blk * UBM + quarter * 32 + rr < p.M) *reinterpret_cast<float4*>(cbase + (int64_t)rr * p.ldc) = o;
-          }
-          __syncwarp();
-          continue;
-        }
-        if (row_ok && gn0 < p.N && kb0 < kb1) {
-          if (p.epi == 1) {
-            const int hc4 = p.tl_Hc >> 2;
-            float4* dst[8];
-            float4 cv[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {          // all read-modify-write loads first: one L2 round trip, not eight
-              const int n = gn0 + 4 * j;
-              const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
-              dst[j] = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
-              cv[j] = (p.beta != 0.f && n < p.N) ? *dst[j] : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int n = gn0 + 4 * j;
-              if (n < p.N) {
-                float4 o = make_float4(alpha * v[4 * j] + p.beta * cv[j].x, alpha * v[4 * j + 1] + p.beta * cv[j].y,
-                                       alpha * v[4 * j + 2] + p.beta * cv[j].z, alpha * v[4 * j + 3] + p.beta * cv[j].w);
-                if (bias) { o.x += bias[n]; o.y += bias[n + 1]; o.z += bias[n + 2]; o.w += bias[n + 3]; }
-                *dst[j] = o;
-              }
-            }
-          } else if (p.splitk > 1) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (gn0 + j < p.N) {
-                float x = alpha * v[j];
-                if (sp == 0 && bias) x += bias[gn0 + j];
-                atomicAdd(crow + gn0 + j, x);
-              }
-          } else if (vec_ok && gn0 + 32 <= p.N) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 o = make_float4(alpha * v[j], alpha * v[j + 1], alpha * v[j + 2], alpha * v[j + 3]);
-              if (p.beta != 0.f) {
-                const float4 c = *reinterpret_cast<const float4*>(crow + gn0 + j);
-                o.x += p.beta * c.x; o.y += p.beta * c.y; o.z += p.beta * c.z; o.w += p.beta * c.w;
-              }
-              if (bias) { o.x += bias[gn0 + j]; o.y += bias[gn0 + j + 1]; o.z += bias[gn0 + j + 2]; o.w += bias[gn0 + j + 3]; }
-              *reinterpret_cast<float4*>(crow + gn0 + j) = o;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (gn0 + j < p.N) {
-                float x = alpha * v[j];
-                if (p.beta != 0.f) x += p.beta * crow[gn0 + j];
-                if (bias) x += bias[gn0 + j];
-                crow[gn0 + j] = x;
-              }
-          }
-        }
-      }
+      epi_store_tile<BN>(p, tmem_base + (uint32_t)(acc * BN), tr_smem, warp, lane, quarter, chalf, gm, m_blk, n_blk, sp, bz, kb0 < kb1, alpha);
       tc_fence_before();
       mbar_arrive(&tempty[acc]);
     TT_WALK_END
@@ -500,6 +510,148 @@ __global__ void __launch_bounds__(kThreads, 1) umma_gemm_kernel(const __grid_con
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+
+// ------------------------------------------------------------------------------------------ CTA-pair variant (cta_group::2)
+// 256 x 256 x 64 tiles on 2-CTA clusters, K-major operands: each CTA stages its own 128 rows of A and HALF of the B tile
+// (128 of the 256 columns), the leader's single thread issues M = 256 tcgen05.mma.cta_group::2 that read both CTAs' shared
+// memory and write both CTAs' tensor memory; every CTA drains its own 128 x 256 accumulator with the shared epilogue.  Why:
+// the 3-pass GEMMs are bound by operand feed per SM (96 KB of planes per k-block at ~67 GB/s; ncu: tensor pipe 50-76 %
+// active, DRAM 35 %) - a pair pulls 64 KB per CTA and k-block for the same MMAs.  Both batched problems of a row tile run
+// back to back (they share A), so A crosses DRAM once.
+template <int NPASS>
+struct PairCfg {
+  static constexpr int BN = 256;
+  static constexpr int A_BYTES = UBM * UBK * 2;
+  static constexpr int B_BYTES = (BN / 2) * UBK * 2;
+  static constexpr int NPLANES = NPASS == 3 ? 2 : 1;
+  static constexpr int STAGE_BYTES = NPLANES * (A_BYTES + B_BYTES);
+  static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 6 ? 6 : (192 * 1024) / STAGE_BYTES;
+  static constexpr int TR_BYTES = 8 * 32 * 32 * 4;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + TR_BYTES;
+};
+
+template <int NPASS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1) umma_gemm_pair_kernel(const __grid_constant__ UmmaParams p) {
+  using C_ = PairCfg<NPASS>;
+  constexpr int BN = C_::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C_::STAGES * C_::STAGE_BYTES);
+  uint64_t* full = bars;                       // [STAGES]  (the LEADER's are used: bytes of both CTAs' loads)
+  uint64_t* empty = bars + C_::STAGES;         // [STAGES]  (own: multicast commit of the leader's MMAs)
+  uint64_t* tfull = bars + 2 * C_::STAGES;     // [2]       (own: multicast commit)
+  uint64_t* tempty = tfull + 2;                // [2]       (the LEADER's: one arrival per CTA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* tr_smem = reinterpret_cast<float*>(smem + C_::STAGES * C_::STAGE_BYTES + 256);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int MT = (p.M + UBM - 1) / UBM, NT = (p.N + BN - 1) / BN, KB = (p.K + UBK - 1) / UBK;
+  const int MTP = MT >> 1;                     // row-tile pairs (the host guarantees an even MT)
+  const int items = p.nbatch * MTP * NT;
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  // item -> column tile fastest, then the batched problem, then the row-tile pair: consecutive items share A
+#define TT_PAIR_ITEM                                                                             \
+  const int n_blk = it % NT, bz = (it / NT) % p.nbatch, m_blk = 2 * (it / (NT * p.nbatch)) + (int)rank;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < C_::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_pair(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                          // both CTAs' barriers exist before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================================================= TMA producer (both CTAs: own A rows, own half of B)
+    if (lane == 0) {
+      for (int b = 0; b < p.nbatch; ++b) {
+        tma_prefetch_desc(&p.a_hi[b]); tma_prefetch_desc(&p.b_hi[b]);
+        if (NPASS == 3) { tma_prefetch_desc(&p.a_lo[b]); tma_prefetch_desc(&p.b_lo[b]); }
+      }
+      int stage = 0, phase = 0;
+      for (int it = pair; it < items; it += npairs) {
+        TT_PAIR_ITEM
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* st = smem + stage * C_::STAGE_BYTES;
+          uint8_t* sa_hi = st, *sb_hi = st + C_::A_BYTES;
+          uint8_t* sa_lo = st + C_::A_BYTES + C_::B_BYTES, *sb_lo = sa_lo + C_::A_BYTES;
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C_::STAGE_BYTES);
+          int ka = kb * UBK;
+          if (p.a_seg > 0 && ka >= p.a_seg) ka += p.a_skip;
+          if (p.a_seg2 > 0 && kb * UBK >= p.a_seg2) ka += p.a_skip;
+          tma_load_2d_pair(&p.a_hi[bz], &full[stage], sa_hi, ka, m_blk * UBM + p.a_row0[bz]);
+          if (NPASS == 3) tma_load_2d_pair(&p.a_lo[bz], &full[stage], sa_lo, ka, m_blk * UBM + p.a_row0[bz]);
+          tma_load_2d_pair(&p.b_hi[bz], &full[stage], sb_hi, kb * UBK, n_blk * BN + (int)rank * (BN / 2) + p.b_row0);
+          if (NPASS == 3) tma_load_2d_pair(&p.b_lo[bz], &full[stage], sb_lo, kb * UBK, n_blk * BN + (int)rank * (BN / 2) + p.b_row0);
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================= MMA issuer (one thread of the pair)
+    if (lane == 0 && leader) {
+      const uint32_t idesc = p.idesc;            // M = 256, N = 256
+      int stage = 0, phase = 0, tile = 0;
+      for (int it = pair; it < items; it += npairs, ++tile) {
+        const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+        mbar_wait_cluster(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t st = smem_u32(smem + stage * C_::STAGE_BYTES);
+          const uint32_t sa_hi = st, sb_hi = st + C_::A_BYTES;
+          const uint32_t sa_lo = st + C_::A_BYTES + C_::B_BYTES, sb_lo = sa_lo + C_::A_BYTES;
+#pragma unroll
+          for (int term = 0; term < NPASS; ++term) {
+            const uint32_t sa = term == 1 ? sa_lo : sa_hi;
+            const uint32_t sb = term == 2 ? sb_lo : sb_hi;
+#pragma unroll
+            for (int k = 0; k < UBK / 16; ++k)
+              mma_f16_ss_pair(d_tmem, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                              (kb > 0 || term > 0 || k > 0) ? 1u : 0u);
+          }
+          mma_commit_pair(&empty[stage], 3);     // both CTAs' stage is reusable once these MMAs have read it
+          if (++stage == C_::STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit_pair(&tfull[acc], 3);         // accumulator complete in both CTAs -> their epilogues
+      }
+    }
+  } else {
+    // ================================================================= epilogue (warps 2..9 of both CTAs: own 128 rows)
+    const int quarter = warp & 3, chalf = (warp - 2) >> 2;
+    const int row = quarter * 32 + lane;
+    const float alpha = p.alpha * (p.alpha_ptr ? __ldg(p.alpha_ptr) : 1.f);
+    int tile = 0;
+    for (int it = pair; it < items; it += npairs, ++tile) {
+      TT_PAIR_ITEM
+      const int acc = tile & 1, acc_phase = (tile >> 1) & 1;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      epi_store_tile<BN>(p, tmem_base + (uint32_t)(acc * BN), tr_smem, warp, lane, quarter, chalf, m_blk * UBM + row, m_blk, n_blk, 0, bz,
+                         true, alpha);
+      tc_fence_before();
+      named_bar_sync(1, 256);
+      if (threadIdx.x == 64) {
+        if (leader) mbar_arrive(&tempty[acc]);
+        else mbar_arrive_leader(&tempty[acc]);
+      }
+    }
+  }
+#undef TT_PAIR_ITEM
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                          // nobody leaves (or frees tensor memory) while the pair's MMAs / commits may touch it
+  if (warp == 1) tmem_dealloc_pair(tmem_base, 512);
 }
 
 
@@ -566,6 +718,27 @@ static int launch_cfg(const UmmaParams& p, int items, int max_ctas, cudaStream_t
   return TT_OK;
 }
 
+template <int NPASS>
+static int launch_pair(const UmmaParams& p, int items, int max_ctas, cudaStream_t s) {
+  auto kern = umma_gemm_pair_kernel<NPASS>;
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
+    TT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<NPASS>::SMEM_BYTES));
+    attr_once.done();
+  }
+  const int num_sms = device_sm_count();
+  const int cap = (max_ctas > 0 && max_ctas < num_sms) ? max_ctas : num_sms;
+  int pairs = cap / 2;
+  if (items < pairs) pairs = items;
+  if (pairs < 1) pairs = 1;
+  note_launch();
+  prof_begin_gemm(s, p.M, p.N, p.K, p.nbatch, NPASS, (p.epi << 4) | 512);       // flag 512: CTA pairs
+  ProfScope prof(PROF_GEMM_TC, s);
+  kern<<<2 * pairs, kThreads, PairCfg<NPASS>::SMEM_BYTES, s>>>(p);
+  TT_LAUNCH_CHECK();
+  return TT_OK;
+}
+
 static_assert(sizeof(UmmaParams) <= sizeof(((UmmaPrepared*)0)->blob), "UmmaPrepared blob too small");
 
 static int sm_count() {
@@ -575,6 +748,8 @@ static int sm_count() {
 static int g_sel_resident = 1, g_sel_prefetch = 4, g_sel_bn128 = 0;   // 128-column tiles x 4 accumulators measured slower (7.8 vs 5.65 ms)
 void umma_set_sel_resident(int on) { g_sel_resident = on ? 1 : 0; g_sel_bn128 = (on & 4) ? 1 : 0; }
 void umma_set_sel_prefetch(int tiles) { g_sel_prefetch = tiles < 0 ? 0 : tiles; }
+static int g_gemm_pairs = 1;             // 1: large K-major GEMMs run on 2-CTA clusters (umma_gemm_pair_kernel)
+void umma_set_pairs(int on) { g_gemm_pairs = on ? 1 : 0; }
 
 bool umma_sel_two_ok(int32_t K) { return g_sel_resident && ceil_div(K, UBK) <= 2; }
 
@@ -596,6 +771,9 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   int BN = g.N <= 128 ? 128 : 256;
   if (g.epi == 2 && g_sel_bn128 && g_sel_resident && KB <= 2) BN = 128;      // 4 accumulators in flight (see the kernel)
   if (BN == 256 && g.splitk == 1 && MT * ceil_div(g.N, 256) * g.nbatch < 100 && (g.N % 256) == 0 && g.epi != 2) BN = 128;
+  // CTA pairs: K-major operands, 256-column tiles, an even number of row tiles and enough of them to fill the GPU
+  const bool pair = g_gemm_pairs && BN == 256 && !g.a_mn && !g.b_mn && g.epi != 2 && g.splitk == 1 && (MT % 2) == 0 &&
+                    (int64_t)MT * ceil_div(g.N, 256) * g.nbatch >= 2 * 148;
   UmmaParams& p = *reinterpret_cast<UmmaParams*>(out->blob);
   const int f16 = g.f16;
   const int64_t skipA = g.a_seg > 0 ? (int64_t)g.a_skip * (g.a_seg2 > 0 ? 2 : 1) : 0;
@@ -612,8 +790,8 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     }
     if (!g.b_mn) {
       const int64_t rows = g.b_rows > 0 ? g.b_rows : g.N;
-      TT_TRY(make_plane_map(&p.b_hi[b], g.B[b].hi, rows, g.K, g.B[b].pitch, BN, f16));
-      if (npass == 3) TT_TRY(make_plane_map(&p.b_lo[b], g.B[b].lo, rows, g.K, g.B[b].pitch, BN, f16));
+      TT_TRY(make_plane_map(&p.b_hi[b], g.B[b].hi, rows, g.K, g.B[b].pitch, pair ? BN / 2 : BN, f16));
+      if (npass == 3) TT_TRY(make_plane_map(&p.b_lo[b], g.B[b].lo, rows, g.K, g.B[b].pitch, pair ? BN / 2 : BN, f16));
     } else {
       const int64_t rows = g.b_rows > 0 ? g.b_rows : g.K;
       TT_TRY(make_plane_map(&p.b_hi[b], g.B[b].hi, rows, g.N, g.B[b].pitch, 64, f16));
@@ -624,7 +802,8 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
   p.ldc = g.ldc; p.M = g.M; p.N = g.N; p.K = g.K; p.nbatch = g.nbatch; p.alpha = g.alpha; p.beta = g.beta;
   p.alpha_ptr = g.alpha_ptr; p.b_row0 = g.b_row0; p.a_seg = g.a_seg; p.a_skip = g.a_skip; p.a_seg2 = g.a_seg2;
   p.epi = g.epi; p.rm_Bp = g.rm_Bp; p.rm_B = g.rm_B; p.rm_T = g.rm_T; p.tl_Bp = g.tl_Bp; p.tl_G = g.tl_G; p.tl_Hc = g.tl_Hc;
-  p.idesc = f16 ? make_idesc_f16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0) : make_idesc_bf16(UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0);
+  p.idesc = f16 ? make_idesc_f16(pair ? 2 * UBM : UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0)
+                : make_idesc_bf16(pair ? 2 * UBM : UBM, BN, g.a_mn ? 1 : 0, g.b_mn ? 1 : 0);
   if (g.epi == 1)
     TT_CHECK_ARG(g.splitk == 1 && (g.tl_Bp % 128) == 0 && (g.tl_Hc % 4) == 0 && (g.N % 4) == 0 && (g.M % 128) == 0,
                  "umma_gemm: tiled epilogue needs splitk 1, Bp %% 128 == 0, Hc %% 4 == 0");
@@ -670,6 +849,10 @@ int umma_gemm_prepare(const UmmaGemm& g, UmmaPrepared* out) {
     return TT_ERR_INVALID;
   }
   out->kind = (BN == 128 ? 0 : 8) + (npass == 1 ? 4 : 0) + major;
+  if (pair) {
+    out->kind = npass == 1 ? 17 : 16;
+    out->items = (MT / 2) * NT * g.nbatch;
+  }
   out->max_ctas = g.max_ctas;
   return TT_OK;
 }
@@ -701,6 +884,8 @@ int umma_gemm_launch(const UmmaPrepared& prep, const int* a_row0, cudaStream_t s
     case 12: return launch_cfg<256, false, false, 1>(p, items, prep.max_ctas, s);
     case 13: return launch_cfg<256, true, true, 1>(p, items, prep.max_ctas, s);
     case 14: return launch_cfg<256, false, true, 1>(p, items, prep.max_ctas, s);
+    case 16: return launch_pair<3>(p, items, prep.max_ctas, s);
+    case 17: return launch_pair<1>(p, items, prep.max_ctas, s);
   }
   set_error("umma_gemm: bad prepared kind %d", prep.kind);
   return TT_ERR_INVALID;

@@ -67,6 +67,7 @@ struct UmmaGemm {
 };
 bool umma_sel_two_ok(int32_t K);
 int umma_sel_slots(int32_t M, int64_t N);
+void umma_set_pairs(int on);            // 1 (default): large K-major GEMMs on 2-CTA clusters (cta_group::2)
 void umma_set_sel_prefetch(int tiles); // epi == 2, resident A: L2 prefetch distance in column tiles (0 = off)
 void umma_set_sel_resident(int on);   // epi == 2: keep the unit's A tile in shared memory (default on; off = stream it per tile)
 int umma_gemm(const UmmaGemm& g, cudaStream_t s);
