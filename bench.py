@@ -665,13 +665,21 @@ def run_ours(args):
     # the loss of step i goes to a pinned host slot with an async copy right after the step is queued and is READ on
     # the host while step i+1 runs (one-step-late logging, as a training loop would do it): one D2H read per step
     # inside the timed region, but the host never drains the launch queue between steps
-    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
-    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+    LAG = max(1, int(os.environ.get("TT_E2E_LAG", "1")))          # how many steps late a loss is read (measurement knob)
+    NS = LAG + 1
+    loss_host = torch.empty(NS, dtype=torch.float32).pin_memory()
+    loss_ev = [torch.cuda.Event() for _ in range(NS)]
     losses = []
     dbg = os.environ.get("TT_E2E_DEBUG") == "1"
     marks = []
+    sampler2 = ClockSampler(local)
+    sampler2.start()
+    time.sleep(0.3)
+    ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    sampler2.mark_begin()
     t0 = time.perf_counter()
+    ee0.record(st)
     nxt = upload(0)
     t_up0 = time.perf_counter()
     for i in range(args.steps):
@@ -685,26 +693,32 @@ def run_ours(args):
         slot_free[i & 1] = torch.cuda.Event()
         slot_free[i & 1].record(st)
         tc = time.perf_counter()
-        loss_host[i & 1].copy_(loss.detach(), non_blocking=True)
-        loss_ev[i & 1].record(st)
-        if i > 0:
-            loss_ev[(i - 1) & 1].synchronize()
-            losses.append(float(loss_host[(i - 1) & 1]))
+        loss_host[i % NS].copy_(loss.detach(), non_blocking=True)
+        loss_ev[i % NS].record(st)
+        if i >= LAG:
+            loss_ev[(i - LAG) % NS].synchronize()
+            losses.append(float(loss_host[(i - LAG) % NS]))
         if dbg:
             marks.append((round((tb - ta) * 1e3, 2), round((tc - tb) * 1e3, 2), round((time.perf_counter() - tc) * 1e3, 2)))
     t_loop = time.perf_counter()
-    loss_ev[(args.steps - 1) & 1].synchronize()
-    losses.append(float(loss_host[(args.steps - 1) & 1]))
+    for j in range(max(0, args.steps - LAG), args.steps):
+        loss_ev[j % NS].synchronize()
+        losses.append(float(loss_host[j % NS]))
     if dbg and rank == 0:
         print("e2e ms: first upload %.2f, loop %.2f, last loss %.2f" % ((t_up0 - t0) * 1e3, (t_loop - t_up0) * 1e3,
                                                                         (time.perf_counter() - t_loop) * 1e3), file=sys.stderr)
         print("e2e per-step host ms (upload, launch of the step, loss copy + wait for the previous loss):", marks, file=sys.stderr)
     loss_val = losses[-1]
+    ee1.record(st)
     t_b = time.perf_counter()
     barrier()
+    e2e_wall = time.perf_counter() - t0
+    sampler2.mark_end()
+    clocks_e2e = sampler2.stop()
+    e2e_dev_ms = ee0.elapsed_time(ee1) / args.steps
     if dbg and rank == 0:
         print("e2e ms: closing barrier %.2f" % ((time.perf_counter() - t_b) * 1e3), file=sys.stderr)
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    e2e_s = torch.tensor([e2e_wall], device=dev)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_val = world * B * args.steps / e2e_s.item()
@@ -717,6 +731,7 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32 accumulate; forward GEMMs as 3 fp16 hi/lo tensor passes, backward GEMMs 1 fp16 pass",
             "data": "synthetic", "config": workload_config(B, world, V),
             "e2e": {"value": e2e_val, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "device_ms_per_step": e2e_dev_ms, "clocks": clocks_e2e,
                     "note": "wall clock over K steps through the nn.Module API: pinned int64 ids -> device on a copy stream "
                             "(one step ahead), every step's loss copied to pinned memory and read on the host one step late"},
             "gpu_launches": launches, "host_queue_ms_per_step": host_launch_ms, "clocks": clocks, "loss": loss_val,
