@@ -59,6 +59,23 @@ def peaks():
     return dict(hbm=6650.0, bf16_burst=1590.0, bf16_sustained=1400.0, src="fallback")
 
 
+def make_pair_ids(B, Tq, Td, V, gen):
+    """A (query, relevant doc) batch: the doc is random text that CONTAINS the query's tokens (a contiguous window at a random
+    position), as a relevant passage shares words with its query.  With independent random queries and docs there is nothing to
+    learn: the loss stays at ln(B_global), the embeddings drift together and the in-batch scores become near-ties, which is
+    neither what training looks like nor neutral for the timing (rows whose top-k cannot be separated within the tensor
+    route's error bound take the exact re-scan)."""
+    q, d = make_ids(B, Tq, V, gen), make_ids(B, Td, V, gen)
+    qlen, dlen = (q != 0).sum(1), (d != 0).sum(1)
+    n = torch.minimum(qlen, dlen)
+    start = (torch.rand(B, generator=gen) * (dlen - n + 1).float()).long()
+    j = torch.arange(Tq).unsqueeze(0)
+    pos = (start.unsqueeze(1) + j).clamp_(max=Td - 1)
+    keep = j < n.unsqueeze(1)
+    d.scatter_(1, pos, torch.where(keep, q, d.gather(1, pos)))
+    return q, d
+
+
 def make_ids(B, T, V, gen):
     """Power-law (Zipf-like) ids in [1,V), length ~U[T/4,T], pad id 0 after the length (still processed)."""
     u = torch.rand(B, T, generator=gen)
@@ -131,7 +148,7 @@ def cpu_reference(steps, warmup, B, seed=1234):
     V = 13085
     table = torch.randn(V, E, generator=gen) * 0.1
     table[0] = 0
-    batches = [(table[make_ids(B, TQ, V, gen)], table[make_ids(B, TD, V, gen)]) for _ in range(2)]
+    batches = [tuple(table[t] for t in make_pair_ids(B, TQ, TD, V, gen)) for _ in range(2)]
     times = []
     for i in range(warmup + steps):
         q, d = batches[i % 2]
@@ -200,7 +217,7 @@ def torch_gpu_arm(args, steps, warmup):
     gen = torch.Generator().manual_seed(1234)
     table = torch.empty(V, E, device=dev).normal_(0, 0.1, generator=torch.Generator(device=dev).manual_seed(7))
     table[0] = 0
-    ids = [(make_ids(B, TQ, V, gen).to(dev), make_ids(B, TD, V, gen).to(dev)) for _ in range(4)]
+    ids = [tuple(t.to(dev) for t in make_pair_ids(B, TQ, TD, V, gen)) for _ in range(4)]
     eye = torch.eye(B, device=dev)
     for tf32 in (True, False):
         torch.backends.cudnn.allow_tf32 = tf32
@@ -471,7 +488,7 @@ def secondary_configs(args, dev, table, graphed):
             crit = mkloss()
             gen = torch.Generator().manual_seed(4321)
             V = tab.shape[0]
-            ids = [(make_ids(B, Tq, V, gen).to(dev), make_ids(B, Td, V, gen).to(dev)) for _ in range(4)]
+            ids = [tuple(t.to(dev) for t in make_pair_ids(B, Tq, Td, V, gen)) for _ in range(4)]
             results = {}
             for mode in (["graph", "eager"] if graphed else ["eager"]):
                 opt = mkopt(model.parameters(), mode == "graph")
@@ -553,7 +570,7 @@ def run_ours(args):
         torch.optim.Adam(model.parameters(), fused=True)
     reducer = dops.GradientAllReducer(None, group, named_params=model.named_parameters()) if world > 1 else None
     nb = 4
-    host = [(make_ids(B, TQ, V, gen).pin_memory(), make_ids(B, TD, V, gen).pin_memory()) for _ in range(nb)]
+    host = [tuple(t.pin_memory() for t in make_pair_ids(B, TQ, TD, V, gen)) for _ in range(nb)]
     resident = [(q.to(dev), d.to(dev)) for q, d in host]
     resident_shape = host[0]
 
@@ -580,15 +597,48 @@ def run_ours(args):
     elif graphed:
         towers = tt.GraphedTowers(model)
 
+    seg = []                                  # TT_E2E_DEBUG=1: CUDA events at the phase boundaries of every step
+    dbg_losses = []
+
+    def _mark(row):
+        if os.environ.get("TT_E2E_DEBUG") == "1":
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(torch.cuda.current_stream())
+            row.append(e)
+
     def towers_step(q, d):
+        row = []
+        _mark(row)
         opt.zero_grad(set_to_none=True)
         qv, dv = towers(q, d)
+        _mark(row)
         loss = crit(qv, dv)
-        hard = tt.get_hard_negatives_batch(qv.detach(), dops.all_gather_rows(dv.detach(), group), k=TOPK, pos_offset=rank * B)
+        _mark(row)
+        docs_all = dops.all_gather_rows(dv.detach(), group)
+        _mark(row)
+        hard = tt.get_hard_negatives_batch(qv.detach(), docs_all, k=TOPK, pos_offset=rank * B)
+        _mark(row)
         loss.backward()
+        _mark(row)
         reducer.finish()
+        _mark(row)
         opt.step()
+        _mark(row)
+        seg.append(row)
+        if os.environ.get("TT_E2E_DEBUG") == "1":
+            dbg_losses.append(loss.detach().clone())
         return loss, hard
+
+    def seg_report(tag, rows):
+        if not rows or not rows[0] or rank != 0:
+            return
+        torch.cuda.synchronize()
+        names = ["towers fwd (graph)", "loss fwd (all-gather, CE)", "all-gather of the docs", "mining top-k", "backward (CE, reduce-scatter, towers graph)",
+                 "reducer.finish", "optimizer"]
+        n = len(rows)
+        avg = [sum(r[j].elapsed_time(r[j + 1]) for r in rows) / n for j in range(len(names))]
+        gaps = sum(a[-1].elapsed_time(b[0]) for a, b in zip(rows, rows[1:])) / max(1, n - 1)
+        print(f"[segments] {tag}: " + "; ".join(f"{nm} {v:.2f}" for nm, v in zip(names, avg)) + f"; between steps {gaps:.2f} ms", file=sys.stderr)
 
     step = gstep if gstep is not None else (towers_step if towers is not None else eager_step)
 
@@ -596,6 +646,25 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # Both timed loops run the SAME training steps (W warm-up + K timed from the same initial weights and optimizer state): the
+    # step is not data-independent - on synthetic pairs this recipe collapses to constant scores after a few dozen steps
+    # (loss = ln(B_global) - margin), every row's top-8 is then a near-tie below the tensor route's error bound and the mining
+    # takes the exact scan for ALL rows (0.9 -> 4.2 ms at 8 GPUs, tools/mining_probe.py) - so a loop that starts where the
+    # other one ended, or that draws other dropout masks, would measure a different mix of the two regimes.
+    init_params = [p.detach().clone() for p in model.parameters()]
+
+    def reset_training_state():
+        with torch.no_grad():
+            for p, v in zip(model.parameters(), init_params):
+                p.copy_(v)                                  # in place: captured graphs, buckets and Adam tables keep their pointers
+            for stt in opt.state.values():
+                for v in stt.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+            for obj in (gstep, towers):                     # same dropout masks again: the device-side seed offset of the graphs
+                if obj is not None and getattr(obj, "_seed", None) is not None:
+                    obj._seed.zero_()
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -614,6 +683,10 @@ def run_ours(args):
     host_launch_ms = (time.perf_counter() - th0) * 1e3 / args.steps     # host time to QUEUE a step (no sync inside)
     e1.record(st)
     barrier()
+    seg_report("resident loop", seg[-args.steps:])
+    if dbg_losses and rank == 0:
+        print("[losses] warm-up + resident loop:", [round(float(v), 3) for v in dbg_losses], file=sys.stderr)
+    del seg[:], dbg_losses[:]
     launches = int(lib.tt_kernel_launches() - k0)
     if gstep is not None:
         launches = int(gstep.launches_per_replay(*resident[0]) or 0) * args.steps      # replays do not pass through the host counter
@@ -621,21 +694,6 @@ def run_ours(args):
         launches += int(towers.launches_per_replay(*resident[0]) or 0) * args.steps     # eager part counted above + the two replays
     sampler.mark_end()
     clocks = sampler.stop()
-    # ---- dominant-kernel timing: the same K steps again with the towers on ONE stream (kernel durations under
-    # two-stream overlap would include time-slicing with the other tower), CUDA events around every launch
-    model.overlap_towers = False
-    lib.tt_debug_wgrad_overlap(0)
-    eager_step(*resident[0])
-    barrier()
-    lib.tt_prof_enable(1)
-    for i in range(args.steps):
-        eager_step(*resident[i % nb])
-    barrier()
-    roofs, fams = kernel_rooflines(lib, args.steps, B, peaks())
-    gemm_rows, gemm_roof = gemm_table(lib, args.steps, peaks())
-    lib.tt_prof_enable(0)
-    lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
-    model.overlap_towers = not args.serial_towers
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
@@ -668,13 +726,19 @@ def run_ours(args):
     LAG = max(1, int(os.environ.get("TT_E2E_LAG", "1")))          # how many steps late a loss is read (measurement knob)
     NS = LAG + 1
     loss_host = torch.empty(NS, dtype=torch.float32).pin_memory()
-    loss_ev = [torch.cuda.Event() for _ in range(NS)]
+    # blocking events: the host thread sleeps in synchronize() instead of spinning (8 ranks share the box's cores with their
+    # NCCL / sampler threads)
+    loss_ev = [torch.cuda.Event(blocking=True) for _ in range(NS)]
     losses = []
     dbg = os.environ.get("TT_E2E_DEBUG") == "1"
-    marks = []
+    marks, step_done = [], []
     sampler2 = ClockSampler(local)
     sampler2.start()
-    time.sleep(0.3)
+    reset_training_state()
+    for i in range(args.warmup):
+        step(*resident[i % nb])
+    torch.cuda.synchronize()
+    time.sleep(0.2)
     ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     sampler2.mark_begin()
@@ -689,11 +753,17 @@ def run_ours(args):
             nxt = upload(i + 1)
         st.wait_event(ev)
         tb = time.perf_counter()
+        if os.environ.get("TT_E2E_RESIDENT") == "1":              # diagnosis only: the step reads the resident copy instead
+            qd, dd = resident[i % nb]
         loss, _ = step(qd, dd)
         slot_free[i & 1] = torch.cuda.Event()
         slot_free[i & 1].record(st)
         tc = time.perf_counter()
-        loss_host[i % NS].copy_(loss.detach(), non_blocking=True)
+        if dbg:
+            step_done.append(torch.cuda.Event(enable_timing=True))
+            step_done[-1].record(st)
+        if os.environ.get("TT_E2E_NOLOSS") != "1":                # diagnosis only
+            loss_host[i % NS].copy_(loss.detach(), non_blocking=True)
         loss_ev[i % NS].record(st)
         if i >= LAG:
             loss_ev[(i - LAG) % NS].synchronize()
@@ -708,6 +778,14 @@ def run_ours(args):
         print("e2e ms: first upload %.2f, loop %.2f, last loss %.2f" % ((t_up0 - t0) * 1e3, (t_loop - t_up0) * 1e3,
                                                                         (time.perf_counter() - t_loop) * 1e3), file=sys.stderr)
         print("e2e per-step host ms (upload, launch of the step, loss copy + wait for the previous loss):", marks, file=sys.stderr)
+        seg_report("e2e loop", seg[-args.steps:])
+        print("[losses] warm-up + e2e loop:", [round(float(v), 3) for v in dbg_losses], file=sys.stderr)
+        torch.cuda.synchronize()
+        tk = [r[3].elapsed_time(r[4]) for r in seg[-args.steps:]]
+        print("[mining top-k ms per e2e step]", [round(v, 2) for v in tk], file=sys.stderr)
+        torch.cuda.synchronize()
+        print("e2e device ms between consecutive step ends:", [round(a.elapsed_time(b), 2) for a, b in zip(step_done, step_done[1:])],
+              file=sys.stderr)
     loss_val = losses[-1]
     ee1.record(st)
     t_b = time.perf_counter()
@@ -722,6 +800,22 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_val = world * B * args.steps / e2e_s.item()
+    # ---- dominant-kernel timing (LAST: its eager passes change allocator / library state, and the two timed loops above
+    # must see the same state): the same K steps again with the towers on ONE stream (kernel durations under
+    # two-stream overlap would include time-slicing with the other tower), CUDA events around every launch
+    model.overlap_towers = False
+    lib.tt_debug_wgrad_overlap(0)
+    eager_step(*resident[0])
+    barrier()
+    lib.tt_prof_enable(1)
+    for i in range(args.steps):
+        eager_step(*resident[i % nb])
+    barrier()
+    roofs, fams = kernel_rooflines(lib, args.steps, B, peaks())
+    gemm_rows, gemm_roof = gemm_table(lib, args.steps, peaks())
+    lib.tt_prof_enable(0)
+    lib.tt_debug_wgrad_overlap(0 if args.serial_towers else 1)
+    model.overlap_towers = not args.serial_towers
     h2d = B * (TQ + TD) * 8
     if rank == 0:
         pk = peaks()
