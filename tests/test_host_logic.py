@@ -132,3 +132,38 @@ def test_single_process_collectives_are_identity():
     assert dops.all_gather_rows(x) is x
     assert dops.sum_over_ranks(x.sum()) is not None
     assert dops.shard_bounds(10) == (0, 10)
+
+
+def test_engine_selection_api():
+    """set_engine / use_engine (the Python face of tt_set_engine): names and numbers, restore on exit, bad values raise."""
+    import two_towers_b200 as tt
+    assert tt.engine() == "tcgen05-f16x3-fwd/f16-bwd"
+    prev = tt.set_engine(0)
+    try:
+        assert prev == 2 and tt.engine() == "simt-fp32"
+        with tt.use_engine("tcgen05-bf16x3"):
+            assert tt.engine() == "tcgen05-bf16x3"
+        assert tt.engine() == "simt-fp32"
+        with pytest.raises(RuntimeError):
+            tt.set_engine(7)
+    finally:
+        tt.set_engine(prev)
+    assert tt.engine() == "tcgen05-f16x3-fwd/f16-bwd"
+
+
+def test_bench_synthetic_pairs_share_the_query_tokens():
+    """bench.py's synthetic (query, relevant doc) batches: each doc contains its query's tokens as a contiguous window, pads
+    stay at the end, shapes / dtype as the model's id inputs."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(os.path.dirname(__file__)), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    g = torch.Generator().manual_seed(3)
+    q, d = bench.make_pair_ids(64, 32, 128, 50000, g)
+    assert q.shape == (64, 32) and d.shape == (64, 128) and q.dtype == torch.int64
+    for i in range(64):
+        ql, dl = int((q[i] != 0).sum()), int((d[i] != 0).sum())
+        assert (q[i, ql:] == 0).all() and (d[i, dl:] == 0).all() and ql >= 8 and dl >= 32
+        n = min(ql, dl)
+        row, want = d[i, :dl].tolist(), q[i, :n].tolist()
+        assert any(row[s:s + n] == want for s in range(dl - n + 1)), i

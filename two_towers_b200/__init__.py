@@ -3,6 +3,7 @@
 Python mirrors the reference's nn.Module / loss surface; all arithmetic runs in libtt_b200.so (hand-written
 CUDA behind the C ABI of include/tt_b200.h).  There is no CPU or stock-torch fallback."""
 from . import functional  # noqa: F401
+from .functional import engine, set_engine, use_engine  # noqa: F401
 from .graph import GraphedTowers, GraphedTrainStep  # noqa: F401
 from .gru import GRU  # noqa: F401
 from .losses import (InfoNCELoss, MarginRankingLoss, SymmetricInfoNCELoss, get_hard_negatives,  # noqa: F401

@@ -449,3 +449,42 @@ def gemm_nt(a, b, bias=None, alpha=1.0):
     c = torch.empty(M, N, device=a.device, dtype=torch.float32)
     L.run(a.device, lib.tt_gemm_nt, "tt_gemm_nt", L.ptr(a), K, L.ptr(b), K, L.ptr(c), N, L.ptr(bias), M, N, K, alpha, 0.0)
     return c
+
+
+# ------------------------------------------------------------------------------------------- arithmetic engine
+_ENGINES = {"simt-fp32": 0, "tcgen05-bf16x3": 1, "tcgen05-f16x3-fwd/f16-bwd": 2}
+
+
+def engine():
+    """Name of the arithmetic engine the library is using (`tt_engine`)."""
+    return L.lib().tt_engine().decode()
+
+
+def set_engine(mode):
+    """Process-wide choice of the arithmetic engine (`tt_set_engine`):
+      2  default - tcgen05 GEMMs on fp16 hi/lo planes, three passes forward, ONE fp16 pass on loss-scaled gradients backward.
+         This is the training-precision deviation from the fp32 reference: gradients agree to ~4e-4..8e-4 relative (north-star
+         bound 1e-3), and values beyond the fp16 range (|x| >= 65504) overflow - FusedAdam(skip_nonfinite=True) then skips
+         the step instead of corrupting the weights;
+      1  tcgen05 bf16 x3 in both directions (~fp32 accuracy, bf16 range, several times slower: per-timestep kernels);
+      0  exact fp32 SIMT kernels (the on-device oracle of the parity tests; ~17x slower).
+    Accepts the number or the engine's name; returns the previous engine's number."""
+    prev = _ENGINES[engine()]
+    m = _ENGINES[mode] if isinstance(mode, str) else int(mode)
+    L.check(L.lib().tt_set_engine(m), "tt_set_engine")
+    return prev
+
+
+class use_engine:
+    """`with use_engine(0): ...` - run a block on another engine (e.g. re-run a step that produced non-finite gradients on the
+    exact engine) and restore the previous one."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = set_engine(self.mode)
+        return self
+
+    def __exit__(self, *exc):
+        set_engine(self.prev)
