@@ -169,13 +169,23 @@ __device__ __forceinline__ void epi_store_tile(const UmmaParams& p, uint32_t tme
       if (p.epi == 1) {
         const int hc4 = p.tl_Hc >> 2;
         float4* dst[8];
-        float4 cv[8];
+        float4 cv[8], bv[8];
+        // (gate, unit) of column n = gn0 + 4 j: ONE division per 32-column block, then steps of 4 with a wrap (eight runtime
+        // divisions per block made this loop longer than the MMAs of a K = 300 tile: ncu, tensor pipe 50 % active)
+        int g = gn0 / p.tl_Hc, u = gn0 - g * p.tl_Hc;
+        const bool bias4 = bias && (reinterpret_cast<uintptr_t>(bias) & 15) == 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {          // all read-modify-write loads first: one L2 round trip, not eight
+        for (int j = 0; j < 8; ++j) {          // all loads first (read-modify-write values, bias): one L2 round trip, not eight
           const int n = gn0 + 4 * j;
-          const int g = n / p.tl_Hc, u = n - g * p.tl_Hc;
           dst[j] = reinterpret_cast<float4*>(crow + ((tl_base + g) * hc4 + (u >> 2)) * 512);
           cv[j] = (p.beta != 0.f && n < p.N) ? *dst[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+          bv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (bias && n < p.N) {
+            if (bias4) bv[j] = __ldg(reinterpret_cast<const float4*>(bias + n));
+            else bv[j] = make_float4(bias[n], bias[n + 1], bias[n + 2], bias[n + 3]);
+          }
+          u += 4;
+          while (u >= p.tl_Hc) { u -= p.tl_Hc; ++g; }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -183,7 +193,7 @@ __device__ __forceinline__ void epi_store_tile(const UmmaParams& p, uint32_t tme
           if (n < p.N) {
             float4 o = make_float4(alpha * v[4 * j] + p.beta * cv[j].x, alpha * v[4 * j + 1] + p.beta * cv[j].y,
                                    alpha * v[4 * j + 2] + p.beta * cv[j].z, alpha * v[4 * j + 3] + p.beta * cv[j].w);
-            if (bias) { o.x += bias[n]; o.y += bias[n + 1]; o.z += bias[n + 2]; o.w += bias[n + 3]; }
+            o.x += bv[j].x; o.y += bv[j].y; o.z += bv[j].z; o.w += bv[j].w;
             *dst[j] = o;
           }
         }
