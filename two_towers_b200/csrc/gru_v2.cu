@@ -76,24 +76,6 @@ __device__ __forceinline__ void split8(const float (&x)[8], uint4& hi, uint4& lo
   lo = make_uint4(pack_h2(l[0], l[1]), pack_h2(l[2], l[3]), pack_h2(l[4], l[5]), pack_h2(l[6], l[7]));
 }
 
-// 16-bit fixed point for saved gates: r, z in [0,1] -> u16 ; n in [-1,1], q = h - n in [-2,2] -> 16-bit offset binary
-// (stored = round(x * scale) + 32768).  Conversions go through the mantissa of 2^23 (magic-number add / or) on the
-// FMA and ALU pipes: F2I / I2F issue at 16 per clock and SM on the XU pipe, which was the busiest pipe of both
-// persistent kernels (it also carries the ex2 / rcp of the gate activations).
-__device__ __forceinline__ uint32_t q_u16(float x) { return __float_as_uint(fmaf(__saturatef(x), 65535.f, 8388608.f)) & 0xFFFFu; }
-__device__ __forceinline__ uint32_t q_s16(float x, float scale) {
-  const float lim = 32767.f / scale;
-  return __float_as_uint(fmaf(fminf(fmaxf(x, -lim), lim), scale, 8388608.f + 32768.f)) & 0xFFFFu;
-}
-__device__ __forceinline__ float dq_u16(uint32_t v) {                      // low 16 bits of v
-  constexpr float c = 1.f / 65535.f;
-  return fmaf(__uint_as_float((v & 0xFFFFu) | 0x4B000000u), c, -8388608.f * c);   // == float(v16) * c, one rounding
-}
-__device__ __forceinline__ float dq_s16(uint32_t v, float inv_scale) {
-  return (__uint_as_float((v & 0xFFFFu) | 0x4B000000u) - (8388608.f + 32768.f)) * inv_scale;
-}
-constexpr float kNScale = 32767.f, kQScale = 16383.5f;
-
 // ---- saved gate records (what the BPTT needs of a forward step), five 16-bit planes of 8 units per 16-byte word:
 //   Z = z, R = r                       u16, x 65535
 //   A = (1 - z)(1 - n^2)               u16, x 65535          dn_pre       = dh * A
@@ -108,6 +90,8 @@ constexpr float kNScale = 32767.f, kQScale = 16383.5f;
 // k starts k * g16_plane words further on.
 enum { GP_Z = 0, GP_R = 1, GP_A = 2, GP_C = 3, GP_B = 4, GP_PLANES = 5 };
 constexpr float kCScale = 65000.f;
+// 16-bit fixed-point codes through the mantissa of 2^23 (magic-number FMA, PRMT to unpack) on the FMA / ALU pipes: F2I / I2F
+// issue at 16 per clock and SM on the XU pipe, which also carries the ex2 / rcp of the gate activations.
 // quantisers without clamps (the value ranges are guaranteed by construction); the result's LOW 16 bits are the code
 __device__ __forceinline__ uint32_t qf_u16(float x) { return __float_as_uint(fmaf(x, 65535.f, 8388608.f)); }
 __device__ __forceinline__ uint32_t qf_s16(float x, float scale) { return __float_as_uint(fmaf(x, scale, 8388608.f + 32768.f)); }
@@ -697,7 +681,6 @@ __global__ void __launch_bounds__(128 * EWQ + 128, 1) gru_seq_kernel(const __gri
       for (int tile = blockIdx.x; tile < sp.tiles; tile += gridDim.x, ++item) {
         const int us = tile % US, mt = (tile / US) % MT, dir = tile / (US * MT);
         const int t = dir == 0 ? step : T - 1 - step;
-        const int wslot = dir == 0 ? t + 1 : t;
         const int m0 = mt * S_BM, u0 = us * S_UN, b = m0 + row;
         const int uh = u0 + UT * sub;
         const bool row_ok = b < p.B;
