@@ -320,7 +320,7 @@ def kernel_rooflines(lib, steps, B, pk):
                     "peak_source": f"HBM copy bandwidth, {pk['src']} (MEASURED_PEAKS.json); kernel timed inside the step",
                     "timed": "CUDA events around every launch on its stream, over K steps run with both towers on one stream "
                              "right after the timed region (the headline steps overlap the towers on two streams)",
-                    "why_hbm": "at the saved-gate formats this kernel's HBM floor exceeds its tensor floor (DESIGN.md 5)"})
+                    "why_hbm": "at the saved-gate formats this kernel's HBM floor exceeds its tensor floor (DESIGN.md section 4)"})
     out.sort(key=lambda r: -r["ms_per_step"])
     return out, fams
 
