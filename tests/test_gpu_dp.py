@@ -1,5 +1,6 @@
 """GPU x2: the data-parallel step under NCCL against one process on the concatenated batch (loss, every gradient, mined
-indices), with the towers on two streams and on one, eager and captured in a CUDA graph.  Needs two visible GPUs
+indices), with the towers on two streams and on one, eager and graphed (world > 1: `GraphedTowers` - tower forward / backward
+replayed from CUDA graphs, collectives eager; world 1: the whole step in one graph).  Needs two visible GPUs
 (`gpurun --gpus 2`); the single-GPU driver tier skips it - `bench.py` repeats the same check at every N > 1 and reports it
 as `parity_check` in its JSON line."""
 import os

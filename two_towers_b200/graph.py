@@ -171,7 +171,10 @@ class GraphedTowers:
     optimizer stay eager.  This is the data-parallel form of GraphedTrainStep: NCCL collectives captured INSIDE a CUDA graph
     cost ~2.5 ms per step at 8 GPUs (measured: 25.4 vs 22.8 ms, profiles/r2_summary.md), so under data parallelism only the
     collective-free part of the step is graphed.  Dropout draws fresh masks on every call (device seed, bumped here).
-    Train mode only; the model must keep returning a (query_vec, doc_vec) tuple."""
+    Train mode only; the model must keep returning a (query_vec, doc_vec) tuple.  The outputs and everything the backward
+    graph reads are static buffers of the capture: run backward (or drop the outputs) before calling again with the same
+    input shape - two forwards in flight for one shape would share them (gradient accumulation over micro-batches works:
+    forward, backward, forward, backward)."""
 
     def __init__(self, model, warmup=2):
         self.model, self.warmup = model, max(1, int(warmup))
