@@ -753,8 +753,6 @@ def run_ours(args):
             nxt = upload(i + 1)
         st.wait_event(ev)
         tb = time.perf_counter()
-        if os.environ.get("TT_E2E_RESIDENT") == "1":              # diagnosis only: the step reads the resident copy instead
-            qd, dd = resident[i % nb]
         loss, _ = step(qd, dd)
         slot_free[i & 1] = torch.cuda.Event()
         slot_free[i & 1].record(st)
@@ -762,8 +760,7 @@ def run_ours(args):
         if dbg:
             step_done.append(torch.cuda.Event(enable_timing=True))
             step_done[-1].record(st)
-        if os.environ.get("TT_E2E_NOLOSS") != "1":                # diagnosis only
-            loss_host[i % NS].copy_(loss.detach(), non_blocking=True)
+        loss_host[i % NS].copy_(loss.detach(), non_blocking=True)
         loss_ev[i % NS].record(st)
         if i >= LAG:
             loss_ev[(i - LAG) % NS].synchronize()
