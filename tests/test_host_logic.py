@@ -113,6 +113,22 @@ def _dp_worker(rank, world, port, ret):
         for (n_, p_), q_ in zip(net.named_parameters(), ref_net.parameters()):
             ok = ok and (p_.grad - q_.grad).norm() < 1e-5 * q_.grad.norm() + 1e-7
             ok = ok and p_.grad.untyped_storage().data_ptr() == red2._flat[red2._bucket_of[id(p_)]].untyped_storage().data_ptr()
+        red2.remove()
+        # overlap=False (TT_DP_OVERLAP=0): nothing is launched from the hooks, finish() reduces every bucket - same gradients;
+        # the bucket size comes from TT_DP_BUCKET_MB when the argument is omitted
+        os.environ["TT_DP_OVERLAP"], os.environ["TT_DP_BUCKET_MB"] = "0", "0.000001"
+        try:
+            net.zero_grad(set_to_none=True)
+            red3 = dops.GradientAllReducer(None, named_params=net.named_parameters())
+            ok = ok and red3.overlap is False and [len(b) for b in red3.buckets] == [1, 1, 1, 1]
+            net["b"](net["a"](xs[rank].reshape(-1, D))).square().sum().backward()
+            ok = ok and not any(red3._launched)
+            red3.finish()
+            for p_, q_ in zip(net.parameters(), ref_net.parameters()):
+                ok = ok and (p_.grad - q_.grad).norm() < 1e-5 * q_.grad.norm() + 1e-7
+            red3.remove()
+        finally:
+            del os.environ["TT_DP_OVERLAP"], os.environ["TT_DP_BUCKET_MB"]
         lo, hi = dops.shard_bounds(11)
         ok = ok and (lo, hi) == ((0, 6) if rank == 0 else (6, 11))
         ret[rank] = (bool(ok), loss.item(), full.item(), (w.grad - wf.grad).abs().max().item(), lo, hi)
