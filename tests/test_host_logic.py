@@ -183,3 +183,16 @@ def test_bench_synthetic_pairs_share_the_query_tokens():
         n = min(ql, dl)
         row, want = d[i, :dl].tolist(), q[i, :n].tolist()
         assert any(row[s:s + n] == want for s in range(dl - n + 1)), i
+
+
+def test_graph_wrappers_reject_misuse_before_touching_the_gpu():
+    """GraphedTrainStep needs a capturable optimizer; GraphedTowers is a training-step wrapper (eval mode raises)."""
+    import two_towers_b200 as tt
+    m = tt.EnhancedTwoTowerModel(20, 32)
+    with pytest.raises(ValueError, match="capturable"):
+        tt.GraphedTrainStep(m, tt.MarginRankingLoss(), tt.FusedAdam(m.parameters()))
+    step = tt.GraphedTrainStep(m, tt.MarginRankingLoss(), tt.FusedAdam(m.parameters(), capturable=True), mine_k=4)
+    assert step.replays == 0 and step.launches_per_replay(torch.zeros(2, 3), torch.zeros(2, 3)) is None
+    towers = tt.GraphedTowers(m.eval())
+    with pytest.raises(RuntimeError, match="training step"):
+        towers(torch.zeros(2, 3, dtype=torch.long), torch.zeros(2, 5, dtype=torch.long))
